@@ -1,0 +1,218 @@
+"""Host-side Python binding of the B200 LM_DISKANN query path (ctypes over include/lmd_b200.h).
+
+The product is the C-ABI library ``liblmd_b200.so`` (CUDA, sm_100a). This module only marshals
+pointers; it never computes a distance and has no CPU fallback: if the library is missing or no
+CUDA device is present, calls fail with :class:`LmdError`.
+
+The directory name contains a hyphen (it mirrors the reference's repository name), so import it with
+``importlib.import_module("duckdb-lm-diskann_b200")`` with the repository root on ``sys.path``.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblmd_b200.so")
+
+# common/ann.hpp:16-32
+METRIC_L2, METRIC_COSINE, METRIC_IP = 1, 2, 3
+VEC_FLOAT32, VEC_INT8 = 1, 2
+ROUTE_EXACT, ROUTE_TERNARY = 0, 1
+SEARCH_SEPARATE_RERANK = 1
+SEARCH_PER_QUERY_STATS = 2
+EMPTY_ROW_ID = np.iinfo(np.int64).max  # core/GraphManager.cpp:154-156
+OK, ERR_INVALID_ARG, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_UNSUPPORTED = range(6)
+METRIC_BY_NAME = {"L2": METRIC_L2, "COSINE": METRIC_COSINE, "IP": METRIC_IP}
+
+
+class LmdError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__("lmd status %d: %s" % (status, message))
+        self.status = status
+
+
+class Layout(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "count_off", "vector_off", "ids_off", "pos_off", "neg_off", "total_node_size", "ternary_edge_bytes")]
+
+
+class Config(C.Structure):
+    _fields_ = [("dims", C.c_uint32), ("r", C.c_uint32), ("metric", C.c_uint32), ("vec_type", C.c_uint32),
+                ("l_search", C.c_uint32), ("reserved", C.c_uint32), ("block_bytes", C.c_uint64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("queries", C.c_uint64), ("expansions", C.c_uint64), ("distance_evals", C.c_uint64),
+                ("reranked", C.c_uint64), ("filter_evictions", C.c_uint64), ("algorithmic_bytes", C.c_uint64),
+                ("traverse_ms", C.c_float), ("rerank_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
+                ("launches", C.c_uint32), ("l_used", C.c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+# every symbol include/lmd_b200.h declares: (name, restype, argtypes)
+_P = C.c_void_p
+SYMBOLS = [
+    ("lmd_layout_calc", C.c_int32, [C.c_uint64, C.c_uint32, C.c_uint32, C.POINTER(Layout)]),
+    ("lmd_block_bytes", C.c_uint64, [C.c_uint64]),
+    ("lmd_store_create", C.c_int32, [C.POINTER(Config), C.c_int, C.c_uint64, C.POINTER(_P)]),
+    ("lmd_store_destroy", C.c_int32, [_P]),
+    ("lmd_store_upload", C.c_int32, [_P, _P, _P, C.c_uint64]),
+    ("lmd_store_update", C.c_int32, [_P, C.c_int64, _P]),
+    ("lmd_store_set_entry", C.c_int32, [_P, C.c_int64]),
+    ("lmd_store_finalize", C.c_int32, [_P]),
+    ("lmd_store_download_block", C.c_int32, [_P, C.c_int64, _P]),
+    ("lmd_store_node_count", C.c_uint64, [_P]),
+    ("lmd_store_device_bytes", C.c_uint64, [_P]),
+    ("lmd_search_batch", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P,
+                                    _P, C.POINTER(Stats)]),
+    ("lmd_merge_topk", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P]),
+    ("lmd_last_error", C.c_char_p, []),
+    ("lmd_abi_version", C.c_uint32, []),
+    ("lmd_set_tuning", C.c_int32, [_P, C.c_char_p, C.c_int64]),
+]
+
+_lib = None
+
+
+def lib():
+    """Loads liblmd_b200.so. Raises if it has not been built - there is nothing to fall back to."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise LmdError(ERR_STATE, "%s is missing: run `python duckdb-lm-diskann_b200/build.py` "
+                                      "(there is no CPU fallback)" % LIB_PATH)
+        l = C.CDLL(LIB_PATH)
+        for name, res, args in SYMBOLS:
+            f = getattr(l, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = l
+    return _lib
+
+
+def _check(status):
+    if status != OK:
+        raise LmdError(status, lib().lmd_last_error().decode("utf-8", "replace"))
+
+
+def _ptr(x):
+    """Address of a numpy array (host) or of anything with .data_ptr() (torch tensor, host or device)."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if hasattr(x, "data_ptr"):
+        if hasattr(x, "is_contiguous") and not x.is_contiguous():
+            raise ValueError("tensor must be contiguous")
+        return x.data_ptr()
+    if isinstance(x, np.ndarray):
+        if not x.flags["C_CONTIGUOUS"]:
+            raise ValueError("array must be C-contiguous")
+        return x.ctypes.data
+    raise TypeError("unsupported buffer type %r" % type(x))
+
+
+def layout_calc(dims, vec_type=VEC_FLOAT32, r=64):
+    """core/index_config.cpp:104-148 through the C ABI (host code; no device needed)."""
+    out = Layout()
+    _check(lib().lmd_layout_calc(dims, vec_type, r, C.byref(out)))
+    return out
+
+
+def block_bytes(total_node_size):
+    return int(lib().lmd_block_bytes(total_node_size))
+
+
+class Store:
+    """Device node store + search. Mirrors the query-side surface of the reference:
+    IStorageManager::GetNodeBlockData / IGraphManager::{TryGetNodePointer, GetEntryPoint*} are replaced by
+    upload()/set_entry(), ISearcher::Search by search()."""
+
+    def __init__(self, dims, r, metric=METRIC_L2, vec_type=VEC_FLOAT32, l_search=100, capacity=0, device=0,
+                 block_bytes=0):
+        if isinstance(metric, str):
+            metric = METRIC_BY_NAME[metric.upper()]
+        self.cfg = Config(dims, r, metric, vec_type, l_search, 0, block_bytes)
+        self._h = _P()
+        _check(lib().lmd_store_create(C.byref(self.cfg), device, capacity, C.byref(self._h)))
+        self.layout = layout_calc(dims, vec_type, r)
+        self.block_bytes = block_bytes or int(lib().lmd_block_bytes(self.layout.total_node_size))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib().lmd_store_destroy(self._h)
+            self._h = _P()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def upload(self, blocks, row_ids=None, n=None):
+        if n is None:
+            n = blocks.shape[0]
+        if row_ids is not None and isinstance(row_ids, np.ndarray):
+            row_ids = np.ascontiguousarray(row_ids, dtype=np.int64)
+        _check(lib().lmd_store_upload(self._h, _ptr(row_ids), _ptr(blocks), n))
+
+    def update(self, row_id, block):
+        _check(lib().lmd_store_update(self._h, int(row_id), _ptr(block)))
+
+    def set_entry(self, row_id):
+        _check(lib().lmd_store_set_entry(self._h, int(row_id)))
+
+    def finalize(self):
+        _check(lib().lmd_store_finalize(self._h))
+
+    def download_block(self, row_id):
+        out = np.empty(self.block_bytes, dtype=np.uint8)
+        _check(lib().lmd_store_download_block(self._h, int(row_id), _ptr(out)))
+        return out
+
+    def set_tuning(self, key, value):
+        _check(lib().lmd_set_tuning(self._h, key.encode(), int(value)))
+
+    @property
+    def node_count(self):
+        return int(lib().lmd_store_node_count(self._h))
+
+    @property
+    def device_bytes(self):
+        return int(lib().lmd_store_device_bytes(self._h))
+
+    def search_raw(self, queries, nq, k, L=0, route=ROUTE_EXACT, flags=0, out_ids=None, out_dist=None, out_count=None,
+                   out_qstats=None):
+        """Thin call: any mix of numpy arrays / torch tensors / raw addresses, all on the same side."""
+        st = Stats()
+        _check(lib().lmd_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist),
+                                      _ptr(out_count), _ptr(out_qstats), C.byref(st)))
+        return st
+
+    def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0, qstats=False):
+        """Host-buffer search: queries [nq, dims] float32 numpy -> (ids [nq,k] int64, dist [nq,k] f32,
+        count [nq] u32, Stats[, qstats [nq,2] u32])."""
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim != 2 or q.shape[1] != self.cfg.dims:
+            # db/LmDiskannIndex.cpp:651-655
+            raise LmdError(ERR_INVALID_ARG, "Query vector dimension (%d) does not match index dimension (%d)." %
+                           (q.shape[-1] if q.ndim else 0, self.cfg.dims))
+        nq = q.shape[0]
+        ids = np.full((nq, k), -1, dtype=np.int64)
+        dist = np.zeros((nq, k), dtype=np.float32)
+        count = np.zeros(nq, dtype=np.uint32)
+        qs = np.zeros((nq, 2), dtype=np.uint32) if qstats else None
+        if qstats:
+            flags |= SEARCH_PER_QUERY_STATS
+        st = self.search_raw(q, nq, k, L, route, flags, ids, dist, count, qs)
+        return (ids, dist, count, st, qs) if qstats else (ids, dist, count, st)
+
+
+def merge_topk(ids, dist, shards, nq, k, out_ids, out_dist, device=0):
+    _check(lib().lmd_merge_topk(device, _ptr(ids), _ptr(dist), shards, nq, k, _ptr(out_ids), _ptr(out_dist)))

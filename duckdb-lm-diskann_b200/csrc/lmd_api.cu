@@ -1,0 +1,297 @@
+// lmd_search_batch / lmd_merge_topk: the batched replacement of core/ISearcher.hpp:30-34 (Search).
+// Host orchestration only: argument checks in the reference's order, staging of host buffers through
+// the store's stream, kernel launches, statistics.
+#include "lmd_common.cuh"
+
+#include <algorithm>
+#include <cstring>
+
+using namespace lmd;
+
+namespace {
+
+bool on_device(const void *p) {
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+template <typename T>
+lmd_status grow(T *&ptr, uint64_t &have, uint64_t need_elems, lmd_store *s) {
+	if (have >= need_elems && ptr) {
+		return LMD_OK;
+	}
+	if (ptr) {
+		cudaFree(ptr);
+		ptr = nullptr;
+	}
+	cudaError_t e = cudaMalloc((void **)&ptr, need_elems * sizeof(T));
+	if (e != cudaSuccess) {
+		have = 0;
+		set_error("cudaMalloc(%llu bytes) for search scratch failed: %s", (unsigned long long)(need_elems * sizeof(T)),
+		          cudaGetErrorString(e));
+		return LMD_ERR_OOM;
+	}
+	have = need_elems;
+	(void)s;
+	return LMD_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
+                            uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                            uint32_t *out_qstats, lmd_stats *stats) {
+	if (stats) {
+		memset(stats, 0, sizeof(*stats));
+	}
+	if (!s) {
+		set_error("lmd_search_batch: null store");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (k == 0) { // core/Coordinator.cpp:72-74, db/LmDiskannIndex.cpp:656-658
+		set_error("k_neighbors cannot be 0 for search");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (nq == 0) {
+		return LMD_OK;
+	}
+	if (!queries || !out_ids) {
+		set_error("lmd_search_batch: null queries / out_ids");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (nq > 0xFFFFFFF0ull) {
+		set_error("lmd_search_batch: batch too large");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (route != LMD_ROUTE_EXACT && route != LMD_ROUTE_TERNARY) {
+		set_error("lmd_search_batch: unknown route %u", route);
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (route == LMD_ROUTE_TERNARY && s->cfg.metric == LMD_METRIC_L2) {
+		// core/distance.hpp:236-239
+		set_error("L2 metric is not directly compatible with the current ternary CalculateApproxDistance");
+		return LMD_ERR_UNSUPPORTED;
+	}
+	// core/Searcher.cpp:261-265
+	uint32_t l_used = L > 0 ? L : s->cfg.l_search;
+	if (l_used == 0) {
+		l_used = k > 20 ? k + 20 : 40;
+	}
+	l_used = std::max(l_used, k);
+	if (l_used > 512) {
+		set_error("search list size L = %u exceeds this build's limit of 512", l_used);
+		return LMD_ERR_UNSUPPORTED;
+	}
+	if (s->dirty) {
+		lmd_status st = lmd_store_finalize(s);
+		if (st != LMD_OK) {
+			return st;
+		}
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	cudaStream_t st = s->stream;
+	const uint32_t q32 = (uint32_t)nq;
+	const bool dev_io = on_device(queries);
+	const bool separate = route == LMD_ROUTE_TERNARY || (flags & LMD_SEARCH_SEPARATE_RERANK);
+	const bool want_qstats = (flags & LMD_SEARCH_PER_QUERY_STATS) && out_qstats;
+	lmd_status rc;
+
+	const float *d_q = queries;
+	int64_t *d_ids = out_ids;
+	float *d_dist = out_dist;
+	uint32_t *d_count = out_count;
+	uint32_t *d_qstats = want_qstats ? out_qstats : nullptr;
+	if (!dev_io) {
+		uint64_t need_q = nq * (uint64_t)s->cfg.dims;
+		uint64_t have_q = s->scratch_q;
+		if ((rc = grow(s->d_q, have_q, need_q, s)) != LMD_OK) {
+			s->scratch_q = 0;
+			return rc;
+		}
+		s->scratch_q = have_q;
+		uint64_t need_k = nq * (uint64_t)k;
+		if (s->scratch_k < need_k || !s->d_out_ids) {
+			uint64_t a = 0, b = 0, c = 0, d = 0;
+			if ((rc = grow(s->d_out_ids, a, need_k, s)) != LMD_OK || (rc = grow(s->d_out_dist, b, need_k, s)) != LMD_OK ||
+			    (rc = grow(s->d_out_count, c, need_k, s)) != LMD_OK ||
+			    (rc = grow(s->d_qstats, d, std::max<uint64_t>(need_k, 2 * nq), s)) != LMD_OK) {
+				s->scratch_k = 0;
+				return rc;
+			}
+			s->scratch_k = need_k;
+		}
+		LMD_CUDA_OK(cudaEventRecord(s->ev[0], st));
+		LMD_CUDA_OK(cudaMemcpyAsync(s->d_q, queries, need_q * sizeof(float), cudaMemcpyHostToDevice, st));
+		d_q = s->d_q;
+		d_ids = s->d_out_ids;
+		d_dist = s->d_out_dist; // always computed on the device; copied back only when asked for
+		d_count = s->d_out_count;
+		d_qstats = want_qstats ? s->d_qstats : nullptr;
+	}
+	uint64_t *d_cand = nullptr;
+	if (separate) {
+		uint64_t need_c = nq * (uint64_t)l_used;
+		uint64_t have_c = s->scratch_cand;
+		if ((rc = grow(s->d_cand, have_c, need_c, s)) != LMD_OK) {
+			s->scratch_cand = 0;
+			return rc;
+		}
+		s->scratch_cand = have_c;
+		d_cand = s->d_cand;
+	}
+	LMD_CUDA_OK(cudaMemsetAsync(s->d_counters, 0, 5 * sizeof(unsigned long long), st));
+
+	TraverseArgs ta;
+	ta.s = s;
+	ta.d_queries = d_q;
+	ta.nq = q32;
+	ta.k = k;
+	ta.L = l_used;
+	ta.route = route;
+	ta.d_out_ids = separate ? nullptr : d_ids;
+	ta.d_out_dist = separate ? nullptr : d_dist;
+	ta.d_out_count = separate ? nullptr : d_count;
+	ta.d_qstats = d_qstats;
+	ta.d_cand = d_cand;
+	LMD_CUDA_OK(cudaEventRecord(s->ev[1], st));
+	if ((rc = launch_traverse(ta, st)) != LMD_OK) {
+		return rc;
+	}
+	LMD_CUDA_OK(cudaEventRecord(s->ev[2], st));
+	uint32_t launches = 1;
+	if (separate) {
+		RerankArgs ra;
+		ra.s = s;
+		ra.d_queries = d_q;
+		ra.nq = q32;
+		ra.k = k;
+		ra.L = l_used;
+		ra.d_cand = d_cand;
+		ra.d_out_ids = d_ids;
+		ra.d_out_dist = d_dist;
+		ra.d_out_count = d_count;
+		if ((rc = launch_rerank(ra, st)) != LMD_OK) {
+			return rc;
+		}
+		launches++;
+	}
+	LMD_CUDA_OK(cudaEventRecord(s->ev[3], st));
+	if (!dev_io) {
+		LMD_CUDA_OK(cudaMemcpyAsync(out_ids, d_ids, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+		if (out_dist) {
+			LMD_CUDA_OK(cudaMemcpyAsync(out_dist, d_dist, nq * k * sizeof(float), cudaMemcpyDeviceToHost, st));
+		}
+		if (out_count) {
+			LMD_CUDA_OK(cudaMemcpyAsync(out_count, d_count, nq * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		}
+		if (want_qstats) {
+			LMD_CUDA_OK(cudaMemcpyAsync(out_qstats, d_qstats, nq * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		}
+	}
+	unsigned long long h_cnt[5] = {0, 0, 0, 0, 0};
+	if (stats) {
+		LMD_CUDA_OK(cudaMemcpyAsync(h_cnt, s->d_counters, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
+	}
+	LMD_CUDA_OK(cudaEventRecord(s->ev[4], st));
+	cudaError_t e = cudaStreamSynchronize(st);
+	if (e != cudaSuccess) {
+		set_error("search kernels failed: %s", cudaGetErrorString(e));
+		return LMD_ERR_CUDA;
+	}
+	if (stats) {
+		stats->queries = nq;
+		stats->expansions = h_cnt[1];
+		stats->distance_evals = h_cnt[2];
+		stats->filter_evictions = h_cnt[3];
+		stats->reranked = h_cnt[4];
+		stats->launches = launches;
+		stats->l_used = l_used;
+		cudaEventElapsedTime(&stats->traverse_ms, s->ev[1], s->ev[2]);
+		if (separate) {
+			cudaEventElapsedTime(&stats->rerank_ms, s->ev[2], s->ev[3]);
+		}
+		if (!dev_io) {
+			cudaEventElapsedTime(&stats->h2d_ms, s->ev[0], s->ev[1]);
+			cudaEventElapsedTime(&stats->d2h_ms, s->ev[3], s->ev[4]);
+		}
+		// SURVEY.md section 8d. The sidecar holds uint32 slots, so an expansion reads 4R bytes of ids
+		// (the reference's 8 + 8R becomes 4R); padding is never counted.
+		const uint64_t vec = (uint64_t)s->cfg.dims * 4;
+		uint64_t bytes = nq * ((uint64_t)s->cfg.dims * 4 + (uint64_t)k * 12);
+		if (route == LMD_ROUTE_EXACT) {
+			bytes += h_cnt[1] * 4ull * s->cfg.r + h_cnt[2] * vec;
+		} else {
+			bytes += h_cnt[1] * (4ull * s->cfg.r) + h_cnt[2] * (uint64_t)s->lay.ternary_edge_bytes + vec * nq;
+		}
+		bytes += h_cnt[4] * vec;
+		if (separate) {
+			bytes += 2ull * nq * l_used * 8; // candidate list written by the traversal, read by the rerank
+		}
+		stats->algorithmic_bytes = bytes;
+	}
+	return LMD_OK;
+}
+
+lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq, uint32_t k,
+                          int64_t *out_ids, float *out_dist) {
+	if (!ids || !dist || !out_ids || !out_dist) {
+		set_error("lmd_merge_topk: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (k == 0 || shards == 0 || shards > 64) {
+		set_error("lmd_merge_topk: k must be > 0 and shards in [1, 64]");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (nq == 0) {
+		return LMD_OK;
+	}
+	LMD_CUDA_OK(cudaSetDevice(device));
+	const bool dev_io = on_device(ids);
+	const uint64_t in_elems = (uint64_t)shards * nq * k, out_elems = nq * k;
+	if (dev_io) {
+		lmd_status rc = launch_merge_topk(ids, dist, shards, nq, k, out_ids, out_dist, 0);
+		if (rc != LMD_OK) {
+			return rc;
+		}
+		LMD_CUDA_OK(cudaStreamSynchronize(0));
+		return LMD_OK;
+	}
+	int64_t *d_ids = nullptr, *d_oids = nullptr;
+	float *d_dist = nullptr, *d_odist = nullptr;
+	lmd_status rc = LMD_OK;
+	auto cleanup = [&]() {
+		cudaFree(d_ids);
+		cudaFree(d_oids);
+		cudaFree(d_dist);
+		cudaFree(d_odist);
+	};
+	if (cudaMalloc((void **)&d_ids, in_elems * 8) != cudaSuccess || cudaMalloc((void **)&d_dist, in_elems * 4) != cudaSuccess ||
+	    cudaMalloc((void **)&d_oids, out_elems * 8) != cudaSuccess ||
+	    cudaMalloc((void **)&d_odist, out_elems * 4) != cudaSuccess) {
+		cleanup();
+		set_error("lmd_merge_topk: cudaMalloc failed");
+		return LMD_ERR_OOM;
+	}
+	cudaMemcpy(d_ids, ids, in_elems * 8, cudaMemcpyHostToDevice);
+	cudaMemcpy(d_dist, dist, in_elems * 4, cudaMemcpyHostToDevice);
+	rc = launch_merge_topk(d_ids, d_dist, shards, nq, k, d_oids, d_odist, 0);
+	if (rc == LMD_OK) {
+		cudaMemcpy(out_ids, d_oids, out_elems * 8, cudaMemcpyDeviceToHost);
+		cudaError_t e = cudaMemcpy(out_dist, d_odist, out_elems * 4, cudaMemcpyDeviceToHost);
+		if (e != cudaSuccess) {
+			set_error("lmd_merge_topk: %s", cudaGetErrorString(e));
+			rc = LMD_ERR_CUDA;
+		}
+	}
+	cleanup();
+	return rc;
+}
+
+} // extern "C"

@@ -1,0 +1,153 @@
+// Shared declarations of the B200 LM_DISKANN query path (device node store + kernels).
+// sm_100a only; no CPU fallback anywhere below this header.
+#pragma once
+
+#include "../../include/lmd_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <mutex>
+#include <string>
+
+#define LMD_INVALID_SLOT 0xFFFFFFFFu
+#define LMD_KEY_NONE 0xFFFFFFFFFFFFFFFFull
+
+namespace lmd {
+
+void set_error(const char *fmt, ...);
+
+#define LMD_CUDA_OK(expr)                                                                                              \
+	do {                                                                                                               \
+		cudaError_t _e = (expr);                                                                                       \
+		if (_e != cudaSuccess) {                                                                                       \
+			lmd::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__);                \
+			return (_e == cudaErrorMemoryAllocation) ? LMD_ERR_OOM : LMD_ERR_CUDA;                                     \
+		}                                                                                                              \
+	} while (0)
+
+// ---- candidate keys -------------------------------------------------------------------------
+// A candidate is one u64: [63:32] order-preserving image of the fp32 distance, [31:1] slot, [0] expanded flag.
+// Unsigned comparison of (key >> 1) is the reference's H4 order (distance, id) with id = slot
+// (core/Searcher.cpp:35-37 + oracle/patches/searcher_fixed.patch).
+__host__ __device__ __forceinline__ uint32_t float_to_ordered(float f) {
+#ifdef __CUDA_ARCH__
+	uint32_t b = __float_as_uint(f);
+#else
+	union {
+		float f;
+		uint32_t u;
+	} cv;
+	cv.f = f;
+	uint32_t b = cv.u;
+#endif
+	return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ordered_to_float(uint32_t o) {
+	uint32_t b = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+#ifdef __CUDA_ARCH__
+	return __uint_as_float(b);
+#else
+	union {
+		float f;
+		uint32_t u;
+	} cv;
+	cv.u = b;
+	return cv.f;
+#endif
+}
+__host__ __device__ __forceinline__ uint64_t make_key(float d, uint32_t slot) {
+	return ((uint64_t)float_to_ordered(d) << 32) | ((uint64_t)slot << 1);
+}
+__host__ __device__ __forceinline__ uint32_t key_slot(uint64_t k) {
+	return (uint32_t)(k & 0xFFFFFFFFull) >> 1;
+}
+__host__ __device__ __forceinline__ float key_dist(uint64_t k) {
+	return ordered_to_float((uint32_t)(k >> 32));
+}
+
+// ---- the store ---------------------------------------------------------------------------------
+struct Tuning {
+	int filter_log2 = 0;   // 0 = heuristic
+	int warps_per_cta = 4;
+	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
+};
+
+} // namespace lmd
+
+struct lmd_store {
+	lmd_config cfg;
+	lmd_layout lay;
+	int device = 0;
+	int sm_count = 148;
+	uint64_t capacity = 0; // nodes
+	uint64_t n = 0;        // nodes uploaded
+	uint32_t row_floats = 0; // packed row length (dims padded to 32 floats)
+	uint32_t words = 0;      // u64 words per ternary plane
+
+	// device memory (all owned)
+	uint8_t *d_blocks = nullptr;   // [capacity][block_bytes]   raw mirror, reference layout untouched
+	float *d_vecs = nullptr;       // [capacity][row_floats]    packed fp32 view of the node vectors
+	uint32_t *d_nbrs = nullptr;    // [capacity][r]             neighbour SLOTS (sidecar), LMD_INVALID_SLOT = none
+	int64_t *d_row_ids = nullptr;  // [capacity]                slot -> row id
+	int64_t *d_map_keys = nullptr; // [map_cap]                 row id -> slot, open addressing
+	uint32_t *d_map_vals = nullptr;
+	uint64_t map_cap = 0;
+	bool identity = true;          // every row id so far equals its slot: the map is bypassed
+	unsigned long long *d_counters = nullptr; // [8] work counter + statistics
+	uint64_t device_bytes = 0;
+
+	// scratch for host<->device staging of one search call (grown on demand)
+	float *d_q = nullptr;
+	int64_t *d_out_ids = nullptr;
+	float *d_out_dist = nullptr;
+	uint32_t *d_out_count = nullptr;
+	uint32_t *d_qstats = nullptr;
+	uint64_t *d_cand = nullptr; // [nq][L] candidate keys for the separate rerank kernel
+	uint64_t scratch_q = 0, scratch_k = 0, scratch_cand = 0;
+	void *h_stage = nullptr; // pinned staging for pageable uploads
+	size_t h_stage_bytes = 0;
+
+	bool has_entry = false;
+	int64_t entry_row = INT64_MAX;
+	uint32_t entry_slot = LMD_INVALID_SLOT;
+	bool dirty = true; // views need (re)building
+
+	cudaStream_t stream = nullptr, copy_stream = nullptr;
+	cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+	lmd::Tuning tune;
+	std::mutex mu;
+};
+
+namespace lmd {
+
+// Kernel launchers (each returns a status and has set_error() on failure).
+struct TraverseArgs {
+	const lmd_store *s;
+	const float *d_queries; // [nq][dims]
+	uint32_t nq, k, L, route;
+	int64_t *d_out_ids;   // [nq][k] or null when the separate rerank writes them
+	float *d_out_dist;    // [nq][k] or null
+	uint32_t *d_out_count;
+	uint32_t *d_qstats;   // [nq][2] or null
+	uint64_t *d_cand;     // [nq][L] or null
+};
+lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st);
+
+struct RerankArgs {
+	const lmd_store *s;
+	const float *d_queries;
+	uint32_t nq, k, L;
+	const uint64_t *d_cand; // [nq][L], LMD_KEY_NONE padded
+	int64_t *d_out_ids;
+	float *d_out_dist;
+	uint32_t *d_out_count;
+};
+lmd_status launch_rerank(const RerankArgs &a, cudaStream_t st);
+
+lmd_status launch_merge_topk(const int64_t *d_ids, const float *d_dist, uint32_t shards, uint64_t nq, uint32_t k,
+                             int64_t *d_out_ids, float *d_out_dist, cudaStream_t st);
+
+} // namespace lmd

@@ -1,0 +1,603 @@
+// Device node store: HBM mirror of the LM_DISKANN node blocks + the derived search views.
+//
+// Replaces, on the query path, core/IStorageManager.hpp:156 (GetNodeBlockData) and the
+// std::map<row_t, IndexPointer> behind core/GraphManager.cpp:523-531 (TryGetNodePointer).
+//
+// HBM layout (per store, N = capacity):
+//   d_blocks  [N][block_bytes]  raw blocks, reference layout untouched (core/index_config.cpp:104-148)
+//   d_vecs    [N][row_floats]   node vectors as fp32, rows padded with zeros to 128 B multiples so that every
+//                               gather is 16-byte aligned (the in-block vector sits at offset 8)
+//   d_nbrs    [N][r] u32        neighbour SLOTS: ids[j] of the block resolved once through the row-id map,
+//                               LMD_INVALID_SLOT for j >= count, INT64_MAX sentinels and unknown row ids
+//                               (the three skip rules of GraphManager.cpp:241-254 and Searcher.cpp:132,146)
+//   d_row_ids [N] i64           slot -> row id for the result write-out
+#include "lmd_common.cuh"
+
+#include <cstring>
+#include <new>
+
+namespace lmd {
+
+static thread_local std::string g_err;
+
+void set_error(const char *fmt, ...) {
+	char buf[1024];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	g_err = buf;
+}
+
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+	x ^= x >> 33;
+	x *= 0xff51afd7ed558ccdULL;
+	x ^= x >> 33;
+	x *= 0xc4ceb9fe1a85ec53ULL;
+	x ^= x >> 33;
+	return x;
+}
+
+#define LMD_MAP_EMPTY ((long long)0x8000000000000000LL) // INT64_MIN is never a DuckDB row id
+
+// One thread per uploaded node: record row id, insert row id -> slot.
+// A row id seen twice keeps the LATEST slot (an update of the mapping, like std::map::operator[]).
+__global__ void ingest_rowids_kernel(const int64_t *row_ids, uint64_t base, uint64_t n,
+                                     int64_t *slot_row, long long *map_keys, uint32_t *map_vals,
+                                     uint64_t map_mask) {
+	uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (i >= n) {
+		return;
+	}
+	int64_t rid = row_ids ? row_ids[i] : (int64_t)(base + i);
+	slot_row[base + i] = rid;
+	uint64_t h = mix64((uint64_t)rid) & map_mask;
+	for (;;) {
+		long long old = (long long)atomicCAS((unsigned long long *)&map_keys[h], (unsigned long long)LMD_MAP_EMPTY,
+		                                     (unsigned long long)rid);
+		if (old == LMD_MAP_EMPTY || old == (long long)rid) {
+			atomicMax(&map_vals[h], (uint32_t)(base + i)); // later slot wins deterministically
+			return;
+		}
+		h = (h + 1) & map_mask;
+	}
+}
+
+__device__ __forceinline__ uint32_t map_lookup(const long long *__restrict__ map_keys,
+                                               const uint32_t *__restrict__ map_vals, uint64_t map_mask, int64_t rid) {
+	uint64_t h = mix64((uint64_t)rid) & map_mask;
+	for (;;) {
+		long long k = map_keys[h];
+		if (k == (long long)rid) {
+			return map_vals[h];
+		}
+		if (k == LMD_MAP_EMPTY) {
+			return LMD_INVALID_SLOT;
+		}
+		h = (h + 1) & map_mask;
+	}
+}
+
+__global__ void lookup_one_kernel(const long long *map_keys, const uint32_t *map_vals, uint64_t map_mask, int64_t rid,
+                                  uint32_t *out) {
+	*out = map_lookup(map_keys, map_vals, map_mask, rid);
+}
+
+// One warp per node: unpack the node vector of block `slot` into the packed fp32 row (common/ann.hpp:42-62:
+// FLOAT32 is a byte copy, INT8 is a plain static_cast<float>), zero the padding.
+__global__ void unpack_vectors_kernel(const uint8_t *__restrict__ blocks, uint64_t block_bytes, uint64_t vector_off,
+                                      uint32_t dims, uint32_t vec_type, uint32_t row_floats, uint64_t base, uint64_t n,
+                                      float *__restrict__ vecs) {
+	uint64_t node = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+	uint32_t lane = threadIdx.x & 31;
+	if (node >= n) {
+		return;
+	}
+	const uint8_t *src = blocks + (base + node) * block_bytes + vector_off;
+	float *dst = vecs + (base + node) * (uint64_t)row_floats;
+	for (uint32_t i = lane; i < row_floats; i += 32) {
+		float v = 0.0f;
+		if (i < dims) {
+			if (vec_type == LMD_VEC_FLOAT32) {
+				v = reinterpret_cast<const float *>(src)[i]; // vector_off is 8-aligned, block base 256-aligned
+			} else {
+				v = (float)reinterpret_cast<const int8_t *>(src)[i];
+			}
+		}
+		dst[i] = v;
+	}
+}
+
+// One thread per (node, j): resolve neighbour j of the mirrored block to a slot.
+// core/GraphManager.cpp:241-254: only the first `count` ids are neighbours, INT64_MAX entries are dropped;
+// core/Searcher.cpp:146-148: a row id that does not resolve is skipped.
+__global__ void build_sidecar_kernel(const uint8_t *__restrict__ blocks, uint64_t block_bytes, uint64_t count_off,
+                                     uint64_t ids_off, uint32_t r, uint64_t n, int identity,
+                                     const long long *__restrict__ map_keys, const uint32_t *__restrict__ map_vals,
+                                     uint64_t map_mask, uint32_t *__restrict__ nbrs) {
+	uint64_t t = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	uint64_t node = t / r;
+	uint32_t j = (uint32_t)(t % r);
+	if (node >= n) {
+		return;
+	}
+	const uint8_t *blk = blocks + node * block_bytes;
+	uint32_t count = *reinterpret_cast<const uint16_t *>(blk + count_off);
+	uint32_t out = LMD_INVALID_SLOT;
+	if (j < count) {
+		int64_t rid = reinterpret_cast<const int64_t *>(blk + ids_off)[j];
+		if (rid != INT64_MAX) {
+			if (identity) {
+				out = (rid >= 0 && (uint64_t)rid < n) ? (uint32_t)rid : LMD_INVALID_SLOT;
+			} else {
+				out = map_lookup(map_keys, map_vals, map_mask, rid);
+			}
+		}
+	}
+	nbrs[node * r + j] = out;
+}
+
+__global__ void fill_i64_kernel(long long *p, uint64_t n, long long v) {
+	uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (i < n) {
+		p[i] = v;
+	}
+}
+
+__global__ void check_identity_kernel(const int64_t *row_ids, uint64_t base, uint64_t n, int *not_identity) {
+	uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (i < n && row_ids[i] != (int64_t)(base + i)) {
+		*not_identity = 1;
+	}
+}
+
+static bool is_device_ptr(const void *p) {
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+static lmd_status lookup_slot(lmd_store *s, int64_t row_id, uint32_t *slot) {
+	if (s->identity) {
+		*slot = (row_id >= 0 && (uint64_t)row_id < s->n) ? (uint32_t)row_id : LMD_INVALID_SLOT;
+		return LMD_OK;
+	}
+	uint32_t *d_tmp = reinterpret_cast<uint32_t *>(s->d_counters + 7);
+	lookup_one_kernel<<<1, 1, 0, s->stream>>>((const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, row_id,
+	                                          d_tmp);
+	LMD_CUDA_OK(cudaGetLastError());
+	LMD_CUDA_OK(cudaMemcpyAsync(slot, d_tmp, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+	return LMD_OK;
+}
+
+} // namespace lmd
+
+using namespace lmd;
+
+extern "C" {
+
+const char *lmd_last_error(void) {
+	return g_err.c_str();
+}
+
+uint32_t lmd_abi_version(void) {
+	return LMD_ABI_VERSION;
+}
+
+static uint64_t align_up64(uint64_t v, uint64_t a) {
+	return (v + a - 1) / a * a;
+}
+
+// core/index_config.cpp:104-148 (CalculateLayoutInternal); element sizes :40-52, plane sizes :55-64,
+// words per plane core/ternary_quantization.hpp:120-123.
+lmd_status lmd_layout_calc(uint64_t dims, uint32_t vec_type, uint32_t r, lmd_layout *out) {
+	if (!out) {
+		set_error("lmd_layout_calc: out is null");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (dims == 0 || (vec_type != LMD_VEC_FLOAT32 && vec_type != LMD_VEC_INT8)) {
+		set_error("CalculateLayoutInternal requires dimensions and node_vector_type to be set in config");
+		return LMD_ERR_INVALID_ARG;
+	}
+	const uint64_t elem = vec_type == LMD_VEC_FLOAT32 ? 4 : 1;
+	const uint64_t plane = ((dims + 63) >> 6) * 8;
+	uint64_t off = sizeof(uint16_t);
+	out->count_off = 0;
+	off = align_up64(off, 8);
+	out->vector_off = off;
+	off = align_up64(off + elem * dims, 8);
+	out->ids_off = off;
+	off = align_up64(off + (uint64_t)r * 8, 8);
+	out->pos_off = off;
+	off = align_up64(off + (uint64_t)r * plane, 8);
+	out->neg_off = off;
+	off += (uint64_t)r * plane;
+	out->total_node_size = off;
+	out->ternary_edge_bytes = 2 * plane;
+	return LMD_OK;
+}
+
+// db/LmDiskannIndex.cpp:161-162 with Storage::SECTOR_SIZE = 4096
+uint64_t lmd_block_bytes(uint64_t total_node_size) {
+	return align_up64(total_node_size, 4096);
+}
+
+lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity_nodes, lmd_store **out) {
+	if (!cfg || !out) {
+		set_error("lmd_store_create: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	*out = nullptr;
+	// core/index_config.cpp:66-102 (ValidateParameters), the parts that concern the query path
+	if (cfg->r == 0) {
+		set_error("LM_DISKANN parameter R must be > 0");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (cfg->metric != LMD_METRIC_L2 && cfg->metric != LMD_METRIC_COSINE && cfg->metric != LMD_METRIC_IP) {
+		set_error("Unsupported metric type %u", cfg->metric);
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (capacity_nodes == 0 || capacity_nodes >= 0x7FFFFFFFull) {
+		set_error("capacity_nodes must be in [1, 2^31-1)");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (cfg->r > 1024) {
+		set_error("R = %u exceeds this build's limit of 1024", cfg->r);
+		return LMD_ERR_UNSUPPORTED;
+	}
+	lmd_layout lay;
+	lmd_status st = lmd_layout_calc(cfg->dims, cfg->vec_type, cfg->r, &lay);
+	if (st != LMD_OK) {
+		return st;
+	}
+	uint64_t bb = cfg->block_bytes ? cfg->block_bytes : lmd_block_bytes(lay.total_node_size);
+	if (bb < lay.total_node_size || (bb % 8) != 0) {
+		set_error("block_bytes %llu smaller than the node layout (%llu) or not a multiple of 8",
+		          (unsigned long long)bb, (unsigned long long)lay.total_node_size);
+		return LMD_ERR_INVALID_ARG;
+	}
+	int ndev = 0;
+	LMD_CUDA_OK(cudaGetDeviceCount(&ndev));
+	if (device < 0 || device >= ndev) {
+		set_error("device %d out of range (%d visible)", device, ndev);
+		return LMD_ERR_INVALID_ARG;
+	}
+	LMD_CUDA_OK(cudaSetDevice(device));
+	lmd_store *s = new (std::nothrow) lmd_store();
+	if (!s) {
+		set_error("host allocation failed");
+		return LMD_ERR_OOM;
+	}
+	s->cfg = *cfg;
+	s->cfg.block_bytes = bb;
+	s->lay = lay;
+	s->device = device;
+	s->capacity = capacity_nodes;
+	s->row_floats = (uint32_t)align_up64(cfg->dims, 32);
+	s->words = (uint32_t)((cfg->dims + 63) >> 6);
+	cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
+	s->map_cap = 64;
+	while (s->map_cap < capacity_nodes * 2) {
+		s->map_cap <<= 1;
+	}
+	auto fail = [&](lmd_status code) {
+		lmd_store_destroy(s);
+		return code;
+	};
+#define LMD_ALLOC(ptr, bytes)                                                                                          \
+	do {                                                                                                               \
+		cudaError_t _e = cudaMalloc((void **)&(ptr), (bytes));                                                         \
+		if (_e != cudaSuccess) {                                                                                       \
+			set_error("cudaMalloc(%llu bytes) for %s failed: %s", (unsigned long long)(bytes), #ptr,                   \
+			          cudaGetErrorString(_e));                                                                         \
+			return fail(LMD_ERR_OOM);                                                                                  \
+		}                                                                                                              \
+		s->device_bytes += (bytes);                                                                                    \
+	} while (0)
+	LMD_ALLOC(s->d_blocks, capacity_nodes * bb);
+	LMD_ALLOC(s->d_vecs, capacity_nodes * (uint64_t)s->row_floats * sizeof(float));
+	LMD_ALLOC(s->d_nbrs, capacity_nodes * (uint64_t)cfg->r * sizeof(uint32_t));
+	LMD_ALLOC(s->d_row_ids, capacity_nodes * sizeof(int64_t));
+	LMD_ALLOC(s->d_map_keys, s->map_cap * sizeof(int64_t));
+	LMD_ALLOC(s->d_map_vals, s->map_cap * sizeof(uint32_t));
+	LMD_ALLOC(s->d_counters, 8 * sizeof(unsigned long long));
+#undef LMD_ALLOC
+	if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess ||
+	    cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+		set_error("cudaStreamCreate failed");
+		return fail(LMD_ERR_CUDA);
+	}
+	for (auto &e : s->ev) {
+		if (cudaEventCreate(&e) != cudaSuccess) {
+			set_error("cudaEventCreate failed");
+			return fail(LMD_ERR_CUDA);
+		}
+	}
+	fill_i64_kernel<<<(unsigned)((s->map_cap + 255) / 256), 256, 0, s->stream>>>((long long *)s->d_map_keys, s->map_cap,
+	                                                                              LMD_MAP_EMPTY);
+	if (cudaGetLastError() != cudaSuccess || cudaMemsetAsync(s->d_map_vals, 0, s->map_cap * 4, s->stream) != cudaSuccess ||
+	    cudaMemsetAsync(s->d_counters, 0, 64, s->stream) != cudaSuccess ||
+	    cudaStreamSynchronize(s->stream) != cudaSuccess) {
+		set_error("store initialisation failed: %s", cudaGetErrorString(cudaGetLastError()));
+		return fail(LMD_ERR_CUDA);
+	}
+	*out = s;
+	return LMD_OK;
+}
+
+lmd_status lmd_store_destroy(lmd_store *s) {
+	if (!s) {
+		return LMD_OK;
+	}
+	cudaSetDevice(s->device);
+	if (s->stream) {
+		cudaStreamSynchronize(s->stream);
+	}
+	cudaFree(s->d_blocks);
+	cudaFree(s->d_vecs);
+	cudaFree(s->d_nbrs);
+	cudaFree(s->d_row_ids);
+	cudaFree(s->d_map_keys);
+	cudaFree(s->d_map_vals);
+	cudaFree(s->d_counters);
+	cudaFree(s->d_q);
+	cudaFree(s->d_out_ids);
+	cudaFree(s->d_out_dist);
+	cudaFree(s->d_out_count);
+	cudaFree(s->d_qstats);
+	cudaFree(s->d_cand);
+	if (s->h_stage) {
+		cudaFreeHost(s->h_stage);
+	}
+	for (auto &e : s->ev) {
+		if (e) {
+			cudaEventDestroy(e);
+		}
+	}
+	if (s->stream) {
+		cudaStreamDestroy(s->stream);
+	}
+	if (s->copy_stream) {
+		cudaStreamDestroy(s->copy_stream);
+	}
+	delete s;
+	return LMD_OK;
+}
+
+uint64_t lmd_store_node_count(const lmd_store *s) {
+	return s ? s->n : 0;
+}
+
+uint64_t lmd_store_device_bytes(const lmd_store *s) {
+	return s ? s->device_bytes : 0;
+}
+
+
+// Copies `bytes` from src (host or device) to device dst on the store's stream. Pageable host memory goes
+// through the store's pinned staging buffer in 32 MiB pieces, double-buffered against the copy engine.
+static lmd_status copy_to_device(lmd_store *s, void *dst, const void *src, size_t bytes) {
+	if (bytes == 0) {
+		return LMD_OK;
+	}
+	if (is_device_ptr(src)) {
+		LMD_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s->stream));
+		return LMD_OK;
+	}
+	cudaPointerAttributes at;
+	bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+	cudaGetLastError();
+	if (pinned) {
+		LMD_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s->stream));
+		return LMD_OK;
+	}
+	const size_t piece = 32u << 20;
+	if (s->h_stage_bytes < 2 * piece) {
+		if (s->h_stage) {
+			cudaFreeHost(s->h_stage);
+			s->h_stage = nullptr;
+		}
+		LMD_CUDA_OK(cudaMallocHost(&s->h_stage, 2 * piece));
+		s->h_stage_bytes = 2 * piece;
+	}
+	size_t done = 0;
+	int buf = 0;
+	while (done < bytes) {
+		size_t now = bytes - done < piece ? bytes - done : piece;
+		uint8_t *stage = (uint8_t *)s->h_stage + (size_t)buf * piece;
+		// the copy issued two pieces ago from this half must have drained
+		LMD_CUDA_OK(cudaEventSynchronize(s->ev[6 + buf]));
+		memcpy(stage, (const uint8_t *)src + done, now);
+		LMD_CUDA_OK(cudaMemcpyAsync((uint8_t *)dst + done, stage, now, cudaMemcpyHostToDevice, s->stream));
+		LMD_CUDA_OK(cudaEventRecord(s->ev[6 + buf], s->stream));
+		done += now;
+		buf ^= 1;
+	}
+	return LMD_OK;
+}
+
+lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n) {
+	if (!s || (!blocks && n)) {
+		set_error("lmd_store_upload: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (n == 0) {
+		return LMD_OK;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	if (s->n + n > s->capacity) {
+		set_error("lmd_store_upload: %llu + %llu nodes exceed the store capacity %llu", (unsigned long long)s->n,
+		          (unsigned long long)n, (unsigned long long)s->capacity);
+		return LMD_ERR_INVALID_ARG;
+	}
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	const uint64_t bb = s->cfg.block_bytes;
+	const uint64_t base = s->n;
+	lmd_status st = copy_to_device(s, s->d_blocks + base * bb, blocks, n * bb);
+	if (st != LMD_OK) {
+		return st;
+	}
+	const int64_t *d_rid = nullptr;
+	if (row_ids) {
+		// stage the row ids in the slot->row table itself, then let the kernel read them from there
+		st = copy_to_device(s, s->d_row_ids + base, row_ids, n * sizeof(int64_t));
+		if (st != LMD_OK) {
+			return st;
+		}
+		d_rid = s->d_row_ids + base;
+		if (s->identity) {
+			int *d_flag = reinterpret_cast<int *>(s->d_counters + 6);
+			LMD_CUDA_OK(cudaMemsetAsync(d_flag, 0, sizeof(int), s->stream));
+			check_identity_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(d_rid, base, n, d_flag);
+			int h_flag = 0;
+			LMD_CUDA_OK(cudaMemcpyAsync(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+			LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+			if (h_flag) {
+				s->identity = false;
+			}
+		}
+	}
+	ingest_rowids_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(
+	    d_rid, base, n, s->d_row_ids, (long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1);
+	LMD_CUDA_OK(cudaGetLastError());
+	unpack_vectors_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, s->stream>>>(
+	    s->d_blocks, bb, s->lay.vector_off, s->cfg.dims, s->cfg.vec_type, s->row_floats, base, n, s->d_vecs);
+	LMD_CUDA_OK(cudaGetLastError());
+	LMD_CUDA_OK(cudaStreamSynchronize(s->stream)); // caller may free / reuse its buffers on return
+	s->n += n;
+	s->dirty = true;
+	if (s->entry_row != INT64_MAX && !s->has_entry) {
+		// an entry row id set before its block arrived resolves now
+		uint32_t slot;
+		st = lookup_slot(s, s->entry_row, &slot);
+		if (st != LMD_OK) {
+			return st;
+		}
+		s->entry_slot = slot;
+		s->has_entry = slot != LMD_INVALID_SLOT;
+	}
+	return LMD_OK;
+}
+
+lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block) {
+	if (!s || !block) {
+		set_error("lmd_store_update: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	uint32_t slot;
+	lmd_status st = lookup_slot(s, row_id, &slot);
+	if (st != LMD_OK) {
+		return st;
+	}
+	if (slot == LMD_INVALID_SLOT) {
+		set_error("lmd_store_update: row id %lld is not in the store", (long long)row_id);
+		return LMD_ERR_INVALID_ARG;
+	}
+	const uint64_t bb = s->cfg.block_bytes;
+	st = copy_to_device(s, s->d_blocks + (uint64_t)slot * bb, block, bb);
+	if (st != LMD_OK) {
+		return st;
+	}
+	unpack_vectors_kernel<<<1, 32, 0, s->stream>>>(s->d_blocks, bb, s->lay.vector_off, s->cfg.dims, s->cfg.vec_type,
+	                                               s->row_floats, slot, 1, s->d_vecs);
+	LMD_CUDA_OK(cudaGetLastError());
+	// only this node's neighbour row changes; the other rows keep pointing at valid slots
+	build_sidecar_kernel<<<(s->cfg.r + 127) / 128, 128, 0, s->stream>>>(
+	    s->d_blocks + (uint64_t)slot * bb, bb, s->lay.count_off, s->lay.ids_off, s->cfg.r, 1, 0,
+	    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->d_nbrs + (uint64_t)slot * s->cfg.r);
+	LMD_CUDA_OK(cudaGetLastError());
+	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+	return LMD_OK;
+}
+
+lmd_status lmd_store_set_entry(lmd_store *s, int64_t row_id) {
+	if (!s) {
+		set_error("lmd_store_set_entry: null store");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	s->entry_row = row_id;
+	s->has_entry = false;
+	s->entry_slot = LMD_INVALID_SLOT;
+	if (row_id == INT64_MAX) {
+		return LMD_OK; // "no entry point" (core/Searcher.cpp:74)
+	}
+	uint32_t slot;
+	lmd_status st = lookup_slot(s, row_id, &slot);
+	if (st != LMD_OK) {
+		return st;
+	}
+	s->entry_slot = slot;
+	s->has_entry = slot != LMD_INVALID_SLOT;
+	return LMD_OK;
+}
+
+lmd_status lmd_store_finalize(lmd_store *s) {
+	if (!s) {
+		set_error("lmd_store_finalize: null store");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	if (!s->dirty || s->n == 0) {
+		s->dirty = false;
+		return LMD_OK;
+	}
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	uint64_t total = s->n * (uint64_t)s->cfg.r;
+	build_sidecar_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s->stream>>>(
+	    s->d_blocks, s->cfg.block_bytes, s->lay.count_off, s->lay.ids_off, s->cfg.r, s->n, s->identity ? 1 : 0,
+	    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->d_nbrs);
+	LMD_CUDA_OK(cudaGetLastError());
+	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+	s->dirty = false;
+	return LMD_OK;
+}
+
+lmd_status lmd_store_download_block(lmd_store *s, int64_t row_id, void *out_block) {
+	if (!s || !out_block) {
+		set_error("lmd_store_download_block: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	uint32_t slot;
+	lmd_status st = lookup_slot(s, row_id, &slot);
+	if (st != LMD_OK) {
+		return st;
+	}
+	if (slot == LMD_INVALID_SLOT) {
+		set_error("lmd_store_download_block: row id %lld is not in the store", (long long)row_id);
+		return LMD_ERR_INVALID_ARG;
+	}
+	LMD_CUDA_OK(cudaMemcpyAsync(out_block, s->d_blocks + (uint64_t)slot * s->cfg.block_bytes, s->cfg.block_bytes,
+	                            cudaMemcpyDefault, s->stream));
+	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+	return LMD_OK;
+}
+
+lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
+	if (!s || !key) {
+		set_error("lmd_set_tuning: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::string k(key);
+	if (k == "filter_log2") {
+		s->tune.filter_log2 = (int)value;
+	} else if (k == "warps_per_cta") {
+		s->tune.warps_per_cta = (int)value;
+	} else if (k == "ctas_per_sm") {
+		s->tune.ctas_per_sm = (int)value;
+	} else {
+		set_error("lmd_set_tuning: unknown key %s", key);
+		return LMD_ERR_INVALID_ARG;
+	}
+	return LMD_OK;
+}
+
+} // extern "C"

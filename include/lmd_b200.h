@@ -1,0 +1,142 @@
+/* lmd_b200.h - C ABI of the B200-native LM_DISKANN query path.
+ *
+ * This is the whole drop-in boundary: plain C types, caller-owned host buffers, library-owned device
+ * memory, integer status codes + lmd_last_error(); no exception crosses it and no torch / DuckDB type
+ * appears in it. The reference has no FFI of its own (it is one C++ process); each
+ * entry point below names the reference interface it replaces (paths relative to
+ * /root/reference/src/lm_diskann/). INTEGRATION.md shows the reference-side adapter
+ * (GpuSearcher : core::ISearcher, DeviceNodeStore fed from core::IStorageManager) that binds them.
+ *
+ * There is NO CPU fallback: every entry point that computes needs a CUDA device (sm_100a build) and
+ * returns LMD_ERR_CUDA otherwise.
+ */
+#ifndef LMD_B200_H
+#define LMD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LMD_ABI_VERSION 1
+
+typedef int32_t lmd_status;
+enum {
+	LMD_OK = 0,
+	LMD_ERR_INVALID_ARG = 1, /* reference: InvalidInputException / BinderException */
+	LMD_ERR_CUDA = 2,        /* reference: IOException (Scan rewraps, db/LmDiskannIndex.cpp:718-721) */
+	LMD_ERR_OOM = 3,
+	LMD_ERR_STATE = 4,       /* reference: std::runtime_error "index not loaded" (core/Coordinator.cpp:66-74) */
+	LMD_ERR_UNSUPPORTED = 5  /* reference: NotImplementedException / the L2 ternary throw (core/distance.hpp:236-239) */
+};
+
+/* common/ann.hpp:16-32 - same numeric values as the reference enums */
+enum { LMD_METRIC_L2 = 1, LMD_METRIC_COSINE = 2, LMD_METRIC_IP = 3 };
+enum { LMD_VEC_FLOAT32 = 1, LMD_VEC_INT8 = 2 };
+
+/* Routing distance used while traversing.
+ * EXACT   = what core/Searcher.cpp:145-173 executes today: exact fp32 distance to each neighbour's own vector.
+ * TERNARY = the designed LM-DiskANN mode (Searcher.cpp:168-171 TODO): ternary planes of the neighbours held in
+ *           the EXPANDED block (core/distance.hpp:212-243), exact rerank afterwards. COSINE / IP only. */
+enum { LMD_ROUTE_EXACT = 0, LMD_ROUTE_TERNARY = 1 };
+
+/* lmd_search_batch flags */
+enum {
+	LMD_SEARCH_SEPARATE_RERANK = 1u << 0, /* run the rerank kernel even when traversal distances are already exact */
+	LMD_SEARCH_PER_QUERY_STATS = 1u << 1  /* fill out_qstats */
+};
+
+#define LMD_EMPTY_ROW_ID INT64_MAX /* empty neighbour slot, core/GraphManager.cpp:154-156,451-453 */
+
+/* core/index_config.hpp:78-87 (NodeLayoutOffsets) */
+typedef struct {
+	uint64_t count_off;          /* uint16 neighbour count */
+	uint64_t vector_off;         /* node vector, dims * sizeof(T) */
+	uint64_t ids_off;            /* int64 row ids [r] */
+	uint64_t pos_off;            /* positive planes [r][words] u64 */
+	uint64_t neg_off;            /* negative planes [r][words] u64 */
+	uint64_t total_node_size;    /* live bytes, before sector alignment */
+	uint64_t ternary_edge_bytes; /* 2 * words * 8 */
+} lmd_layout;
+
+/* Subset of core/index_config.hpp:49-69 (LmDiskannConfig) that the query path reads. */
+typedef struct {
+	uint32_t dims;        /* config.dimensions */
+	uint32_t r;           /* config.r */
+	uint32_t metric;      /* LMD_METRIC_* */
+	uint32_t vec_type;    /* LMD_VEC_* (config.node_vector_type) */
+	uint32_t l_search;    /* config.l_search, used when a search passes L = 0 */
+	uint32_t reserved;    /* must be 0 */
+	uint64_t block_bytes; /* 0 = AlignValue<4096>(total_node_size) as db/LmDiskannIndex.cpp:161-162 */
+} lmd_config;
+
+typedef struct {
+	uint64_t queries;
+	uint64_t expansions;      /* E: node blocks expanded (GetNeighbors calls) */
+	uint64_t distance_evals;  /* V: routing distances evaluated, entry included */
+	uint64_t reranked;        /* C: exact distances computed by the rerank kernel */
+	uint64_t filter_evictions;/* visited-filter entries overwritten (costs recomputation, never changes results) */
+	uint64_t algorithmic_bytes; /* SURVEY.md section 8d formula for this call */
+	float traverse_ms;        /* CUDA-event time of the traversal kernel */
+	float rerank_ms;          /* CUDA-event time of the rerank kernel (0 when fused away) */
+	float h2d_ms, d2h_ms;     /* copies done by the call (0 for device-resident buffers) */
+	uint32_t launches;        /* kernels launched by the call */
+	uint32_t l_used;          /* L after Searcher.cpp:261-265 resolution */
+} lmd_stats;
+
+typedef struct lmd_store lmd_store;
+
+/* --- layout (core/index_config.cpp:104-148 CalculateLayoutInternal; host code, no device needed) --- */
+lmd_status lmd_layout_calc(uint64_t dims, uint32_t vec_type, uint32_t r, lmd_layout *out);
+uint64_t lmd_block_bytes(uint64_t total_node_size);
+
+/* --- device node store: replaces core/IStorageManager.hpp:156 GetNodeBlockData + the row_id -> IndexPointer
+ *     map of core/GraphManager.hpp:122 / GraphManager.cpp:523-531 on the query path --- */
+lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity_nodes, lmd_store **out);
+lmd_status lmd_store_destroy(lmd_store *s);
+/* Appends n node blocks (reference layout, block_bytes apart). row_ids == NULL: row id = slot number.
+ * `blocks` / `row_ids` may be pageable or pinned host memory, or device memory on the store's device. */
+lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n);
+/* Re-uploads one block that the host marked dirty (core/IStorageManager.hpp MarkBlockDirty). */
+lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block);
+/* core/GraphManager.cpp:468-474 GetEntryPointRowId/Pointer. Unknown row id => searches return empty
+ * results (Searcher.cpp:74-77). */
+lmd_status lmd_store_set_entry(lmd_store *s, int64_t row_id);
+/* Builds the derived search views (packed vectors, uint32 neighbour-slot sidecar). Called implicitly by the
+ * first search after an upload/update. */
+lmd_status lmd_store_finalize(lmd_store *s);
+/* Reads one mirrored block back (verification / tests). */
+lmd_status lmd_store_download_block(lmd_store *s, int64_t row_id, void *out_block);
+uint64_t lmd_store_node_count(const lmd_store *s);
+uint64_t lmd_store_device_bytes(const lmd_store *s); /* core/ISearcher.hpp:43 GetInMemorySize */
+
+/* --- search: replaces core/ISearcher.hpp:30-34 Search -> core/Searcher.cpp:256-272 -> PerformSearch :45-246,
+ *     batched (ISearcher.hpp:36-37 anticipates it) ---
+ * queries  [nq][dims] fp32, host or device.
+ * k, L     as Searcher::Search: L == 0 -> cfg.l_search, then (k > 20 ? k + 20 : 40) if still 0, then max(L, k).
+ * out_ids  [nq][k] row ids ascending by (distance, id), padded with -1; out_dist [nq][k] exact distances (may be
+ *          NULL); out_count [nq] (may be NULL). Host or device (all outputs on the same side as `queries`).
+ * out_qstats [nq][2] = {expansions, distance evals} when LMD_SEARCH_PER_QUERY_STATS (may be NULL).
+ * Thread-safety: concurrent searches on one store are serialised internally; uploads must not overlap searches. */
+lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
+                            uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                            uint32_t *out_qstats, lmd_stats *stats);
+
+/* --- dataset sharding: k-way merge of G gathered per-shard results.
+ * ids [G][nq][k], dist [G][nq][k] (device or host, as produced by lmd_search_batch on each shard and
+ * all-gathered by the caller) -> out [nq][k] smallest by (distance, id); -1 ids are padding. */
+lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq, uint32_t k,
+                          int64_t *out_ids, float *out_dist);
+
+/* --- misc --- */
+const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
+uint32_t lmd_abi_version(void);
+/* Tuning knobs for experiments (not needed for correct use): "filter_log2", "warps_per_cta", "ctas_per_sm". */
+lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LMD_B200_H */
