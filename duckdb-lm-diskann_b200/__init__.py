@@ -21,6 +21,7 @@ VEC_FLOAT32, VEC_INT8 = 1, 2
 ROUTE_EXACT, ROUTE_TERNARY = 0, 1
 SEARCH_SEPARATE_RERANK = 1
 SEARCH_PER_QUERY_STATS = 2
+SEARCH_ASYNC = 4
 EMPTY_ROW_ID = np.iinfo(np.int64).max  # core/GraphManager.cpp:154-156
 OK, ERR_INVALID_ARG, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_UNSUPPORTED = range(6)
 METRIC_BY_NAME = {"L2": METRIC_L2, "COSINE": METRIC_COSINE, "IP": METRIC_IP}
@@ -46,7 +47,7 @@ class Stats(C.Structure):
     _fields_ = [("queries", C.c_uint64), ("expansions", C.c_uint64), ("distance_evals", C.c_uint64),
                 ("reranked", C.c_uint64), ("filter_evictions", C.c_uint64), ("algorithmic_bytes", C.c_uint64),
                 ("traverse_ms", C.c_float), ("rerank_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
-                ("launches", C.c_uint32), ("l_used", C.c_uint32)]
+                ("total_ms", C.c_float), ("launches", C.c_uint32), ("l_used", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -64,6 +65,7 @@ SYMBOLS = [
     ("lmd_store_set_entry", C.c_int32, [_P, C.c_int64]),
     ("lmd_store_finalize", C.c_int32, [_P]),
     ("lmd_store_download_block", C.c_int32, [_P, C.c_int64, _P]),
+    ("lmd_store_set_stream", C.c_int32, [_P, _P]),
     ("lmd_store_node_count", C.c_uint64, [_P]),
     ("lmd_store_device_bytes", C.c_uint64, [_P]),
     ("lmd_search_batch", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P,
@@ -176,6 +178,10 @@ class Store:
         _check(lib().lmd_store_download_block(self._h, int(row_id), _ptr(out)))
         return out
 
+    def set_stream(self, cuda_stream):
+        """cuda_stream: a raw cudaStream_t address (e.g. torch.cuda.current_stream().cuda_stream) or None."""
+        _check(lib().lmd_store_set_stream(self._h, cuda_stream or None))
+
     def set_tuning(self, key, value):
         _check(lib().lmd_set_tuning(self._h, key.encode(), int(value)))
 
@@ -190,6 +196,10 @@ class Store:
     def search_raw(self, queries, nq, k, L=0, route=ROUTE_EXACT, flags=0, out_ids=None, out_dist=None, out_count=None,
                    out_qstats=None):
         """Thin call: any mix of numpy arrays / torch tensors / raw addresses, all on the same side."""
+        if flags & SEARCH_ASYNC:
+            _check(lib().lmd_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids),
+                                          _ptr(out_dist), _ptr(out_count), _ptr(out_qstats), None))
+            return None
         st = Stats()
         _check(lib().lmd_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist),
                                       _ptr(out_count), _ptr(out_qstats), C.byref(st)))

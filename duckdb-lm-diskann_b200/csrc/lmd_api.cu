@@ -101,8 +101,16 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 	const bool dev_io = on_device(queries);
 	const bool separate = route == LMD_ROUTE_TERNARY || (flags & LMD_SEARCH_SEPARATE_RERANK);
 	const bool want_qstats = (flags & LMD_SEARCH_PER_QUERY_STATS) && out_qstats;
+	const bool async = (flags & LMD_SEARCH_ASYNC) != 0;
 	lmd_status rc;
+	if (async && (!dev_io || stats)) {
+		set_error("LMD_SEARCH_ASYNC needs device-resident buffers and stats == NULL");
+		return LMD_ERR_INVALID_ARG;
+	}
 
+	if (!async) {
+		LMD_CUDA_OK(cudaEventRecord(s->ev[0], st));
+	}
 	const float *d_q = queries;
 	int64_t *d_ids = out_ids;
 	float *d_dist = out_dist;
@@ -127,7 +135,6 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 			}
 			s->scratch_k = need_k;
 		}
-		LMD_CUDA_OK(cudaEventRecord(s->ev[0], st));
 		LMD_CUDA_OK(cudaMemcpyAsync(s->d_q, queries, need_q * sizeof(float), cudaMemcpyHostToDevice, st));
 		d_q = s->d_q;
 		d_ids = s->d_out_ids;
@@ -160,11 +167,15 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 	ta.d_out_count = separate ? nullptr : d_count;
 	ta.d_qstats = d_qstats;
 	ta.d_cand = d_cand;
-	LMD_CUDA_OK(cudaEventRecord(s->ev[1], st));
+	if (!async) {
+		LMD_CUDA_OK(cudaEventRecord(s->ev[1], st));
+	}
 	if ((rc = launch_traverse(ta, st)) != LMD_OK) {
 		return rc;
 	}
-	LMD_CUDA_OK(cudaEventRecord(s->ev[2], st));
+	if (!async) {
+		LMD_CUDA_OK(cudaEventRecord(s->ev[2], st));
+	}
 	uint32_t launches = 1;
 	if (separate) {
 		RerankArgs ra;
@@ -181,6 +192,9 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 			return rc;
 		}
 		launches++;
+	}
+	if (async) {
+		return LMD_OK;
 	}
 	LMD_CUDA_OK(cudaEventRecord(s->ev[3], st));
 	if (!dev_io) {
@@ -217,6 +231,7 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 		if (separate) {
 			cudaEventElapsedTime(&stats->rerank_ms, s->ev[2], s->ev[3]);
 		}
+		cudaEventElapsedTime(&stats->total_ms, s->ev[0], s->ev[4]);
 		if (!dev_io) {
 			cudaEventElapsedTime(&stats->h2d_ms, s->ev[0], s->ev[1]);
 			cudaEventElapsedTime(&stats->d2h_ms, s->ev[3], s->ev[4]);

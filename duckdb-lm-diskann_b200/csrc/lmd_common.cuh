@@ -115,7 +115,7 @@ struct lmd_store {
 	uint32_t entry_slot = LMD_INVALID_SLOT;
 	bool dirty = true; // views need (re)building
 
-	cudaStream_t stream = nullptr, copy_stream = nullptr;
+	cudaStream_t stream = nullptr, own_stream = nullptr, copy_stream = nullptr; // stream = the active one
 	cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 	lmd::Tuning tune;
 	std::mutex mu;

@@ -306,11 +306,12 @@ lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity
 	LMD_ALLOC(s->d_map_vals, s->map_cap * sizeof(uint32_t));
 	LMD_ALLOC(s->d_counters, 8 * sizeof(unsigned long long));
 #undef LMD_ALLOC
-	if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess ||
+	if (cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
 	    cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
 		set_error("cudaStreamCreate failed");
 		return fail(LMD_ERR_CUDA);
 	}
+	s->stream = s->own_stream;
 	for (auto &e : s->ev) {
 		if (cudaEventCreate(&e) != cudaSuccess) {
 			set_error("cudaEventCreate failed");
@@ -358,13 +359,25 @@ lmd_status lmd_store_destroy(lmd_store *s) {
 			cudaEventDestroy(e);
 		}
 	}
-	if (s->stream) {
-		cudaStreamDestroy(s->stream);
+	if (s->own_stream) {
+		cudaStreamDestroy(s->own_stream);
 	}
 	if (s->copy_stream) {
 		cudaStreamDestroy(s->copy_stream);
 	}
 	delete s;
+	return LMD_OK;
+}
+
+lmd_status lmd_store_set_stream(lmd_store *s, void *cuda_stream) {
+	if (!s) {
+		set_error("lmd_store_set_stream: null store");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	LMD_CUDA_OK(cudaStreamSynchronize(s->stream)); // nothing of ours may still be running on the old stream
+	s->stream = cuda_stream ? (cudaStream_t)cuda_stream : s->own_stream;
 	return LMD_OK;
 }
 

@@ -45,7 +45,9 @@ enum { LMD_ROUTE_EXACT = 0, LMD_ROUTE_TERNARY = 1 };
 /* lmd_search_batch flags */
 enum {
 	LMD_SEARCH_SEPARATE_RERANK = 1u << 0, /* run the rerank kernel even when traversal distances are already exact */
-	LMD_SEARCH_PER_QUERY_STATS = 1u << 1  /* fill out_qstats */
+	LMD_SEARCH_PER_QUERY_STATS = 1u << 1, /* fill out_qstats */
+	LMD_SEARCH_ASYNC = 1u << 2            /* device-resident buffers only: enqueue on the store's stream and return
+	                                         without synchronising; `stats` must be NULL */
 };
 
 #define LMD_EMPTY_ROW_ID INT64_MAX /* empty neighbour slot, core/GraphManager.cpp:154-156,451-453 */
@@ -82,6 +84,7 @@ typedef struct {
 	float traverse_ms;        /* CUDA-event time of the traversal kernel */
 	float rerank_ms;          /* CUDA-event time of the rerank kernel (0 when fused away) */
 	float h2d_ms, d2h_ms;     /* copies done by the call (0 for device-resident buffers) */
+	float total_ms;           /* CUDA-event time of everything the call enqueued */
 	uint32_t launches;        /* kernels launched by the call */
 	uint32_t l_used;          /* L after Searcher.cpp:261-265 resolution */
 } lmd_stats;
@@ -109,6 +112,9 @@ lmd_status lmd_store_set_entry(lmd_store *s, int64_t row_id);
 lmd_status lmd_store_finalize(lmd_store *s);
 /* Reads one mirrored block back (verification / tests). */
 lmd_status lmd_store_download_block(lmd_store *s, int64_t row_id, void *out_block);
+/* Runs all later work of this store on the caller's CUDA stream (a cudaStream_t passed as void*; NULL = back to
+ * the store's own stream). Lets a host with its own streams / events order and time the searches. */
+lmd_status lmd_store_set_stream(lmd_store *s, void *cuda_stream);
 uint64_t lmd_store_node_count(const lmd_store *s);
 uint64_t lmd_store_device_bytes(const lmd_store *s); /* core/ISearcher.hpp:43 GetInMemorySize */
 

@@ -1,0 +1,264 @@
+"""-m gpu: the CUDA path (through the C ABI, include/lmd_b200.h) against the CPU oracle on the same graph and
+queries. Oracle = oracle/liblmd_oracle.so (C restatement, pinned against the reference's own sources by
+tests/test_oracle.py and tests/golden/)."""
+import numpy as np
+import pytest
+
+from parity import check_parity, rel_close
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    # n, dims, r, metric, kind, k, L
+    (3000, 128, 32, "L2", "clustered", 10, 64),
+    (3000, 128, 32, "L2", "iid", 10, 32),
+    (2000, 96, 32, "L2", "clustered", 10, 100),
+    (2000, 128, 64, "L2", "clustered", 10, 128),
+    (1500, 768, 32, "COSINE", "clustered", 10, 64),
+    (2000, 128, 32, "IP", "iid", 10, 64),
+    (2000, 128, 32, "COSINE", "iid", 5, 256),
+    (1500, 100, 24, "L2", "iid", 7, 48),      # generic (non-specialised) shape, odd R
+    (1200, 33, 16, "COSINE", "clustered", 10, 40),
+    (2000, 128, 32, "L2", "clustered", 100, 0),  # L = 0 -> cfg.l_search (100), k = L
+    (2000, 128, 32, "L2", "clustered", 1, 10),
+    (2500, 128, 32, "L2", "clustered", 10, 512),
+]
+METRIC = {"L2": 1, "COSINE": 2, "IP": 3}
+
+
+def _store(lmd, ix, dims, r, metric, **kw):
+    s = lmd.Store(dims, r, metric=METRIC[metric], capacity=ix["blocks_np"].shape[0], l_search=100, **kw)
+    return s
+
+
+@pytest.mark.parametrize("n,dims,r,metric,kind,k,L", CASES)
+def test_exact_routing_parity(lmd, oracle, make_index, n, dims, r, metric, kind, k, L):
+    ix = make_index(n, dims, r, metric=metric, kind=kind, nq=96)
+    with _store(lmd, ix, dims, r, metric) as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        ids, dist, cnt, st, qs = s.search(ix["queries"], k, L, qstats=True)
+    o_ids, o_dist, o_cnt, o_st = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, ix["queries"], k, L,
+                                                metric=METRIC[metric], entry_row_id=0, cfg_l_search=100)
+    ties, total = check_parity(ids, dist, cnt, o_ids, o_dist, o_cnt, what="%s n=%d D=%d" % (metric, n, dims))
+    assert ties <= max(2, total // 200)
+    # expansions equal the oracle's per query (same traversal), up to rounding-induced divergence on a few queries
+    same = (qs[:, 0].astype(np.int64) == o_st[:, 0].astype(np.int64)).mean()
+    assert same >= 0.9, "expansion counts agree on only %.2f of the queries" % same
+    assert st.launches >= 1 and st.expansions == int(qs[:, 0].sum())
+
+
+@pytest.mark.parametrize("metric", ["COSINE", "IP"])
+@pytest.mark.parametrize("dims,r", [(128, 32), (768, 32), (96, 64), (100, 24)])
+def test_ternary_routing_parity(lmd, oracle, make_index, metric, dims, r):
+    n, k, L = 1500, 10, 64
+    ix = make_index(n, dims, r, metric=metric, kind="iid", nq=64)
+    with _store(lmd, ix, dims, r, metric) as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        ids, dist, cnt, st = s.search(ix["queries"], k, L, route=lmd.ROUTE_TERNARY)
+    o_ids, o_dist, o_cnt, _ = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, ix["queries"], k, L,
+                                            metric=METRIC[metric], entry_row_id=0, route=1)
+    # routing distances are integers (popcounts): the traversal is bit-exact, only the rerank is floating point
+    check_parity(ids, dist, cnt, o_ids, o_dist, o_cnt, what="ternary %s D=%d" % (metric, dims))
+    assert st.reranked > 0 and st.launches == 2
+
+
+def test_ternary_l2_is_rejected(lmd, make_index):
+    ix = make_index(1200, 33, 16, metric="L2", kind="iid", nq=8)
+    with _store(lmd, ix, 33, 16, "L2") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        with pytest.raises(lmd.LmdError) as e:  # core/distance.hpp:236-239
+            s.search(ix["queries"], 5, 32, route=lmd.ROUTE_TERNARY)
+        assert e.value.status == lmd.ERR_UNSUPPORTED
+
+
+def test_separate_rerank_matches_fused(lmd, make_index):
+    ix = make_index(3000, 128, 32, metric="L2", kind="clustered", nq=96)
+    with _store(lmd, ix, 128, 32, "L2") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        a = s.search(ix["queries"], 10, 64)
+        b = s.search(ix["queries"], 10, 64, flags=lmd.SEARCH_SEPARATE_RERANK)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+    assert np.array_equal(a[1], b[1])  # same arithmetic in both kernels
+    assert b[3].launches == 2 and b[3].reranked > 0
+
+
+def test_row_id_mapping(lmd, oracle, fixtures_mod):
+    """Row ids that are not slot numbers (DuckDB row_t after deletes): GraphManager.cpp:523-531 semantics."""
+    n, dims, r = 2000, 128, 32
+    rng = np.random.default_rng(5)
+    row_ids = np.sort(rng.choice(np.arange(10, 10 * n, dtype=np.int64), size=n, replace=False))
+    rng.shuffle(row_ids)
+    ix = fixtures_mod.build_index(n, dims, r, device="cpu", row_ids=row_ids)
+    blocks = ix["blocks"].numpy()
+    q = fixtures_mod.make_dataset(64, dims, seed=43)
+    entry = int(row_ids[17])
+    with lmd.Store(dims, r, capacity=n) as s:
+        s.upload(blocks[:1200], row_ids=row_ids[:1200])   # two uploads: the sidecar resolves ids across both
+        s.upload(blocks[1200:], row_ids=row_ids[1200:])
+        s.set_entry(entry)
+        ids, dist, cnt, _ = s.search(q, 10, 64)
+        got = s.download_block(int(row_ids[1500]))
+    assert np.array_equal(got, blocks[1500])
+    o = oracle.search(blocks, ix["layout"]["block_bytes"], dims, r, q, 10, 64, row_ids=row_ids, entry_row_id=entry)
+    check_parity(ids, dist, cnt, o[0], o[1], o[2], what="row-id map")
+    assert set(np.unique(ids[ids >= 0])).issubset(set(row_ids.tolist()))
+
+
+def test_skip_rules_and_edge_cases(lmd, oracle, fixtures_mod):
+    """count < stored ids, INT64_MAX sentinels inside the count, dangling row ids, isolated entry, missing entry,
+    k > reachable nodes (core/GraphManager.cpp:241-254, core/Searcher.cpp:74-83,120-122,132,146-148)."""
+    n, dims, r = 600, 64, 16
+    ix = fixtures_mod.build_index(n, dims, r, device="cpu", kind="iid")
+    blocks = ix["blocks"].numpy().copy()
+    lay = ix["layout"]
+    ids_view = blocks[:, lay["ids_off"]:lay["ids_off"] + 8 * r].view(np.int64)
+    cnt_view = blocks[:, 0:2].view(np.uint16)
+    rng = np.random.default_rng(3)
+    for node in rng.choice(n, 150, replace=False):
+        c = int(cnt_view[node, 0])
+        what = rng.integers(0, 3)
+        if what == 0 and c > 2:
+            cnt_view[node, 0] = c - 2            # ids beyond count must be ignored
+        elif what == 1 and c > 1:
+            ids_view[node, rng.integers(0, c)] = np.iinfo(np.int64).max  # sentinel inside the count
+        elif c > 0:
+            ids_view[node, rng.integers(0, c)] = 10 ** 9 + int(node)      # dangling row id
+    q = fixtures_mod.make_dataset(48, dims, kind="iid", seed=45)
+    with lmd.Store(dims, r, capacity=n) as s:
+        s.upload(blocks)
+        s.set_entry(0)
+        g = s.search(q, 10, 32)
+        o = oracle.search(blocks, lay["block_bytes"], dims, r, q, 10, 32, entry_row_id=0)
+        check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="skip rules")
+        # missing entry point -> empty results, no error (Searcher.cpp:74-77)
+        s.set_entry(123456789)
+        g = s.search(q, 10, 32)
+        assert (g[0] == -1).all() and (g[2] == 0).all()
+        s.set_entry(np.iinfo(np.int64).max)
+        g = s.search(q, 10, 32)
+        assert (g[0] == -1).all() and (g[2] == 0).all()
+        # isolated entry: only the entry itself is returned
+        iso = blocks[5].copy()
+        iso[0:2] = 0
+        s.update(5, iso)
+        s.set_entry(5)
+        g = s.search(q, 10, 32)
+        assert (g[2] == 1).all() and (g[0][:, 0] == 5).all() and (g[0][:, 1:] == -1).all()
+        b2 = blocks.copy()
+        b2[5] = iso
+        o = oracle.search(b2, lay["block_bytes"], dims, r, q, 10, 32, entry_row_id=5)
+        check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="isolated entry")
+        # k = 0 is an error (Coordinator.cpp:72-74); empty batch is not
+        with pytest.raises(lmd.LmdError):
+            s.search(q, 0, 32)
+        g = s.search(q[:0], 10, 32)
+        assert g[0].shape == (0, 10)
+    # a tiny graph: k and L exceed the number of nodes
+    tiny = fixtures_mod.build_index(8, dims, 4, device="cpu", kind="iid", n_random=1, n_cand=4)
+    tb = tiny["blocks"].numpy()
+    with lmd.Store(dims, 4, capacity=8) as s:
+        s.upload(tb)
+        s.set_entry(0)
+        g = s.search(q, 20, 64)
+    o = oracle.search(tb, tiny["layout"]["block_bytes"], dims, 4, q, 20, 64, entry_row_id=0)
+    check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="tiny graph")
+
+
+def test_int8_nodes(lmd, oracle, fixtures_mod):
+    """node_vector_type INT8: plain static_cast<float> per element (common/ann.hpp:52-58)."""
+    n, dims, r = 1500, 128, 32
+    x = fixtures_mod.make_dataset(n, dims, kind="iid", seed=44)
+    xi = np.clip(np.round(x * 40), -127, 127).astype(np.int8)
+    nbrs, counts = fixtures_mod.build_graph(xi.astype(np.float32), r, device="cpu")
+    blocks = fixtures_mod.pack_blocks(xi, nbrs, counts, r, vec_type=2).numpy()
+    lay = fixtures_mod.layout(dims, r, 2)
+    q = (fixtures_mod.make_dataset(64, dims, kind="iid", seed=45) * 40).astype(np.float32)
+    with lmd.Store(dims, r, vec_type=lmd.VEC_INT8, capacity=n) as s:
+        assert s.block_bytes == lay["block_bytes"]
+        s.upload(blocks)
+        s.set_entry(0)
+        g = s.search(q, 10, 64)
+    o = oracle.search(blocks, lay["block_bytes"], dims, r, q, 10, 64, vec_type=2, entry_row_id=0)
+    check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="int8")
+
+
+def test_filter_size_does_not_change_results(lmd, make_index):
+    """The visited filter may forget: results must not depend on its size."""
+    ix = make_index(3000, 128, 32, metric="L2", kind="iid", nq=96)
+    outs = []
+    with _store(lmd, ix, 128, 32, "L2") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        for lg in (6, 8, 11, 13):
+            s.set_tuning("filter_log2", lg)
+            outs.append(s.search(ix["queries"], 10, 128))
+    for o in outs[1:]:
+        assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1])
+    assert outs[0][3].filter_evictions > 0  # the 64-entry filter really did forget
+    assert outs[0][3].distance_evals >= outs[-1][3].distance_evals
+
+
+def test_device_resident_io(lmd, make_index):
+    """queries / outputs already in HBM (torch tensors): no staging copies."""
+    import torch
+    ix = make_index(3000, 128, 32, metric="L2", kind="clustered", nq=96)
+    nq, k = 96, 10
+    with _store(lmd, ix, 128, 32, "L2") as s:
+        s.upload(torch.from_numpy(ix["blocks_np"]).cuda())  # device-resident blocks
+        s.set_entry(0)
+        h = s.search(ix["queries"], k, 64)
+        dq = torch.from_numpy(ix["queries"]).cuda()
+        d_ids = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        d_dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+        d_cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
+        st = s.search_raw(dq, nq, k, 64, out_ids=d_ids, out_dist=d_dist, out_count=d_cnt)
+        torch.cuda.synchronize()
+    assert np.array_equal(d_ids.cpu().numpy(), h[0]) and np.array_equal(d_dist.cpu().numpy(), h[1])
+    assert st.h2d_ms == 0 and st.d2h_ms == 0
+
+
+def test_merge_topk(lmd):
+    rng = np.random.default_rng(0)
+    G, nq, k = 8, 257, 10
+    dist = np.sort(rng.random((G, nq, k), dtype=np.float32), axis=2)
+    dist[:, :, 3] = dist[:, :, 2]  # ties inside a shard
+    dist[1] = dist[0]              # ties across shards -> id order decides
+    ids = rng.permutation(G * nq * k).astype(np.int64).reshape(G, nq, k)
+    # make each shard's list ascending by (dist, id)
+    for g in range(G):
+        for q in range(nq):
+            o = np.lexsort((ids[g, q], dist[g, q]))
+            ids[g, q], dist[g, q] = ids[g, q][o], dist[g, q][o]
+    ids[2, :, 7:] = -1  # a shard that found fewer than k
+    out_i = np.empty((nq, k), dtype=np.int64)
+    out_d = np.empty((nq, k), dtype=np.float32)
+    lmd.merge_topk(ids, dist, G, nq, k, out_i, out_d)
+    for q in range(nq):
+        cand = [(float(dist[g, q, j]), int(ids[g, q, j])) for g in range(G) for j in range(k) if ids[g, q, j] >= 0]
+        cand.sort()
+        assert [c[1] for c in cand[:k]] == out_i[q].tolist()
+        assert np.array_equal(np.array([c[0] for c in cand[:k]], dtype=np.float32), out_d[q])
+
+
+def test_recall_matches_oracle_10k(lmd, oracle, fixtures_mod):
+    """BASELINE config 1 shape (10k x 128 L2, R=32, L=64, 1k queries, k=10): recall@10 equal to the oracle's."""
+    import torch
+    n, dims, r, nq, k, L = 10000, 128, 32, 1000, 10, 64
+    ix = fixtures_mod.build_index(n, dims, r, device="cuda")
+    blocks = ix["blocks"].numpy()
+    q = fixtures_mod.make_dataset(nq, dims, seed=43)
+    truth = fixtures_mod.brute_force_topk(ix["x"], q, k, "L2", device="cuda")
+    with lmd.Store(dims, r, capacity=n, l_search=L) as s:
+        s.upload(blocks)
+        s.set_entry(0)
+        g = s.search(q, k)  # L = 0 -> cfg.l_search
+    o = oracle.search(blocks, ix["layout"]["block_bytes"], dims, r, q, k, 0, entry_row_id=0, cfg_l_search=L)
+    check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="10k config")
+    rg, ro = fixtures_mod.recall_at_k(g[0], truth), fixtures_mod.recall_at_k(o[0], truth)
+    assert rg == ro, (rg, ro)
+    assert rg >= 0.9, rg
+    del torch
