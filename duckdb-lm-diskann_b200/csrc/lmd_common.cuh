@@ -73,6 +73,7 @@ struct Tuning {
 	int filter_log2 = 0;   // 0 = heuristic
 	int warps_per_cta = 4;
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
+	int tie_slots = -1;    // -1 = default (64 for ternary routing, 0 for exact)
 };
 
 } // namespace lmd

@@ -33,10 +33,10 @@ struct KParams {
 	uint32_t *out_count;
 	uint32_t *qstats;
 	uint64_t *cand;
-	unsigned long long *counters; // [0] next query, [1] E, [2] V, [3] filter evictions, [4] reranked
+	unsigned long long *counters; // [0] next query, [1] E, [2] V, [3] filter evictions, [4] reranked, [5] tie overflows
 	uint64_t block_bytes, pos_off, neg_off;
 	uint32_t nq, dims, row_floats, r, words;
-	uint32_t L, k, metric;
+	uint32_t L, k, metric, list_cap;
 	uint32_t entry_slot, has_entry;
 	uint32_t filter_mask, filter_shift;
 	uint32_t warp_smem_bytes;
@@ -225,10 +225,17 @@ __device__ __forceinline__ bool filter_test_and_set(uint32_t *tab, uint32_t mask
 	return true;
 }
 
-// Sorted insert of one key (warp-uniform) into s_list[0..n), capacity L. Duplicates of a listed (distance, slot)
-// pair are dropped. Returns the new length.
+// Sorted insert of one key (warp-uniform) into s_list[0..n). The list holds the top-L entries in [0, L) and, behind
+// them, the TIE REGION: entries pushed out of the top L whose distance still EQUALS the L-th distance. The oracle
+// keeps such entries in its frontier heap and expands them, because its cut-off is `distance > worst`
+// (core/Searcher.cpp:112-114 + H2), not `>=`; they sort after every top-L entry, so "first unexpanded entry of the
+// whole array" is exactly the oracle's pop order. The region is bounded by cap (= LPL*32 or L + tie_slots); a tied,
+// unexpanded entry that does not fit is dropped and counted in `overflow` (statistics: results may then differ from
+// the oracle inside that distance tie only). Duplicates of a listed (distance, slot) pair are dropped.
+// Returns the new length.
 template <int LPL>
-__device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, uint64_t key, int lane) {
+__device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, int cap, uint64_t key, int lane,
+                                           uint32_t &overflow) {
 	uint64_t e[LPL];
 	int pos = 0;
 	bool dup = false;
@@ -241,14 +248,16 @@ __device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, uint6
 		pos += __popc(__ballot_sync(FULL, e1 < k1));
 		dup |= __any_sync(FULL, e1 == k1);
 	}
-	if (dup || pos >= L) {
+	if (dup || pos >= cap) {
 		return n;
 	}
 	__syncwarp();
+	// entry that falls off the end of the array (only when n == cap)
+	const uint64_t last = n == cap ? s_list[cap - 1] : LMD_KEY_NONE;
 #pragma unroll
 	for (int c = 0; c < LPL; c++) {
 		int i = c * 32 + lane;
-		if (i < n && i >= pos && i + 1 < L) {
+		if (i < n && i >= pos && i + 1 < cap) {
 			s_list[i + 1] = e[c];
 		}
 	}
@@ -256,7 +265,23 @@ __device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, uint6
 		s_list[pos] = key;
 	}
 	__syncwarp();
-	return n < L ? n + 1 : L;
+	int nn = n < cap ? n + 1 : cap;
+	if (nn > L) {
+		// trim the tie region: keep entries behind the top L only while they tie with the L-th distance
+		const uint32_t wd = (uint32_t)(s_list[L - 1] >> 32);
+		int keep = L;
+#pragma unroll
+		for (int c = 0; c < LPL; c++) {
+			int i = c * 32 + lane;
+			bool tie = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
+			keep += __popc(__ballot_sync(FULL, tie));
+		}
+		if (last != LMD_KEY_NONE && keep == cap && (uint32_t)(last >> 32) == wd && !(last & 1ull)) {
+			overflow++;
+		}
+		nn = keep;
+	}
+	return nn;
 }
 
 template <int LPL>
@@ -325,6 +350,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 	uint32_t *s_qp = reinterpret_cast<uint32_t *>(extra + (CH == 0 ? p.row_floats * 4 : 0));
 	uint32_t *s_qn = s_qp + p.words * 2;
 	const int L = (int)p.L;
+	const int cap = (int)p.list_cap;
 
 	for (;;) {
 		uint32_t qi = 0;
@@ -335,7 +361,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		if (qi >= p.nq) {
 			break;
 		}
-		uint32_t n_exp = 0, n_eval = 0, n_evict = 0;
+		uint32_t n_exp = 0, n_eval = 0, n_evict = 0, n_tie_ovf = 0;
 		int n = 0;
 		{
 			uint4 e4 = make_uint4(FILTER_EMPTY, FILTER_EMPTY, FILTER_EMPTY, FILTER_EMPTY);
@@ -418,25 +444,28 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 					}
 				}
 				// core/Searcher.cpp:175-185, candidates taken in neighbour order with a moving threshold
-				float worst = n == L ? key_dist(s_list[L - 1]) : 0.0f;
+				float worst = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
 				uint32_t amask = __ballot_sync(FULL, have && (n < L || d < worst));
 				while (amask) {
 					const int src = __ffs(amask) - 1;
 					amask &= amask - 1;
 					const float dj = __shfl_sync(FULL, d, src);
 					const uint32_t idj = __shfl_sync(FULL, myid, src);
-					if (n == L && !(dj < worst)) {
+					if (n >= L && !(dj < worst)) {
 						continue;
 					}
-					n = list_insert<LPL>(s_list, n, L, make_key(dj, idj), lane);
-					if (n == L) {
+					n = list_insert<LPL>(s_list, n, L, cap, make_key(dj, idj), lane, n_tie_ovf);
+					if (n >= L) {
 						worst = key_dist(s_list[L - 1]);
 					}
 				}
 			}
 		}
 
-		// results
+		// results: the top-L part only (the oracle's final pass drains `top_candidates`, core/Searcher.cpp:193-196)
+		if (n > L) {
+			n = L;
+		}
 		if (p.cand) {
 			uint64_t *dst = p.cand + (uint64_t)qi * p.L;
 			for (int i = lane; i < L; i += 32) {
@@ -471,6 +500,9 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 			atomicAdd(&p.counters[2], (unsigned long long)n_eval);
 			if (n_evict) {
 				atomicAdd(&p.counters[3], (unsigned long long)n_evict);
+			}
+			if (n_tie_ovf) {
+				atomicAdd(&p.counters[5], (unsigned long long)n_tie_ovf);
 			}
 		}
 		__syncwarp();
@@ -658,7 +690,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 }
 
 static int lpl_for(uint32_t L) {
-	return L <= 64 ? 2 : L <= 128 ? 4 : L <= 256 ? 8 : L <= 512 ? 16 : 0;
+	return L <= 32 ? 1 : L <= 64 ? 2 : L <= 96 ? 3 : L <= 128 ? 4 : L <= 192 ? 6 : L <= 256 ? 8 : L <= 384 ? 12 : L <= 512 ? 16 : 0;
 }
 
 // visited-filter size: room for the nodes a search is expected to discover, shrunk until at least 16 warps
@@ -681,12 +713,20 @@ static uint32_t pick_filter_log2(const lmd_store *s, uint32_t L, size_t fixed_by
 
 #define LMD_DISPATCH_LPL(KERNEL, TEAM, CH, G, METRIC, ...)                                                             \
 	switch (lpl) {                                                                                                     \
+	case 1:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 1, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
 	case 2:                                                                                                            \
 		return launch_persistent(KERNEL<TEAM, CH, G, 2, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 3:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 3, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
 	case 4:                                                                                                            \
 		return launch_persistent(KERNEL<TEAM, CH, G, 4, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 6:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 6, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
 	case 8:                                                                                                            \
 		return launch_persistent(KERNEL<TEAM, CH, G, 8, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 12:                                                                                                           \
+		return launch_persistent(KERNEL<TEAM, CH, G, 12, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);               \
 	case 16:                                                                                                           \
 		return launch_persistent(KERNEL<TEAM, CH, G, 16, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);               \
 	default:                                                                                                           \
@@ -745,11 +785,18 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.out_count = a.d_out_count;
 	p.qstats = a.d_qstats;
 	p.cand = a.d_cand;
-	const int lpl = lpl_for(a.L);
+	// room behind the top L for distance ties (see list_insert): integer ternary distances tie all the time, fp32
+	// distances only for duplicate vectors
+	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots : (a.route == LMD_ROUTE_TERNARY ? 64u : 0u);
+	int lpl = lpl_for(a.L + tie_slots);
+	if (!lpl) {
+		lpl = lpl_for(a.L);
+	}
 	if (!lpl) {
 		set_error("search list size L = %u exceeds this build's limit of 512", a.L);
 		return LMD_ERR_UNSUPPORTED;
 	}
+	p.list_cap = (uint32_t)lpl * 32;
 	const bool generic = !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	size_t fixed = (size_t)lpl * 32 * 8 + 256 + (generic ? (size_t)p.row_floats * 4 : 0) +
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0);

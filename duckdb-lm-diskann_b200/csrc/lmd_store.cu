@@ -606,6 +606,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		s->tune.warps_per_cta = (int)value;
 	} else if (k == "ctas_per_sm") {
 		s->tune.ctas_per_sm = (int)value;
+	} else if (k == "tie_slots") {
+		s->tune.tie_slots = (int)value;
 	} else {
 		set_error("lmd_set_tuning: unknown key %s", key);
 		return LMD_ERR_INVALID_ARG;

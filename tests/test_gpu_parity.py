@@ -62,6 +62,7 @@ def test_ternary_routing_parity(lmd, oracle, make_index, metric, dims, r):
     # routing distances are integers (popcounts): the traversal is bit-exact, only the rerank is floating point
     check_parity(ids, dist, cnt, o_ids, o_dist, o_cnt, what="ternary %s D=%d" % (metric, dims))
     assert st.reranked > 0 and st.launches == 2
+    assert st.tie_overflows == 0  # the tie region held every tied frontier entry: oracle-exact
 
 
 def test_ternary_l2_is_rejected(lmd, make_index):
