@@ -228,7 +228,9 @@ def main():
             gbps = st.algorithmic_bytes / (st.traverse_ms * 1e-3) / 1e9
             sweep.append({"L": l, "recall": round(rec, 4), "traverse_ms": round(st.traverse_ms, 4),
                           "kernel_qps": round(a.nq / (st.traverse_ms * 1e-3)), "algorithmic_GBps": round(gbps, 1),
-                          "E_per_q": round(st.expansions / a.nq, 1), "V_per_q": round(st.distance_evals / a.nq, 1)})
+                          "E_per_q": round(st.expansions / a.nq, 1), "V_per_q": round(st.distance_evals / a.nq, 1),
+                          "filter_evictions_per_q": round(st.filter_evictions / a.nq, 2),
+                          "merge_fallbacks": int(st.merge_fallbacks)})
             log("sweep", sweep[-1])
             if a.L == 0 and L == 0 and rec >= a.recall:
                 L = l

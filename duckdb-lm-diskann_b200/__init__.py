@@ -46,7 +46,7 @@ class Config(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("queries", C.c_uint64), ("expansions", C.c_uint64), ("distance_evals", C.c_uint64),
                 ("reranked", C.c_uint64), ("filter_evictions", C.c_uint64), ("tie_overflows", C.c_uint64),
-                ("algorithmic_bytes", C.c_uint64),
+                ("merge_fallbacks", C.c_uint64), ("algorithmic_bytes", C.c_uint64),
                 ("traverse_ms", C.c_float), ("rerank_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
                 ("total_ms", C.c_float), ("launches", C.c_uint32), ("l_used", C.c_uint32)]
 

@@ -13,7 +13,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "liblmd_b200.so")
 SOURCES = ["lmd_store.cu", "lmd_search_kernels.cu", "lmd_api.cu"]
-HEADERS = [os.path.join(CSRC, "lmd_common.cuh"), os.path.join(HERE, "..", "include", "lmd_b200.h")]
+# lmd_kernel_inst.cu is compiled once per kernel family: (object suffix, extra defines)
+INSTANCES = [("trav_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=0", "-DLMD_INST_METRIC=%d" % m, "-DLMD_INST_ROUTE=%d" % r])
+             for m, r in ((1, 0), (2, 0), (3, 0), (2, 1), (3, 1))] + \
+            [("rerank_m%d" % m, ["-DLMD_INST_KIND=1", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)]
+HEADERS = [os.path.join(CSRC, "lmd_common.cuh"), os.path.join(CSRC, "lmd_kernels.cuh"),
+           os.path.join(HERE, "..", "include", "lmd_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -40,6 +45,13 @@ def build(force=False, verbose=False):
             cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op]
             jobs.append(cmd)
 
+    sp = os.path.join(CSRC, "lmd_kernel_inst.cu")
+    for suffix, defs in INSTANCES:
+        op = os.path.join(objdir, "inst_%s.o" % suffix)
+        objs.append(op)
+        if force or _stale(op, [sp] + HEADERS):
+            jobs.append([NVCC] + FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op])
+
     def run(cmd):
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
@@ -48,7 +60,7 @@ def build(force=False, verbose=False):
 
     logs = []
     if jobs:
-        with ThreadPoolExecutor(max_workers=len(jobs)) as ex:
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             logs = list(ex.map(run, jobs))
     if jobs or _stale(OUT, objs):
         run([NVCC, "-shared", "-cudart", "static", "-o", OUT] + objs + ["-lpthread", "-ldl", "-lrt"])

@@ -153,7 +153,7 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 		s->scratch_cand = have_c;
 		d_cand = s->d_cand;
 	}
-	LMD_CUDA_OK(cudaMemsetAsync(s->d_counters, 0, 6 * sizeof(unsigned long long), st));
+	LMD_CUDA_OK(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), st));
 
 	TraverseArgs ta;
 	ta.s = s;
@@ -209,7 +209,7 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 			LMD_CUDA_OK(cudaMemcpyAsync(out_qstats, d_qstats, nq * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		}
 	}
-	unsigned long long h_cnt[6] = {0, 0, 0, 0, 0, 0};
+	unsigned long long h_cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 	if (stats) {
 		LMD_CUDA_OK(cudaMemcpyAsync(h_cnt, s->d_counters, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
 	}
@@ -226,6 +226,7 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 		stats->filter_evictions = h_cnt[3];
 		stats->reranked = h_cnt[4];
 		stats->tie_overflows = h_cnt[5];
+		stats->merge_fallbacks = h_cnt[6];
 		stats->launches = launches;
 		stats->l_used = l_used;
 		cudaEventElapsedTime(&stats->traverse_ms, s->ev[1], s->ev[2]);

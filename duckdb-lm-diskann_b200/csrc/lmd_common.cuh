@@ -74,6 +74,7 @@ struct Tuning {
 	int warps_per_cta = 4;
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
 	int tie_slots = -1;    // -1 = default (64 for ternary routing, 0 for exact)
+	int merge_min = 0;     // batch-merge new candidates when at least this many pass the threshold (0 = default 5)
 };
 
 } // namespace lmd
@@ -97,7 +98,7 @@ struct lmd_store {
 	uint32_t *d_map_vals = nullptr;
 	uint64_t map_cap = 0;
 	bool identity = true;          // every row id so far equals its slot: the map is bypassed
-	unsigned long long *d_counters = nullptr; // [8] work counter + statistics
+	unsigned long long *d_counters = nullptr; // [16] work counter + statistics ([8], [9]: store-side scratch)
 	uint64_t device_bytes = 0;
 
 	// scratch for host<->device staging of one search call (grown on demand)

@@ -1,0 +1,828 @@
+// Traversal + rerank kernels of the LM_DISKANN query path for sm_100a.
+//
+// Replaces core/Searcher.cpp:45-246 (PerformSearch) with the semantics of the patched oracle
+// (oracle/patches/searcher_fixed.patch, hunks H1-H4). One WARP owns one query from start to finish;
+// a persistent grid pulls queries from a global counter. Per query, in the warp's slice of shared memory:
+//
+//   s_list   [LPL*32] u64  the top-L list (core/Searcher.cpp:64-65 `top_candidates` and :67 `candidate_beam`
+//                          in one structure): sorted keys (distance, slot, expanded-bit). The closest entry
+//                          whose expanded bit is clear is the beam's top(); the search ends when none is left,
+//                          which is the H2 `break` (the beam only holds list members and evicted, farther nodes).
+//   s_filter [2^f]   u32   visited filter (core/Searcher.cpp:63 `visited_nodes`), open addressing with at most 8
+//                          probes; when a probe window is full the home slot is overwritten. A forgotten node can
+//                          only be re-evaluated, never re-admitted: it is either still in the list (dropped as a
+//                          duplicate at insert) or was rejected/evicted with distance >= the list's worst, which
+//                          only shrinks. Results are therefore independent of the filter size.
+//   s_nb/s_d/s_d2 [32]     compacted new neighbour slots of the current expansion and their raw distance sums.
+//
+// Memory traffic per expansion (exact routing): one 4*R byte row of the slot sidecar, then one row_floats*4 byte
+// row of the packed vector table per NEW neighbour, fetched with 128-bit loads by TEAM lanes per row, G rows per
+// team in flight at once.
+//
+// This header holds the device code and the launch helpers; it is compiled once per (kernel kind, metric, route)
+// by lmd_kernel_inst.cu so that the template variants build in parallel.
+#pragma once
+#include "lmd_common.cuh"
+
+namespace lmd {
+
+struct KParams {
+	const float *__restrict__ vecs;
+	const uint32_t *__restrict__ nbrs;
+	const int64_t *__restrict__ row_ids;
+	const uint8_t *__restrict__ blocks;
+	const float *__restrict__ queries;
+	int64_t *out_ids;
+	float *out_dist;
+	uint32_t *out_count;
+	uint32_t *qstats;
+	uint64_t *cand;
+	unsigned long long *counters; // [0] next query, [1] E, [2] V, [3] filter evictions, [4] reranked, [5] tie overflows, [6] merge fallbacks
+	uint64_t block_bytes, pos_off, neg_off;
+	uint32_t nq, dims, row_floats, r, words;
+	uint32_t L, k, metric, list_cap, merge_min;
+	uint32_t entry_slot, has_entry;
+	uint32_t filter_mask, filter_shift;
+	uint32_t warp_smem_bytes;
+};
+
+#define FULL 0xFFFFFFFFu
+#define FILTER_EMPTY 0xFFFFFFFFu
+
+__device__ __forceinline__ float4 ldg4(const float *p) {
+	return __ldg(reinterpret_cast<const float4 *>(p));
+}
+
+// core/distance.hpp:50-105 (ComputeExactDistanceFloat), partial sums of one lane over one float4
+template <int METRIC>
+__device__ __forceinline__ void accum(float4 q, float4 x, float &a, float &b) {
+	if (METRIC == LMD_METRIC_L2) {
+		float d0 = q.x - x.x, d1 = q.y - x.y, d2 = q.z - x.z, d3 = q.w - x.w;
+		a = fmaf(d0, d0, a);
+		a = fmaf(d1, d1, a);
+		a = fmaf(d2, d2, a);
+		a = fmaf(d3, d3, a);
+	} else {
+		a = fmaf(q.x, x.x, a);
+		a = fmaf(q.y, x.y, a);
+		a = fmaf(q.z, x.z, a);
+		a = fmaf(q.w, x.w, a);
+		if (METRIC == LMD_METRIC_COSINE) {
+			b = fmaf(x.x, x.x, b);
+			b = fmaf(x.y, x.y, b);
+			b = fmaf(x.z, x.z, b);
+			b = fmaf(x.w, x.w, b);
+		}
+	}
+}
+
+// the tail of each metric (distance.hpp:62-67, :74, :85-98); na = squared norm of the query
+template <int METRIC>
+__device__ __forceinline__ float finish(float a, float b, float na) {
+	float d;
+	if (METRIC == LMD_METRIC_L2) {
+		d = sqrtf(a < 0.0f ? 0.0f : a);
+	} else if (METRIC == LMD_METRIC_IP) {
+		d = -a;
+	} else {
+		if (na <= 0.0f || b <= 0.0f) {
+			return 1.0f;
+		}
+		float ra = sqrtf(na), rb = sqrtf(b);
+		if (ra == 0.0f || rb == 0.0f) {
+			return 1.0f;
+		}
+		float c = a / (ra * rb);
+		c = fmaxf(-1.0f, fminf(1.0f, c));
+		d = 1.0f - c;
+	}
+	return d + 0.0f; // -0.0 -> +0.0 so that equal distances have equal keys
+}
+
+template <int TEAM>
+__device__ __forceinline__ float team_sum(float v) {
+#pragma unroll
+	for (int o = TEAM / 2; o > 0; o >>= 1) {
+		v += __shfl_xor_sync(FULL, v, o);
+	}
+	return v;
+}
+
+// Per-warp view of the query. CH > 0: each lane keeps its CH float4 pieces in registers (piece c of lane t
+// inside a team covers floats [(c*TEAM + t)*4, +4)). CH == 0: generic shape, the query sits in shared memory.
+template <int TEAM, int CH>
+struct QueryRegs {
+	float4 q[CH > 0 ? CH : 1];
+	const float *sq; // generic only
+	float na;
+};
+
+template <int TEAM, int CH, int METRIC>
+__device__ __forceinline__ void load_query(QueryRegs<TEAM, CH> &Q, const KParams &p, uint32_t qi, int lane,
+                                           float *s_q) {
+	const float *src = p.queries + (uint64_t)qi * p.dims;
+	float na = 0.0f;
+	if (CH > 0) {
+		const int tl = lane % TEAM;
+#pragma unroll
+		for (int c = 0; c < (CH > 0 ? CH : 1); c++) {
+			uint32_t f = (uint32_t)(c * TEAM + tl) * 4;
+			float4 v;
+			v.x = f + 0 < p.dims ? __ldg(src + f + 0) : 0.0f;
+			v.y = f + 1 < p.dims ? __ldg(src + f + 1) : 0.0f;
+			v.z = f + 2 < p.dims ? __ldg(src + f + 2) : 0.0f;
+			v.w = f + 3 < p.dims ? __ldg(src + f + 3) : 0.0f;
+			Q.q[c] = v;
+			na = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, na))));
+		}
+		na = team_sum<TEAM>(na);
+	} else {
+		for (uint32_t f = lane; f < p.row_floats; f += 32) {
+			float v = f < p.dims ? __ldg(src + f) : 0.0f;
+			s_q[f] = v;
+			na = fmaf(v, v, na);
+		}
+		na = team_sum<32>(na);
+		Q.sq = s_q;
+		__syncwarp();
+	}
+	Q.na = na;
+}
+
+// Raw partial results of the exact distance from the query to the m (1..32) nodes whose slots are in s_nb[0..m):
+// s_a[j] = sum of squared differences (L2) or dot product (IP / COSINE), s_b2[j] = squared norm of the node (COSINE).
+// TEAM lanes share one row; a warp works on (32/TEAM)*G rows at a time with all their loads issued first.
+// The metric's tail (sqrt / clamp / ...) is applied once per batch by finish_batch(), one lane per row, instead of
+// once per pass by every lane.
+template <int TEAM, int CH, int G, int METRIC>
+__device__ __forceinline__ void compute_batch(const QueryRegs<TEAM, CH> &Q, const KParams &p, const uint32_t *s_nb,
+                                              float *s_a, float *s_b2, int m, int lane) {
+	if (CH > 0) {
+		constexpr int NT = 32 / TEAM;
+		constexpr int CHN = CH > 0 ? CH : 1;
+		const int team = lane / TEAM, tl = lane % TEAM;
+		for (int j0 = 0; j0 < m; j0 += NT * G) {
+			float4 x[G][CHN];
+#pragma unroll
+			for (int g = 0; g < G; g++) {
+				int j = j0 + g * NT + team;
+				uint32_t id = s_nb[j < m ? j : m - 1];
+				const float *row = p.vecs + (uint64_t)id * p.row_floats + tl * 4;
+#pragma unroll
+				for (int c = 0; c < CHN; c++) {
+					x[g][c] = ldg4(row + c * TEAM * 4);
+				}
+			}
+#pragma unroll
+			for (int g = 0; g < G; g++) {
+				float a = 0.0f, b = 0.0f;
+#pragma unroll
+				for (int c = 0; c < CHN; c++) {
+					accum<METRIC>(Q.q[c], x[g][c], a, b);
+				}
+				a = team_sum<TEAM>(a);
+				if (METRIC == LMD_METRIC_COSINE) {
+					b = team_sum<TEAM>(b);
+				}
+				int j = j0 + g * NT + team;
+				if (tl == 0 && j < m) {
+					s_a[j] = a;
+					if (METRIC == LMD_METRIC_COSINE) {
+						s_b2[j] = b;
+					}
+				}
+			}
+		}
+	} else {
+		const uint32_t nch = p.row_floats / 4;
+		for (int j = 0; j < m; j++) {
+			const float *row = p.vecs + (uint64_t)s_nb[j] * p.row_floats;
+			float a = 0.0f, b = 0.0f;
+			for (uint32_t c = lane; c < nch; c += 32) {
+				float4 x = ldg4(row + c * 4);
+				float4 q = *reinterpret_cast<const float4 *>(Q.sq + c * 4);
+				accum<METRIC>(q, x, a, b);
+			}
+			a = team_sum<32>(a);
+			if (METRIC == LMD_METRIC_COSINE) {
+				b = team_sum<32>(b);
+			}
+			if (lane == 0) {
+				s_a[j] = a;
+				if (METRIC == LMD_METRIC_COSINE) {
+					s_b2[j] = b;
+				}
+			}
+		}
+	}
+}
+
+// Lane j < m turns the raw sums of row j into the reference's distance (must follow a __syncwarp()).
+template <int METRIC>
+__device__ __forceinline__ float finish_batch(const float *s_a, const float *s_b2, float na, int m, int lane) {
+	if (lane >= m) {
+		return 0.0f;
+	}
+	return finish<METRIC>(s_a[lane], METRIC == LMD_METRIC_COSINE ? s_b2[lane] : 0.0f, na);
+}
+
+// Pulls the m rows that compute_batch() is about to read into L2, every 128-byte line of every row at once, so that
+// the passes of compute_batch() wait for L2 instead of one HBM round trip each.
+__device__ __forceinline__ void prefetch_rows(const KParams &p, const uint32_t *s_nb, int m, int lane) {
+	const uint32_t lines_per_row = p.row_floats / 32; // row_floats is a multiple of 32 floats = 128 bytes
+	const uint32_t total = (uint32_t)m * lines_per_row;
+	for (uint32_t t = lane; t < total; t += 32) {
+		const uint32_t j = t / lines_per_row, l = t - j * lines_per_row;
+		const float *a = p.vecs + (uint64_t)s_nb[j] * p.row_floats + l * 32;
+		asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+	}
+}
+
+// core/Searcher.cpp:135-139: `if (visited.count(id)) continue; visited.insert(id);` - true when id is new.
+__device__ __forceinline__ bool filter_test_and_set(uint32_t *tab, uint32_t mask, uint32_t shift, uint32_t id,
+                                                    uint32_t &evictions) {
+	const uint32_t home = (id * 2654435761u) >> shift;
+	uint32_t h = home;
+#pragma unroll 1
+	for (int probe = 0; probe < 8; probe++) {
+		uint32_t old = atomicCAS(&tab[h], FILTER_EMPTY, id);
+		if (old == FILTER_EMPTY) {
+			return true;
+		}
+		if (old == id) {
+			return false;
+		}
+		h = (h + 1) & mask;
+	}
+	tab[home] = id; // window full: forget whoever lived at the home slot
+	evictions++;
+	return true;
+}
+
+// Sorted insert of one key (warp-uniform) into s_list[0..n). The list holds the top-L entries in [0, L) and, behind
+// them, the TIE REGION: entries pushed out of the top L whose distance still EQUALS the L-th distance. The oracle
+// keeps such entries in its frontier heap and expands them, because its cut-off is `distance > worst`
+// (core/Searcher.cpp:112-114 + H2), not `>=`; they sort after every top-L entry, so "first unexpanded entry of the
+// whole array" is exactly the oracle's pop order. The region is bounded by cap (= LPL*32 or L + tie_slots); a tied,
+// unexpanded entry that does not fit is dropped and counted in `overflow` (statistics: results may then differ from
+// the oracle inside that distance tie only). Duplicates of a listed (distance, slot) pair are dropped.
+// Returns the new length.
+template <int LPL>
+__device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, int cap, uint64_t key, int lane,
+                                           uint32_t &overflow) {
+	uint64_t e[LPL];
+	int pos = 0;
+	bool dup = false;
+	const uint64_t k1 = key >> 1;
+#pragma unroll
+	for (int c = 0; c < LPL; c++) {
+		int i = c * 32 + lane;
+		e[c] = i < n ? s_list[i] : LMD_KEY_NONE;
+		uint64_t e1 = e[c] >> 1;
+		pos += __popc(__ballot_sync(FULL, e1 < k1));
+		dup |= __any_sync(FULL, e1 == k1);
+	}
+	if (dup || pos >= cap) {
+		return n;
+	}
+	__syncwarp();
+	// entry that falls off the end of the array (only when n == cap)
+	const uint64_t last = n == cap ? s_list[cap - 1] : LMD_KEY_NONE;
+#pragma unroll
+	for (int c = 0; c < LPL; c++) {
+		int i = c * 32 + lane;
+		if (i < n && i >= pos && i + 1 < cap) {
+			s_list[i + 1] = e[c];
+		}
+	}
+	if (lane == 0) {
+		s_list[pos] = key;
+	}
+	__syncwarp();
+	int nn = n < cap ? n + 1 : cap;
+	if (nn > L) {
+		// trim the tie region: keep entries behind the top L only while they tie with the L-th distance
+		const uint32_t wd = (uint32_t)(s_list[L - 1] >> 32);
+		int keep = L;
+#pragma unroll
+		for (int c = 0; c < LPL; c++) {
+			int i = c * 32 + lane;
+			bool tie = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
+			keep += __popc(__ballot_sync(FULL, tie));
+		}
+		if (last != LMD_KEY_NONE && keep == cap && (uint32_t)(last >> 32) == wd && !(last & 1ull)) {
+			overflow++;
+		}
+		nn = keep;
+	}
+	return nn;
+}
+
+// Ascending bitonic sort of one u64 per lane across the warp (LMD_KEY_NONE sorts last).
+__device__ __forceinline__ uint64_t warp_sort_keys(uint64_t key, int lane) {
+#pragma unroll
+	for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+		for (int j = k >> 1; j > 0; j >>= 1) {
+			const uint64_t other = __shfl_xor_sync(FULL, key, j);
+			const bool keep_min = ((lane & j) == 0) == ((lane & k) == 0);
+			const bool lt = key < other;
+			key = (lt == keep_min) ? key : other;
+		}
+	}
+	return key;
+}
+
+// Batch form of list_insert(): merges the warp's sorted batch (lane j holds the j-th smallest new key, cnt valid
+// keys, LMD_KEY_NONE behind them) into s_list[0..n) in one pass. Every list entry and every batch key finds its
+// merged position by a binary search in the other sequence (s_bk = the batch in shared memory), then all of them are
+// written at once. The result equals cnt calls of list_insert() in neighbour order (core/Searcher.cpp:175-185)
+// whenever no batch key shares its DISTANCE with another batch key or a list entry: with distinct distances the
+// final list is the L smallest of the union, however the threshold moved in between. If such a tie (or a duplicate
+// of a listed node) exists, nothing is written and `fallback` is set: the caller replays the batch one by one.
+template <int LPL>
+__device__ __forceinline__ int list_merge_batch(uint64_t *s_list, uint64_t *s_bk, int n, int L, int cap, uint64_t bkey,
+                                                int cnt, int lane, uint32_t &overflow, bool &fallback) {
+	constexpr int CAPP2 = LPL <= 1 ? 32 : LPL <= 2 ? 64 : LPL <= 4 ? 128 : LPL <= 8 ? 256 : 512;
+	s_bk[lane] = bkey;
+	__syncwarp();
+	// list entries: how many batch keys sort before each
+	uint64_t e[LPL];
+	int shift_by[LPL];
+#pragma unroll
+	for (int c = 0; c < LPL; c++) {
+		const int i = c * 32 + lane;
+		e[c] = LMD_KEY_NONE;
+		shift_by[c] = 0;
+		if (c * 32 < n) {
+			e[c] = i < n ? s_list[i] : LMD_KEY_NONE;
+			const uint64_t e1 = e[c] >> 1;
+			int lo = 0;
+#pragma unroll
+			for (int step = 16; step > 0; step >>= 1) {
+				if ((s_bk[lo + step - 1] >> 1) < e1) {
+					lo += step;
+				}
+			}
+			if ((s_bk[lo] >> 1) < e1) {
+				lo++;
+			}
+			shift_by[c] = lo;
+		}
+	}
+	// batch keys: how many list entries sort before each
+	const uint64_t b1 = bkey >> 1;
+	const uint32_t bhi = (uint32_t)(bkey >> 32);
+	int lo = 0;
+#pragma unroll
+	for (int step = CAPP2 / 2; step > 0; step >>= 1) {
+		const int t = lo + step - 1;
+		if (t < n && (s_list[t] >> 1) < b1) {
+			lo += step;
+		}
+	}
+	if (lo < n && (s_list[lo] >> 1) < b1) {
+		lo++;
+	}
+	const uint32_t prev_hi = (uint32_t)(__shfl_up_sync(FULL, bkey, 1) >> 32);
+	bool tie = false;
+	if (lane < cnt) {
+		tie = (lo < n && (uint32_t)(s_list[lo] >> 32) == bhi) || (lo > 0 && (uint32_t)(s_list[lo - 1] >> 32) == bhi) ||
+		      (lane > 0 && prev_hi == bhi);
+	}
+	if (__any_sync(FULL, tie)) {
+		fallback = true;
+		return n;
+	}
+	__syncwarp(); // every read of the old list is done
+#pragma unroll
+	for (int c = 0; c < LPL; c++) {
+		const int i = c * 32 + lane;
+		if (i < n && i + shift_by[c] < cap) {
+			s_list[i + shift_by[c]] = e[c];
+		}
+	}
+	if (lane < cnt && lane + lo < cap) {
+		s_list[lane + lo] = bkey;
+	}
+	__syncwarp();
+	int nn = n + cnt < cap ? n + cnt : cap;
+	if (nn > L) {
+		// trim the tie region exactly as list_insert() does; entries pushed past `cap` that would have stayed count
+		// as overflow
+		const uint32_t wd = (uint32_t)(s_list[L - 1] >> 32);
+		int keep = L;
+		bool lost = false;
+#pragma unroll
+		for (int c = 0; c < LPL; c++) {
+			const int i = c * 32 + lane;
+			const bool tie_kept = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
+			keep += __popc(__ballot_sync(FULL, tie_kept));
+			lost |= i < n && i + shift_by[c] >= cap && (uint32_t)(e[c] >> 32) == wd && !(e[c] & 1ull);
+		}
+		overflow += __popc(__ballot_sync(FULL, lost));
+		nn = keep;
+	}
+	return nn;
+}
+
+template <int LPL>
+__device__ __forceinline__ int find_unexpanded(const uint64_t *s_list, int n, int lane) {
+#pragma unroll
+	for (int c = 0; c < LPL; c++) {
+		int i = c * 32 + lane;
+		bool un = i < n && !(s_list[i] & 1ull);
+		uint32_t b = __ballot_sync(FULL, un);
+		if (b) {
+			return c * 32 + __ffs(b) - 1;
+		}
+		if ((c + 1) * 32 >= n) {
+			break;
+		}
+	}
+	return -1;
+}
+
+// Ternary planes of the query (core/ternary_quantization.hpp:146-199 EncodeTernary) as 32-bit halves:
+// s_qp[g] holds bits [32g, 32g+32) of the positive plane, s_qn likewise.
+__device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t qi, int lane, uint32_t *s_qp,
+                                                    uint32_t *s_qn) {
+	const float *src = p.queries + (uint64_t)qi * p.dims;
+	for (uint32_t g = 0; g < p.words * 2; g++) {
+		uint32_t f = g * 32 + lane;
+		float v = f < p.dims ? __ldg(src + f) : 0.0f;
+		uint32_t bp = __ballot_sync(FULL, v > 0.0f);
+		uint32_t bn = __ballot_sync(FULL, v < 0.0f);
+		if (lane == 0) {
+			s_qp[g] = bp;
+			s_qn[g] = bn;
+		}
+	}
+	__syncwarp();
+}
+
+// core/ternary_quantization.hpp:269-296 (Dot_scalar) + core/distance.hpp:229-235 for neighbour j of block `blk`
+__device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_t *blk, uint32_t j,
+                                                  const uint32_t *s_qp, const uint32_t *s_qn) {
+	const uint2 *vp = reinterpret_cast<const uint2 *>(blk + p.pos_off) + (uint64_t)j * p.words;
+	const uint2 *vn = reinterpret_cast<const uint2 *>(blk + p.neg_off) + (uint64_t)j * p.words;
+	int score = 0;
+	for (uint32_t w = 0; w < p.words; w++) {
+		uint2 a = __ldg(vp + w), b = __ldg(vn + w);
+		uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
+		score += __popc(qp0 & a.x) + __popc(qp1 & a.y) + __popc(qn0 & b.x) + __popc(qn1 & b.y);
+		score -= __popc(qp0 & b.x) + __popc(qp1 & b.y) + __popc(qn0 & a.x) + __popc(qn1 & a.y);
+	}
+	float sim = (float)score;
+	float d = p.metric == LMD_METRIC_IP ? -sim : 1.0f - sim;
+	return d + 0.0f;
+}
+
+template <int TEAM, int CH, int G, int LPL, int METRIC, int ROUTE>
+__global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
+	extern __shared__ __align__(16) uint8_t smem[];
+	const int lane = threadIdx.x & 31;
+	uint8_t *wbase = smem + (threadIdx.x >> 5) * p.warp_smem_bytes;
+	uint64_t *s_list = reinterpret_cast<uint64_t *>(wbase);
+	uint32_t *s_nb = reinterpret_cast<uint32_t *>(s_list + LPL * 32);
+	float *s_d = reinterpret_cast<float *>(s_nb + 32);
+	uint64_t *s_bk = reinterpret_cast<uint64_t *>(s_nb); // the sorted batch of list_merge_batch() reuses s_nb + s_d
+	float *s_d2 = s_d + 32;
+	uint32_t *s_filter = reinterpret_cast<uint32_t *>(s_d2 + 32);
+	uint8_t *extra = reinterpret_cast<uint8_t *>(s_filter + p.filter_mask + 1);
+	float *s_q = reinterpret_cast<float *>(extra); // generic shape only
+	uint32_t *s_qp = reinterpret_cast<uint32_t *>(extra + (CH == 0 ? p.row_floats * 4 : 0));
+	uint32_t *s_qn = s_qp + p.words * 2;
+	const int L = (int)p.L;
+	const int cap = (int)p.list_cap;
+	const uint32_t nbr_lines = (p.r * 4 + 127) / 128;
+
+	for (;;) {
+		uint32_t qi = 0;
+		if (lane == 0) {
+			qi = (uint32_t)atomicAdd(&p.counters[0], 1ull);
+		}
+		qi = __shfl_sync(FULL, qi, 0);
+		if (qi >= p.nq) {
+			break;
+		}
+		uint32_t n_exp = 0, n_eval = 0, n_evict = 0, n_tie_ovf = 0, n_fallback = 0;
+		int n = 0;
+		{
+			uint4 e4 = make_uint4(FILTER_EMPTY, FILTER_EMPTY, FILTER_EMPTY, FILTER_EMPTY);
+			uint4 *f4 = reinterpret_cast<uint4 *>(s_filter);
+			for (uint32_t i = lane; i < (p.filter_mask + 1) / 4; i += 32) {
+				f4[i] = e4;
+			}
+		}
+		QueryRegs<TEAM, CH> Q;
+		load_query<TEAM, CH, METRIC>(Q, p, qi, lane, s_q);
+		if (ROUTE == LMD_ROUTE_TERNARY) {
+			encode_query_planes(p, qi, lane, s_qp, s_qn);
+		}
+		__syncwarp();
+
+		if (p.has_entry) { // core/Searcher.cpp:70-103
+			if (lane == 0) {
+				s_nb[0] = p.entry_slot;
+				filter_test_and_set(s_filter, p.filter_mask, p.filter_shift, p.entry_slot, n_evict);
+			}
+			__syncwarp();
+			compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, 1, lane);
+			__syncwarp();
+			const float d0 = finish_batch<METRIC>(s_d, s_d2, Q.na, 1, lane);
+			if (lane == 0) {
+				s_list[0] = make_key(d0, p.entry_slot);
+			}
+			n = 1;
+			n_eval = 1;
+			__syncwarp();
+		}
+
+		while (n > 0) { // core/Searcher.cpp:108-187
+			int idx = find_unexpanded<LPL>(s_list, n, lane);
+			if (idx < 0) {
+				break;
+			}
+			const uint64_t cur_key = s_list[idx];
+			const uint32_t cur = key_slot(cur_key);
+			__syncwarp();
+			if (lane == 0) {
+				s_list[idx] = cur_key | 1ull;
+			}
+			__syncwarp();
+			n_exp++;
+			const uint32_t *nrow = p.nbrs + (uint64_t)cur * p.r;
+			const uint8_t *blk = p.blocks + (uint64_t)cur * p.block_bytes;
+			uint32_t id_next = lane < p.r ? __ldg(nrow + lane) : LMD_INVALID_SLOT;
+			{
+				// the runner-up of the frontier is the most likely next expansion: pull its neighbour row into L2 now
+				const int idx2 = find_unexpanded<LPL>(s_list, n, lane);
+				if (idx2 >= 0 && (uint32_t)lane < nbr_lines) {
+					const uint32_t *nx = p.nbrs + (uint64_t)key_slot(s_list[idx2]) * p.r + lane * 32;
+					asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
+				}
+			}
+			for (uint32_t base = 0; base < p.r; base += 32) {
+				const uint32_t j = base + lane;
+				const uint32_t id = id_next;
+				if (base + 32 < p.r) {
+					id_next = j + 32 < p.r ? __ldg(nrow + j + 32) : LMD_INVALID_SLOT;
+				}
+				bool isnew = false;
+				if (id != LMD_INVALID_SLOT) {
+					isnew = filter_test_and_set(s_filter, p.filter_mask, p.filter_shift, id, n_evict);
+				}
+				const uint32_t mask = __ballot_sync(FULL, isnew);
+				const int m = __popc(mask);
+				if (m == 0) {
+					continue;
+				}
+				n_eval += m;
+				float d = 0.0f;
+				uint32_t myid = id;
+				bool have = isnew;
+				if (ROUTE == LMD_ROUTE_EXACT) {
+					const int pos = __popc(mask & ((1u << lane) - 1u));
+					if (isnew) {
+						s_nb[pos] = id;
+					}
+					__syncwarp();
+					prefetch_rows(p, s_nb, m, lane);
+					compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, m, lane);
+					__syncwarp();
+					have = lane < m;
+					d = finish_batch<METRIC>(s_d, s_d2, Q.na, m, lane);
+					if (have) {
+						myid = s_nb[lane];
+					}
+					__syncwarp();
+				} else {
+					if (isnew) {
+						d = ternary_distance(p, blk, j, s_qp, s_qn);
+					}
+				}
+				// core/Searcher.cpp:175-185, candidates taken in neighbour order with a moving threshold
+				float worst = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
+				const bool pass = have && (n < L || d < worst);
+				uint32_t amask = __ballot_sync(FULL, pass);
+				if (ROUTE == LMD_ROUTE_EXACT && __popc(amask) >= (int)p.merge_min) {
+					// same result as the one-by-one loop below, in one merge (see list_merge_batch)
+					const uint64_t bkey = warp_sort_keys(pass ? make_key(d, myid) : LMD_KEY_NONE, lane);
+					bool fallback = false;
+					n = list_merge_batch<LPL>(s_list, s_bk, n, L, cap, bkey, __popc(amask), lane, n_tie_ovf, fallback);
+					if (!fallback) {
+						amask = 0;
+					} else {
+						n_fallback++;
+					}
+				}
+				while (amask) {
+					const int src = __ffs(amask) - 1;
+					amask &= amask - 1;
+					const float dj = __shfl_sync(FULL, d, src);
+					const uint32_t idj = __shfl_sync(FULL, myid, src);
+					if (n >= L && !(dj < worst)) {
+						continue;
+					}
+					n = list_insert<LPL>(s_list, n, L, cap, make_key(dj, idj), lane, n_tie_ovf);
+					if (n >= L) {
+						worst = key_dist(s_list[L - 1]);
+					}
+				}
+			}
+		}
+
+		// results: the top-L part only (the oracle's final pass drains `top_candidates`, core/Searcher.cpp:193-196)
+		if (n > L) {
+			n = L;
+		}
+		if (p.cand) {
+			uint64_t *dst = p.cand + (uint64_t)qi * p.L;
+			for (int i = lane; i < L; i += 32) {
+				dst[i] = i < n ? s_list[i] : LMD_KEY_NONE;
+			}
+		}
+		if (p.out_ids) { // traversal distances are exact: the k best of the list are the answer (Searcher.cpp:189-245)
+			for (uint32_t i = lane; i < p.k; i += 32) {
+				int64_t rid = -1;
+				float dd = 0.0f;
+				if ((int)i < n) {
+					uint64_t key = s_list[i];
+					rid = p.row_ids[key_slot(key)];
+					dd = key_dist(key);
+				}
+				p.out_ids[(uint64_t)qi * p.k + i] = rid;
+				if (p.out_dist) {
+					p.out_dist[(uint64_t)qi * p.k + i] = dd;
+				}
+			}
+			if (p.out_count && lane == 0) {
+				p.out_count[qi] = (uint32_t)n < p.k ? (uint32_t)n : p.k;
+			}
+		}
+		n_evict = __reduce_add_sync(FULL, n_evict);
+		if (lane == 0) {
+			if (p.qstats) {
+				p.qstats[2 * qi] = n_exp;
+				p.qstats[2 * qi + 1] = n_eval;
+			}
+			atomicAdd(&p.counters[1], (unsigned long long)n_exp);
+			atomicAdd(&p.counters[2], (unsigned long long)n_eval);
+			if (n_evict) {
+				atomicAdd(&p.counters[3], (unsigned long long)n_evict);
+			}
+			if (n_tie_ovf) {
+				atomicAdd(&p.counters[5], (unsigned long long)n_tie_ovf);
+			}
+			if (n_fallback) {
+				atomicAdd(&p.counters[6], (unsigned long long)n_fallback);
+			}
+		}
+		__syncwarp();
+	}
+}
+
+// Rerank (core/Searcher.cpp:189-245 + H3): exact distance of every listed candidate, keep the k smallest by
+// (distance, slot), ascending. One warp per query; candidates come from the traversal kernel's list dump.
+template <int TEAM, int CH, int G, int LPL, int METRIC>
+__global__ void __launch_bounds__(128) rerank_kernel(const KParams p) {
+	extern __shared__ __align__(16) uint8_t smem[];
+	const int lane = threadIdx.x & 31;
+	uint8_t *wbase = smem + (threadIdx.x >> 5) * p.warp_smem_bytes;
+	uint32_t *s_nb = reinterpret_cast<uint32_t *>(wbase);
+	float *s_d = reinterpret_cast<float *>(s_nb + 32);
+	float *s_d2 = s_d + 32;
+	float *s_q = s_d2 + 32;
+	const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+	for (uint32_t qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; qi < p.nq; qi += warps) {
+		QueryRegs<TEAM, CH> Q;
+		load_query<TEAM, CH, METRIC>(Q, p, qi, lane, s_q);
+		uint64_t keys[LPL];
+		uint32_t total = 0;
+#pragma unroll
+		for (int c = 0; c < LPL; c++) {
+			const uint32_t i = c * 32 + lane;
+			uint64_t ck = i < p.L ? p.cand[(uint64_t)qi * p.L + i] : LMD_KEY_NONE;
+			const bool valid = ck != LMD_KEY_NONE;
+			const uint32_t mask = __ballot_sync(FULL, valid);
+			const int m = __popc(mask);
+			keys[c] = LMD_KEY_NONE;
+			if (m == 0) {
+				continue;
+			}
+			// the list is dense from the front, so valid lanes are 0..m-1
+			__syncwarp();
+			if (valid) {
+				s_nb[lane] = key_slot(ck);
+			}
+			__syncwarp();
+			prefetch_rows(p, s_nb, m, lane);
+			compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, m, lane);
+			__syncwarp();
+			const float dd = finish_batch<METRIC>(s_d, s_d2, Q.na, m, lane);
+			if (valid) {
+				keys[c] = make_key(dd, key_slot(ck));
+			}
+			total += m;
+		}
+		// k rounds of warp-wide min extraction
+		const uint32_t kk = total < p.k ? total : p.k;
+		for (uint32_t out = 0; out < p.k; out++) {
+			uint64_t best = LMD_KEY_NONE;
+#pragma unroll
+			for (int c = 0; c < LPL; c++) {
+				best = keys[c] < best ? keys[c] : best;
+			}
+			uint64_t wmin = best;
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) {
+				uint64_t other = __shfl_xor_sync(FULL, wmin, o);
+				wmin = other < wmin ? other : wmin;
+			}
+#pragma unroll
+			for (int c = 0; c < LPL; c++) {
+				if (keys[c] == wmin) {
+					keys[c] = LMD_KEY_NONE; // keys are unique per slot
+				}
+			}
+			if (lane == 0) {
+				const bool ok = out < kk && wmin != LMD_KEY_NONE;
+				p.out_ids[(uint64_t)qi * p.k + out] = ok ? p.row_ids[key_slot(wmin)] : -1;
+				if (p.out_dist) {
+					p.out_dist[(uint64_t)qi * p.k + out] = ok ? key_dist(wmin) : 0.0f;
+				}
+			}
+		}
+		if (lane == 0) {
+			if (p.out_count) {
+				p.out_count[qi] = kk;
+			}
+			atomicAdd(&p.counters[4], (unsigned long long)total);
+		}
+		__syncwarp();
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// launch helpers shared by the per-variant translation units
+// ------------------------------------------------------------------------------------------------
+template <typename K>
+static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, uint32_t nq, cudaStream_t st,
+                                    const char *what) {
+	const int warps = 4; // __launch_bounds__(128)
+	size_t smem = (size_t)p.warp_smem_bytes * warps;
+	LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	int per_sm = 0;
+	LMD_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, warps * 32, smem));
+	if (per_sm < 1) {
+		set_error("%s: kernel does not fit on an SM with %zu bytes of shared memory per CTA", what, smem);
+		return LMD_ERR_UNSUPPORTED;
+	}
+	if (s->tune.ctas_per_sm > 0 && s->tune.ctas_per_sm < per_sm) {
+		per_sm = s->tune.ctas_per_sm;
+	}
+	uint32_t grid = (nq + warps - 1) / warps;
+	uint32_t cap = (uint32_t)(per_sm * s->sm_count);
+	if (grid > cap) {
+		grid = cap;
+	}
+	kernel<<<grid, warps * 32, smem, st>>>(p);
+	LMD_CUDA_OK(cudaGetLastError());
+	return LMD_OK;
+}
+
+#define LMD_DISPATCH_LPL(KERNEL, TEAM, CH, G, METRIC, ...)                                                             \
+	switch (lpl) {                                                                                                     \
+	case 1:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 1, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 2:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 2, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 3:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 3, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 4:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 4, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 6:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 6, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 8:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 8, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 12:                                                                                                           \
+		return launch_persistent(KERNEL<TEAM, CH, G, 12, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);               \
+	case 16:                                                                                                           \
+		return launch_persistent(KERNEL<TEAM, CH, G, 16, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);               \
+	default:                                                                                                           \
+		break;                                                                                                         \
+	}
+
+#define LMD_DISPATCH_SHAPE(KERNEL, METRIC, ...)                                                                        \
+	if (p.row_floats == 128) {                                                                                         \
+		LMD_DISPATCH_LPL(KERNEL, 8, 4, 2, METRIC, ##__VA_ARGS__)                                                       \
+	} else if (p.row_floats == 96) {                                                                                   \
+		LMD_DISPATCH_LPL(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                       \
+	} else if (p.row_floats == 768) {                                                                                  \
+		LMD_DISPATCH_LPL(KERNEL, 32, 6, 2, METRIC, ##__VA_ARGS__)                                                      \
+	} else {                                                                                                           \
+		LMD_DISPATCH_LPL(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                                      \
+	}
+
+} // namespace lmd

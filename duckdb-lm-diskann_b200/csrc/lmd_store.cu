@@ -165,7 +165,7 @@ static lmd_status lookup_slot(lmd_store *s, int64_t row_id, uint32_t *slot) {
 		*slot = (row_id >= 0 && (uint64_t)row_id < s->n) ? (uint32_t)row_id : LMD_INVALID_SLOT;
 		return LMD_OK;
 	}
-	uint32_t *d_tmp = reinterpret_cast<uint32_t *>(s->d_counters + 7);
+	uint32_t *d_tmp = reinterpret_cast<uint32_t *>(s->d_counters + 9);
 	lookup_one_kernel<<<1, 1, 0, s->stream>>>((const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, row_id,
 	                                          d_tmp);
 	LMD_CUDA_OK(cudaGetLastError());
@@ -304,7 +304,7 @@ lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity
 	LMD_ALLOC(s->d_row_ids, capacity_nodes * sizeof(int64_t));
 	LMD_ALLOC(s->d_map_keys, s->map_cap * sizeof(int64_t));
 	LMD_ALLOC(s->d_map_vals, s->map_cap * sizeof(uint32_t));
-	LMD_ALLOC(s->d_counters, 8 * sizeof(unsigned long long));
+	LMD_ALLOC(s->d_counters, 16 * sizeof(unsigned long long));
 #undef LMD_ALLOC
 	if (cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
 	    cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -321,7 +321,7 @@ lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity
 	fill_i64_kernel<<<(unsigned)((s->map_cap + 255) / 256), 256, 0, s->stream>>>((long long *)s->d_map_keys, s->map_cap,
 	                                                                              LMD_MAP_EMPTY);
 	if (cudaGetLastError() != cudaSuccess || cudaMemsetAsync(s->d_map_vals, 0, s->map_cap * 4, s->stream) != cudaSuccess ||
-	    cudaMemsetAsync(s->d_counters, 0, 64, s->stream) != cudaSuccess ||
+	    cudaMemsetAsync(s->d_counters, 0, 128, s->stream) != cudaSuccess ||
 	    cudaStreamSynchronize(s->stream) != cudaSuccess) {
 		set_error("store initialisation failed: %s", cudaGetErrorString(cudaGetLastError()));
 		return fail(LMD_ERR_CUDA);
@@ -462,7 +462,7 @@ lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *bl
 		}
 		d_rid = s->d_row_ids + base;
 		if (s->identity) {
-			int *d_flag = reinterpret_cast<int *>(s->d_counters + 6);
+			int *d_flag = reinterpret_cast<int *>(s->d_counters + 8);
 			LMD_CUDA_OK(cudaMemsetAsync(d_flag, 0, sizeof(int), s->stream));
 			check_identity_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(d_rid, base, n, d_flag);
 			int h_flag = 0;
@@ -608,6 +608,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		s->tune.ctas_per_sm = (int)value;
 	} else if (k == "tie_slots") {
 		s->tune.tie_slots = (int)value;
+	} else if (k == "merge_min") {
+		s->tune.merge_min = (int)value;
 	} else {
 		set_error("lmd_set_tuning: unknown key %s", key);
 		return LMD_ERR_INVALID_ARG;

@@ -81,6 +81,7 @@ typedef struct {
 	uint64_t reranked;        /* C: exact distances computed by the rerank kernel */
 	uint64_t filter_evictions;/* visited-filter entries overwritten (costs recomputation, never changes results) */
 	uint64_t tie_overflows;   /* tied frontier entries dropped because the tie region was full (0 = oracle-exact ties) */
+	uint64_t merge_fallbacks; /* candidate batches replayed one by one because of a distance tie (statistics) */
 	uint64_t algorithmic_bytes; /* SURVEY.md section 8d formula for this call */
 	float traverse_ms;        /* CUDA-event time of the traversal kernel */
 	float rerank_ms;          /* CUDA-event time of the rerank kernel (0 when fused away) */
@@ -140,7 +141,8 @@ lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uin
 /* --- misc --- */
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
 uint32_t lmd_abi_version(void);
-/* Tuning knobs for experiments (not needed for correct use): "filter_log2", "warps_per_cta", "ctas_per_sm", "tie_slots". */
+/* Tuning knobs for experiments (not needed for correct use): "filter_log2", "warps_per_cta", "ctas_per_sm", "tie_slots",
+ * "merge_min". */
 lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value);
 
 #ifdef __cplusplus

@@ -203,6 +203,50 @@ def test_filter_size_does_not_change_results(lmd, make_index):
     assert outs[0][3].distance_evals >= outs[-1][3].distance_evals
 
 
+def test_batch_merge_equals_one_by_one(lmd, oracle, make_index):
+    """list_merge_batch() (the default for >= 5 admitted candidates) and the one-by-one insert loop must build the
+    same list: bit-identical ids, distances and per-query expansion / evaluation counts."""
+    for (n, dims, r, metric, kind, L) in [(3000, 128, 32, "L2", "clustered", 64), (2000, 96, 64, "L2", "iid", 100),
+                                          (1500, 768, 32, "COSINE", "clustered", 200), (1500, 100, 24, "IP", "iid", 33)]:
+        ix = make_index(n, dims, r, metric=metric, kind=kind, nq=96)
+        outs = []
+        with _store(lmd, ix, dims, r, metric) as s:
+            s.upload(ix["blocks_np"])
+            s.set_entry(0)
+            for mm in (1, 5, 33):  # always merge / default / never merge
+                s.set_tuning("merge_min", mm)
+                outs.append(s.search(ix["queries"], 10, L, qstats=True))
+        for o in outs[1:]:
+            assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1])
+            assert np.array_equal(o[4], outs[0][4])
+        assert outs[2][3].merge_fallbacks == 0
+
+
+def test_duplicate_vectors_exact_ties(lmd, oracle, fixtures_mod):
+    """A data set where every vector occurs four times: exact fp32 distance ties everywhere, including at the L-th
+    place of the list. The batch merge must detect them and replay one by one, so that the results stay those of the
+    oracle's (distance, row id) order."""
+    n, dims, r = 1600, 64, 16
+    base = fixtures_mod.make_dataset(n // 4, dims, kind="iid", seed=46)
+    x = np.concatenate([base, base, base, base])
+    rng = np.random.default_rng(9)
+    x = x[rng.permutation(n)]
+    nbrs, counts = fixtures_mod.build_graph(x, r, device="cpu")
+    blocks = fixtures_mod.pack_blocks(x, nbrs, counts, r).numpy()
+    lay = fixtures_mod.layout(dims, r)
+    q = fixtures_mod.make_dataset(64, dims, kind="iid", seed=47)
+    with lmd.Store(dims, r, capacity=n) as s:
+        s.upload(blocks)
+        s.set_entry(0)
+        s.set_tuning("tie_slots", 32)
+        g = s.search(q, 10, 24, qstats=True)
+        o = oracle.search(blocks, lay["block_bytes"], dims, r, q, 10, 24, entry_row_id=0)
+        check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="duplicate vectors")
+        assert np.array_equal(g[0], o[0])  # identical even inside the ties: same (distance, id) order
+        assert g[3].merge_fallbacks > 0 and g[3].tie_overflows == 0
+        assert np.array_equal(g[4][:, 0].astype(np.int64), o[3][:, 0].astype(np.int64))  # same expansions per query
+
+
 def test_device_resident_io(lmd, make_index):
     """queries / outputs already in HBM (torch tensors): no staging copies."""
     import torch
