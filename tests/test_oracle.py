@@ -1,0 +1,193 @@
+"""-m "not gpu": pins the CPU oracle (oracle/lmd_oracle.c, the plain-C restatement) against
+
+  1. tests/golden/*.npz - frozen outputs of the REFERENCE'S OWN SOURCES compiled by oracle/Makefile
+     (tests/golden/make_golden.py; liblmd_ref_literal.so for the arithmetic, liblmd_ref_fixed.so =
+     Searcher.cpp + oracle/patches/searcher_fixed.patch for the search), and
+  2. oracle/_ref/*.so live, when those libraries are present (they are built in the container that has
+     /root/reference and travel to the GPU box prebuilt).
+
+Bit-exact everywhere: ids, counts, per-query expansion / fetch counters and fp32 distances.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+SEARCH_FILES = sorted(glob.glob(os.path.join(GOLDEN, "search_*.npz")))
+
+
+def _bits(a):
+    return np.asarray(a, dtype=np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def arith():
+    return np.load(os.path.join(GOLDEN, "arith.npz"))
+
+
+def test_golden_files_present():
+    assert os.path.exists(os.path.join(GOLDEN, "arith.npz"))
+    assert len(SEARCH_FILES) >= 7
+
+
+# ---- core/distance.hpp:50-105 --------------------------------------------------------------------
+@pytest.mark.parametrize("dims", [1, 3, 33, 96, 128, 768])
+def test_distance_kat(oracle, arith, dims):
+    a, b, want = arith["dist_a_%d" % dims], arith["dist_b_%d" % dims], arith["dist_out_%d" % dims]
+    for m in (1, 2, 3):
+        for i in range(a.shape[0]):
+            got, err = oracle.distance(a[i], b[i], m)
+            assert err == 0
+            w = want[m - 1, i]
+            if np.isnan(w):
+                assert np.isnan(got)
+            else:
+                assert _bits(got) == _bits(w), "metric %d dims %d row %d: %r vs %r" % (m, dims, i, got, w)
+
+
+def test_distance_unknown_metric_errors(oracle):
+    # core/distance.hpp:100-103 throws for any other metric (HAMMING = 4 included)
+    _, err = oracle.distance(np.ones(4, np.float32), np.ones(4, np.float32), 4)
+    assert err != 0
+
+
+# ---- core/ternary_quantization.hpp:146-199,269-296; core/distance.hpp:212-243 --------------------
+@pytest.mark.parametrize("dims", [1, 63, 64, 65, 96, 128, 200, 768])
+def test_ternary_kat(oracle, arith, dims):
+    v, w = arith["tern_v_%d" % dims], arith["tern_w_%d" % dims]
+    pos, neg = arith["tern_pos_%d" % dims], arith["tern_neg_%d" % dims]
+    dots, approx = arith["tern_dot_%d" % dims], arith["tern_approx_%d" % dims]
+    for i in range(v.shape[0]):
+        p, n = oracle.encode_ternary(v[i])
+        assert np.array_equal(p, pos[i]) and np.array_equal(n, neg[i])
+        wp, wn = oracle.encode_ternary(w[i])
+        assert oracle.ternary_dot(p, n, wp, wn) == int(dots[i])
+        edge = np.concatenate([wp, wn]).view(np.uint8)
+        for row, metric in ((0, 2), (1, 3)):
+            d, err = oracle.approx_distance(v[i], edge, dims, metric)
+            assert err == 0 and _bits(d) == _bits(approx[row, i])
+        _, err = oracle.approx_distance(v[i], edge, dims, 1)
+        assert err != 0  # L2 throws, core/distance.hpp:236-239
+
+
+# ---- core/index_config.cpp:104-148 ----------------------------------------------------------------
+def test_layout_kat(oracle, arith, fixtures_mod):
+    names = ("count_off", "vector_off", "ids_off", "pos_off", "neg_off", "total_node_size", "ternary_edge_bytes")
+    for (d, r, vt), want in zip(arith["layout_shapes"], arith["layout_out"]):
+        got = oracle.layout(int(d), int(vt), int(r))
+        assert [got[n] for n in names] == [int(x) for x in want[:7]]
+        assert int(oracle.port().lmdo_block_bytes(got["total_node_size"])) == int(want[7])
+        py = fixtures_mod.layout(int(d), int(r), int(vt))
+        assert [py[n] for n in names] == [int(x) for x in want[:7]] and py["block_bytes"] == int(want[7])
+
+
+# ---- core/Searcher.cpp:45-272 (+ H1-H4) ------------------------------------------------------------
+def _load_case(fixtures_mod, path):
+    z = np.load(path)
+    n, dims, r, metric, vec_type, nq, k, L, cfg_l, entry = (int(v) for v in z["meta"])
+    row_ids = z["row_ids"] if "row_ids" in z.files else None
+    blocks = fixtures_mod.pack_blocks(z["x"], z["nbrs"].astype(np.int64), z["counts"].astype(np.int64), r,
+                                      row_ids=row_ids, vec_type=vec_type).numpy()
+    lay = fixtures_mod.layout(dims, r, vec_type)
+    return z, blocks, lay, dict(dims=dims, r=r, metric=metric, vec_type=vec_type, k=k, L=L, cfg_l=cfg_l, entry=entry,
+                                row_ids=row_ids)
+
+
+@pytest.mark.parametrize("path", SEARCH_FILES, ids=[os.path.basename(p)[7:-4] for p in SEARCH_FILES])
+def test_search_golden(oracle, fixtures_mod, path):
+    z, blocks, lay, c = _load_case(fixtures_mod, path)
+    for threads in (1, 3):
+        ids, dist, cnt, st = oracle.search(blocks, lay["block_bytes"], c["dims"], c["r"], z["queries"], c["k"], c["L"],
+                                           metric=c["metric"], vec_type=c["vec_type"], row_ids=c["row_ids"],
+                                           entry_row_id=c["entry"], cfg_l_search=c["cfg_l"], nthreads=threads)
+        assert np.array_equal(ids, z["fixed_ids"])
+        assert np.array_equal(cnt, z["fixed_count"])
+        assert np.array_equal(_bits(dist), _bits(z["fixed_dist"]))
+        assert np.array_equal(st, z["fixed_stats"])
+    # the fixed results are ascending by (distance, id) and the search found something for every query
+    d = z["fixed_dist"]
+    for q in range(d.shape[0]):
+        m = int(z["fixed_count"][q])
+        assert m > 0 and np.all(np.diff(d[q, :m]) >= 0)
+
+
+@pytest.mark.parametrize("path", SEARCH_FILES[:3], ids=[os.path.basename(p)[7:-4] for p in SEARCH_FILES[:3]])
+def test_literal_reference_is_not_a_nearest_neighbour_search(fixtures_mod, path):
+    """the untouched Searcher.cpp keeps the k FARTHEST of a frozen first-L list. The golden
+    files keep its output for transparency; the grading oracle is the patched build."""
+    z = np.load(path)
+    lit, fix = z["literal_dist"], z["fixed_dist"]
+    m = np.minimum(z["literal_count"], z["fixed_count"]).astype(int)
+    worse = sum(float(lit[q, :m[q]].mean()) > float(fix[q, :m[q]].mean()) for q in range(len(m)) if m[q] > 0)
+    assert worse >= 0.9 * len(m)
+
+
+# ---- live against the reference's own sources when oracle/_ref is present -------------------------------
+def _need_ref(oracle, kind):
+    if not oracle.have_ref(kind):
+        pytest.skip("oracle/_ref/%s not built here" % kind)
+
+
+@pytest.mark.parametrize("metric,dims,r,kind,vt", [(1, 64, 16, "clustered", 1), (2, 48, 12, "iid", 1),
+                                                  (3, 72, 20, "iid", 1), (1, 24, 8, "iid", 2)])
+def test_port_equals_reference_fixed_live(oracle, fixtures_mod, metric, dims, r, kind, vt):
+    _need_ref(oracle, "fixed")
+    n, nq = 900, 40
+    x = fixtures_mod.make_dataset(n, dims, kind=kind, seed=5, normalize=(metric == 2))
+    q = fixtures_mod.make_dataset(nq, dims, kind=kind, seed=6, normalize=(metric == 2))
+    if vt == 2:
+        x = np.clip(np.round(x * 40), -127, 127).astype(np.int8)
+        q = (q * 40).astype(np.float32)
+    nb, cn = fixtures_mod.build_graph(np.asarray(x, np.float32), r, device="cpu")
+    rng = np.random.default_rng(3)
+    row_ids = rng.choice(np.arange(0, 50 * n, dtype=np.int64), size=n, replace=False)
+    blocks = fixtures_mod.pack_blocks(x, nb, cn, r, row_ids=row_ids, vec_type=vt).numpy()
+    bb = fixtures_mod.layout(dims, r, vt)["block_bytes"]
+    for k, L in ((10, 32), (1, 0), (50, 20)):
+        a = oracle.search(blocks, bb, dims, r, q, k, L, metric=metric, vec_type=vt, row_ids=row_ids,
+                          entry_row_id=int(row_ids[0]), cfg_l_search=25, impl="port")
+        b = oracle.search(blocks, bb, dims, r, q, k, L, metric=metric, vec_type=vt, row_ids=row_ids,
+                          entry_row_id=int(row_ids[0]), cfg_l_search=25, impl="fixed")
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+        assert np.array_equal(_bits(a[1]), _bits(b[1]))
+
+
+def test_port_skip_rules_equal_reference_live(oracle, fixtures_mod):
+    """Missing entry point -> empty result (Searcher.cpp:74-83); neighbour ids that do not resolve and INT64_MAX
+    sentinels are skipped (:120-122,146-156; GraphManager.cpp:241-254)."""
+    _need_ref(oracle, "fixed")
+    n, dims, r = 300, 16, 8
+    x = fixtures_mod.make_dataset(n, dims, kind="iid", seed=9)
+    q = fixtures_mod.make_dataset(12, dims, kind="iid", seed=10)
+    nb, cn = fixtures_mod.build_graph(x, r, device="cpu")
+    lay = fixtures_mod.layout(dims, r)
+    blocks = fixtures_mod.pack_blocks(x, nb, cn, r).numpy().copy()
+    ids_view = blocks[:, lay["ids_off"]:lay["ids_off"] + 8 * r].copy().view(np.int64)
+    ids_view[5, 0] = 10 ** 12          # dangling row id
+    ids_view[7, 1] = np.iinfo(np.int64).max  # sentinel inside the counted range
+    blocks[:, lay["ids_off"]:lay["ids_off"] + 8 * r] = ids_view.view(np.uint8)
+    for entry in (0, 123456789):
+        a = oracle.search(blocks, lay["block_bytes"], dims, r, q, 5, 16, entry_row_id=entry, impl="port")
+        b = oracle.search(blocks, lay["block_bytes"], dims, r, q, 5, 16, entry_row_id=entry, impl="fixed")
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+        assert np.array_equal(_bits(a[1]), _bits(b[1]))
+        if entry != 0:
+            assert int(a[2].sum()) == 0 and np.all(a[0] == -1)
+
+
+def test_golden_matches_reference_live(oracle, fixtures_mod):
+    """The committed fixtures are what the reference sources produce today (guards against a stale golden)."""
+    _need_ref(oracle, "fixed")
+    _need_ref(oracle, "literal")
+    for path in SEARCH_FILES[:2]:
+        z, blocks, lay, c = _load_case(fixtures_mod, path)
+        for impl in ("fixed", "literal"):
+            ids, dist, cnt, _ = oracle.search(blocks, lay["block_bytes"], c["dims"], c["r"], z["queries"], c["k"],
+                                              c["L"], metric=c["metric"], vec_type=c["vec_type"],
+                                              row_ids=c["row_ids"], entry_row_id=c["entry"], cfg_l_search=c["cfg_l"],
+                                              nthreads=1, impl=impl)
+            assert np.array_equal(ids, z[impl + "_ids"]) and np.array_equal(cnt, z[impl + "_count"])
+            assert np.array_equal(_bits(dist), _bits(z[impl + "_dist"]))
