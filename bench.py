@@ -38,8 +38,8 @@ def log(*a):
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=1_000_000)
     ap.add_argument("--dims", type=int, default=128)
@@ -55,7 +55,7 @@ def parse():
     return ap.parse_args()
 
 
-L_SWEEP = [32, 48, 64, 96, 128, 192, 256]
+L_SWEEP = [32, 40, 48, 56, 64, 80, 96, 128, 192, 256]
 N_BATCHES = 4  # distinct query batches rotated through the steps
 
 
@@ -140,8 +140,10 @@ class ClockSampler:
                 "samples": len(self.rows), "power_w_max": max(float(r[2]) for r in self.rows)}
 
 
-def cpu_reference_qps(a, blocks_np, block_bytes, queries, L, seconds, nthreads=0):
-    """Times the reference's CPU search (oracle/_ref fixed build when present, else the C port) on a bounded sample."""
+def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0):
+    """Times the reference's CPU search (oracle/_ref fixed build when present, else the C port) on a bounded sample:
+    the rotated query batches, over and over, until about `seconds` of CPU work are done. Returns the ids of batch 0
+    (the parity / recall sample)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle
     kind = "reference" if pyoracle.have_ref("fixed") else "port"
@@ -149,20 +151,31 @@ def cpu_reference_qps(a, blocks_np, block_bytes, queries, L, seconds, nthreads=0
     cores = os.cpu_count() or 1
     if nthreads <= 0:
         nthreads = cores
-    probe = min(queries.shape[0], 64 * nthreads)
-    t0 = time.perf_counter()
-    pyoracle.search(blocks_np, block_bytes, a.dims, a.r, queries[:probe], a.k, L, entry_row_id=0, nthreads=nthreads,
-                    impl=impl)
-    dt = time.perf_counter() - t0
-    per_q = dt / probe
-    nsamp = int(max(probe, min(queries.shape[0], seconds / max(per_q, 1e-9))))
-    t0 = time.perf_counter()
-    ids, _, _, _ = pyoracle.search(blocks_np, block_bytes, a.dims, a.r, queries[:nsamp], a.k, L, entry_row_id=0,
-                                   nthreads=nthreads, impl=impl)
-    dt = time.perf_counter() - t0
-    return {"value": nsamp / dt, "unit": "queries/s", "cores": nthreads, "kind": kind,
-            "sample": "%d of the %d queries of batch 0 at L=%d, %d host threads, %.1f s" % (
-                nsamp, queries.shape[0], L, nthreads, dt)}, ids, nsamp
+    done, dt, ids0, i = 0, 0.0, None, 0
+    while dt < seconds:
+        q = batches[i % len(batches)]
+        t0 = time.perf_counter()
+        ids, _, _, _ = pyoracle.search(blocks_np, block_bytes, a.dims, a.r, q, a.k, L, entry_row_id=0,
+                                       nthreads=nthreads, impl=impl)
+        dt += time.perf_counter() - t0
+        done += q.shape[0]
+        if ids0 is None:
+            ids0 = ids
+        i += 1
+    return {"value": done / dt, "unit": "queries/s", "cores": nthreads, "kind": kind,
+            "sample": "%d queries (%d passes over the %d-query batches) at L=%d, %d host threads, %.1f s" % (
+                done, i, batches[0].shape[0], L, nthreads, dt)}, ids0, batches[0].shape[0]
+
+
+def profiled_traffic(a, L):
+    """DRAM bytes per traversal launch from the committed `ncu --set full` capture of this exact workload
+    (profiles/traffic.json, dram__bytes_read.sum + dram__bytes_write.sum), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        key = "n%d_d%d_r%d_%s_q%d_k%d_L%d" % (a.n, a.dims, a.r, a.kind, a.nq, a.k, L)
+        return t.get(key, {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
 
 
 def main():
@@ -316,7 +329,7 @@ def main():
     cpu = None
     parity = None
     if not a.no_cpu:
-        cpu, cpu_ids, nsamp = cpu_reference_qps(a, blocks_np, bb, batches[0], L, a.cpu_seconds)
+        cpu, cpu_ids, nsamp = cpu_reference_qps(a, blocks_np, bb, batches, L, a.cpu_seconds)
         cpu["recall_at_10"] = round(fx.recall_at_k(cpu_ids, truth[:nsamp]), 4)
         parity = float((cpu_ids == ids0[:nsamp]).all(axis=1).mean())
     total_q = a.nq * world * a.steps
@@ -334,7 +347,7 @@ def main():
                 "d2h_bytes_per_step": a.nq * a.k * 12, "ms_per_step": e2e_s * 1e3 / a.steps},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps,
+                     "traffic": profiled_traffic(a, L), "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps,
                      "algorithmic_bytes_per_launch": alg_bytes // a.steps,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
                      "E_per_query": E / (a.nq * a.steps), "V_per_query": V / (a.nq * a.steps)},
