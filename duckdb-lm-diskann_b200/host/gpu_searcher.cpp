@@ -1,0 +1,320 @@
+// See gpu_searcher.hpp. Host orchestration only: every distance, comparison and graph step happens in liblmd_b200.so.
+#include "gpu_searcher.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <iostream>
+#include <stdexcept>
+
+namespace diskann {
+namespace b200 {
+
+std::string LastError() {
+	const char *e = lmd_last_error();
+	return e ? std::string(e) : std::string();
+}
+
+namespace {
+
+// Status -> the reference's exception for the same condition (include/lmd_b200.h documents the mapping).
+[[noreturn]] void ThrowStatus(lmd_status st, const char *where) {
+	const std::string msg = std::string(where) + ": " + LastError();
+	switch (st) {
+	case LMD_ERR_INVALID_ARG:
+		throw ::duckdb::InvalidInputException(msg);
+	case LMD_ERR_UNSUPPORTED:
+		throw ::duckdb::NotImplementedException(msg);
+	case LMD_ERR_STATE:
+		throw std::runtime_error(msg);
+	default: // LMD_ERR_CUDA, LMD_ERR_OOM
+		throw ::duckdb::IOException(msg);
+	}
+}
+
+void Check(lmd_status st, const char *where) {
+	if (st != LMD_OK) {
+		ThrowStatus(st, where);
+	}
+}
+
+lmd_config ToAbiConfig(const core::LmDiskannConfig &c, common::idx_t block_bytes) {
+	lmd_config out;
+	std::memset(&out, 0, sizeof(out));
+	out.dims = static_cast<uint32_t>(c.dimensions);
+	out.r = c.r;
+	out.metric = static_cast<uint32_t>(c.metric_type);        // same numeric values, common/ann.hpp:16-24
+	out.vec_type = static_cast<uint32_t>(c.node_vector_type); // common/ann.hpp:26-32
+	out.l_search = c.l_search;
+	out.block_bytes = block_bytes;
+	return out;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+DeviceNodeStore::DeviceNodeStore(const core::LmDiskannConfig &config, common::idx_t capacity_nodes, int device,
+                                 common::idx_t block_bytes)
+    : config_(config) {
+	lmd_config cfg = ToAbiConfig(config, block_bytes);
+	Check(lmd_store_create(&cfg, device, capacity_nodes, &store_), "DeviceNodeStore");
+	lmd_layout lay;
+	Check(lmd_layout_calc(cfg.dims, cfg.vec_type, cfg.r, &lay), "DeviceNodeStore");
+	block_bytes_ = block_bytes ? block_bytes : lmd_block_bytes(lay.total_node_size);
+}
+
+DeviceNodeStore::~DeviceNodeStore() {
+	if (store_) {
+		lmd_store_destroy(store_);
+	}
+}
+
+common::idx_t DeviceNodeStore::MirrorFrom(const core::IStorageManager &storage, const core::IGraphManager &graph,
+                                          const std::vector<common::row_t> &row_ids, common::idx_t batch_nodes) {
+	if (batch_nodes == 0) {
+		batch_nodes = 1;
+	}
+	std::vector<uint8_t> stage(static_cast<size_t>(batch_nodes) * block_bytes_);
+	std::vector<common::row_t> stage_ids(batch_nodes);
+	common::idx_t filled = 0, total = 0;
+	auto flush = [&]() {
+		if (filled) {
+			Check(lmd_store_upload(store_, stage_ids.data(), stage.data(), filled), "DeviceNodeStore::MirrorFrom");
+			total += filled;
+			filled = 0;
+		}
+	};
+	for (common::row_t rid : row_ids) {
+		common::IndexPointer ptr;
+		if (!graph.TryGetNodePointer(rid, ptr)) {
+			continue;
+		}
+		common::const_data_ptr_t blk = storage.GetNodeBlockData(ptr);
+		if (!blk) {
+			continue;
+		}
+		std::memcpy(stage.data() + static_cast<size_t>(filled) * block_bytes_, blk, block_bytes_);
+		stage_ids[filled++] = rid;
+		if (filled == batch_nodes) {
+			flush();
+		}
+	}
+	flush();
+	Check(lmd_store_finalize(store_), "DeviceNodeStore::MirrorFrom");
+	return total;
+}
+
+void DeviceNodeStore::Upload(const common::row_t *row_ids, common::const_data_ptr_t blocks, common::idx_t n) {
+	Check(lmd_store_upload(store_, row_ids, blocks, n), "DeviceNodeStore::Upload");
+	Check(lmd_store_finalize(store_), "DeviceNodeStore::Upload");
+}
+
+void DeviceNodeStore::RefreshBlock(const core::IStorageManager &storage, const core::IGraphManager &graph,
+                                   common::row_t row_id) {
+	common::IndexPointer ptr;
+	if (!graph.TryGetNodePointer(row_id, ptr)) {
+		throw ::duckdb::InvalidInputException("DeviceNodeStore::RefreshBlock: unknown row id");
+	}
+	common::const_data_ptr_t blk = storage.GetNodeBlockData(ptr);
+	if (!blk) {
+		throw ::duckdb::IOException("DeviceNodeStore::RefreshBlock: GetNodeBlockData returned null");
+	}
+	Check(lmd_store_update(store_, row_id, blk), "DeviceNodeStore::RefreshBlock");
+}
+
+void DeviceNodeStore::SyncEntryPoint(const core::IGraphManager &graph) {
+	// core/Searcher.cpp:70-77: an invalid pointer or the INT64_MAX row id means "no entry point" -> empty results
+	common::IndexPointer ptr = graph.GetEntryPointPointer();
+	common::row_t rid = graph.GetEntryPointRowId();
+	if (ptr == common::IndexPointer()) {
+		rid = common::NumericLimits<common::row_t>::Maximum();
+	}
+	SetEntryPoint(rid);
+}
+
+void DeviceNodeStore::SetEntryPoint(common::row_t row_id) {
+	Check(lmd_store_set_entry(store_, row_id), "DeviceNodeStore::SetEntryPoint");
+}
+
+common::idx_t DeviceNodeStore::NodeCount() const {
+	return lmd_store_node_count(store_);
+}
+
+common::idx_t DeviceNodeStore::DeviceBytes() const {
+	return lmd_store_device_bytes(store_);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+GpuSearcher::GpuSearcher(std::shared_ptr<DeviceNodeStore> store, Route route) : store_(std::move(store)), route_(route) {
+	if (!store_) {
+		throw ::duckdb::InternalException("GpuSearcher requires a DeviceNodeStore");
+	}
+}
+
+void GpuSearcher::Search(const float *query_vector, const core::LmDiskannConfig &config,
+                         core::IGraphManager *graph_manager, common::idx_t k_neighbors,
+                         std::vector<common::row_t> &result_row_ids, common::idx_t search_list_size) {
+	result_row_ids.clear();
+	if (graph_manager) {
+		// the entry point can move between searches (first insert / deletion, core/GraphManager.cpp:119-121)
+		common::row_t rid = graph_manager->GetEntryPointRowId();
+		if (graph_manager->GetEntryPointPointer() == common::IndexPointer()) {
+			rid = common::NumericLimits<common::row_t>::Maximum();
+		}
+		if (!entry_synced_ || rid != synced_entry_) {
+			store_->SetEntryPoint(rid);
+			synced_entry_ = rid;
+			entry_synced_ = true;
+		}
+	}
+	// core/Searcher.cpp:261-265 is applied inside lmd_search_batch with the STORE's l_search; honour a differing
+	// per-call config here so that both resolve identically
+	common::idx_t L = search_list_size > 0 ? search_list_size : config.l_search;
+	if (L == 0) {
+		L = k_neighbors > 20 ? k_neighbors + 20 : 40;
+	}
+	if (k_neighbors == 0) {
+		return; // PerformSearch with k = 0 keeps nothing (core/Searcher.cpp:224-227)
+	}
+	std::vector<common::row_t> ids(k_neighbors);
+	uint32_t count = 0;
+	SearchBatch(query_vector, 1, k_neighbors, L, ids.data(), nullptr, &count, nullptr);
+	result_row_ids.assign(ids.begin(), ids.begin() + count);
+}
+
+common::idx_t GpuSearcher::GetInMemorySize() const {
+	return store_->DeviceBytes();
+}
+
+void GpuSearcher::SearchForInitialCandidates(const float *new_node_vector, common::idx_t dimensions,
+                                             const core::LmDiskannConfig &config, core::IGraphManager *graph_manager,
+                                             common::idx_t num_candidates_to_find,
+                                             common::IndexPointer current_entry_point,
+                                             std::vector<common::row_t> &candidate_row_ids_out) {
+	candidate_row_ids_out.clear();
+	if (dimensions != config.dimensions || num_candidates_to_find == 0 || current_entry_point == common::IndexPointer()) {
+		return; // core/Searcher.cpp:74-77: nothing to start from
+	}
+	// core/Searcher.cpp:281-282: L = max(config.l_insert, num_candidates_to_find)
+	Search(new_node_vector, config, graph_manager, num_candidates_to_find, candidate_row_ids_out,
+	       std::max<common::idx_t>(num_candidates_to_find, config.l_insert));
+}
+
+void GpuSearcher::SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors,
+                              common::idx_t search_list_size, common::row_t *out_ids, float *out_dist,
+                              uint32_t *out_count, lmd_stats *stats) {
+	Check(lmd_search_batch(store_->Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
+	                       static_cast<uint32_t>(search_list_size), static_cast<uint32_t>(route_), 0, out_ids, out_dist,
+	                       out_count, nullptr, stats),
+	      "GpuSearcher::Search");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+void GpuCoordinatorSearch(core::ISearcher *searcher, core::IGraphManager *graph_manager,
+                          const core::LmDiskannConfig &config, bool index_loaded, const float *query_vector,
+                          common::idx_t k_neighbors, std::vector<common::row_t> &result_row_ids,
+                          common::idx_t search_list_size) {
+	// core/Coordinator.cpp:66-74, same order and messages
+	if (!index_loaded) {
+		throw std::runtime_error("Coordinator: Error - Index not loaded for search.");
+	}
+	if (!searcher || !graph_manager) {
+		throw std::runtime_error("Coordinator: Searcher or GraphManager not initialized.");
+	}
+	if (k_neighbors == 0) {
+		throw std::runtime_error("Coordinator: k_neighbors cannot be 0 for search.");
+	}
+	result_row_ids.clear();                                                            // :77
+	common::idx_t L = search_list_size > 0 ? search_list_size : config.l_search;       // :80
+	if (L < k_neighbors) {                                                             // :81-85
+		L = k_neighbors;
+	}
+	try {
+		searcher->Search(query_vector, config, graph_manager, k_neighbors, result_row_ids, L); // :91
+	} catch (const std::exception &e) {                                                        // :97-101
+		std::cerr << "Coordinator: Error during Search: " << e.what() << std::endl;
+		result_row_ids.clear();
+		throw;
+	}
+}
+
+std::unique_ptr<GpuScanState> GpuIndexScan::InitializeScan(const float *query, common::idx_t query_dims,
+                                                           common::idx_t k) const {
+	if (!query) {
+		throw ::duckdb::BinderException("LM_DISKANN query vector must be ARRAY<FLOAT>.");
+	}
+	if (query_dims != config_.dimensions) {
+		throw ::duckdb::BinderException(::duckdb::StringUtil::Format(
+		    "Query vector dimension (%d) does not match index dimension (%d).", (int)query_dims, (int)config_.dimensions));
+	}
+	if (k == 0) {
+		throw ::duckdb::BinderException("Cannot perform index scan with k=0");
+	}
+	auto st = std::make_unique<GpuScanState>();
+	st->query_vector_storage.assign(query, query + query_dims); // db/LmDiskannScanState.cpp:9-32 copies the query
+	st->query_vector_ptr = st->query_vector_storage.data();
+	st->k = k;
+	st->l_search = config_.l_search;
+	return st;
+}
+
+common::idx_t GpuIndexScan::Scan(GpuScanState &state, common::row_t *result, common::idx_t result_capacity) {
+	if (!searcher_) {
+		throw ::duckdb::InternalException("Coordinator not initialized in Scan");
+	}
+	if (!state.query_vector_ptr) {
+		throw ::duckdb::InternalException("Query vector pointer not set in scan state");
+	}
+	common::idx_t output_count = 0;
+	try {
+		if (!state.searched) {
+			GpuCoordinatorSearch(searcher_, graph_, config_, true, state.query_vector_ptr, state.k,
+			                     state.result_row_ids, state.l_search);
+			state.searched = true;
+		}
+		const common::idx_t cap = std::min<common::idx_t>(result_capacity, STANDARD_VECTOR_SIZE);
+		output_count = std::min<common::idx_t>(cap, state.result_row_ids.size());
+		std::copy(state.result_row_ids.begin(), state.result_row_ids.begin() + output_count, result);
+		state.result_row_ids.erase(state.result_row_ids.begin(), state.result_row_ids.begin() + output_count);
+	} catch (const std::exception &e) {
+		throw ::duckdb::IOException(::duckdb::StringUtil::Format("Error during LM_DISKANN scan: %s", e.what()));
+	}
+	return output_count;
+}
+
+void GpuIndexScan::MultiScan(const float *queries, common::idx_t nq, common::idx_t query_dims, common::idx_t k,
+                             common::row_t *out_ids, uint32_t *out_count) {
+	if (query_dims != config_.dimensions) {
+		throw ::duckdb::BinderException(::duckdb::StringUtil::Format(
+		    "Query vector dimension (%d) does not match index dimension (%d).", (int)query_dims, (int)config_.dimensions));
+	}
+	if (k == 0) {
+		throw ::duckdb::BinderException("Cannot perform index scan with k=0");
+	}
+	auto *gpu = dynamic_cast<GpuSearcher *>(searcher_);
+	try {
+		if (gpu) {
+			if (graph_) {
+				gpu->Store().SyncEntryPoint(*graph_);
+			}
+			common::idx_t L = std::max<common::idx_t>(config_.l_search, k); // core/Coordinator.cpp:80-85
+			gpu->SearchBatch(queries, nq, k, L, out_ids, nullptr, out_count, nullptr);
+			return;
+		}
+		// any other ISearcher: the template's loop, one scan per row (hnsw_optimize_join.cpp:113-170)
+		std::vector<common::row_t> ids;
+		for (common::idx_t q = 0; q < nq; q++) {
+			GpuCoordinatorSearch(searcher_, graph_, config_, true, queries + q * query_dims, k, ids, config_.l_search);
+			for (common::idx_t j = 0; j < k; j++) {
+				out_ids[q * k + j] = j < ids.size() ? ids[j] : -1;
+			}
+			if (out_count) {
+				out_count[q] = static_cast<uint32_t>(std::min<common::idx_t>(ids.size(), k));
+			}
+		}
+	} catch (const std::exception &e) {
+		throw ::duckdb::IOException(::duckdb::StringUtil::Format("Error during LM_DISKANN scan: %s", e.what()));
+	}
+}
+
+} // namespace b200
+} // namespace diskann

@@ -1,0 +1,166 @@
+// Host-side adapter of the B200 LM_DISKANN query path, written against the reference's OWN interface headers
+// (paths relative to /root/reference/src/lm_diskann/):
+//
+//   GpuSearcher      : core::ISearcher              core/ISearcher.hpp:14-74   replaces core::Searcher (core/Searcher.cpp)
+//   DeviceNodeStore                                  the HBM mirror behind core/IStorageManager.hpp:156 GetNodeBlockData
+//                                                    and core/IGraphManager.hpp:86 TryGetNodePointer, fed THROUGH those
+//                                                    two interfaces (so any storage backend the reference grows works)
+//   GpuIndexScan / GpuScanState                      db/LmDiskannIndex.cpp:639-724 InitializeScan / Scan and
+//                                                    db/LmDiskannScanState.hpp:34-60, minus the DuckDB Vector types
+//   GpuCoordinatorSearch                             core/Coordinator.cpp:63-102 Search (guards + L clamp + rethrow)
+//
+// Everything below the adapter is the C ABI of include/lmd_b200.h; this file contains no CUDA and no arithmetic.
+// Error behaviour follows the reference: std::runtime_error from the coordinator guards, BinderException for a bad
+// query (dimension / k == 0), IOException wrapping anything the scan throws; a missing entry point gives an empty
+// result (core/Searcher.cpp:74-83), not an error.
+#pragma once
+
+#include "core/IGraphManager.hpp"
+#include "core/ISearcher.hpp"
+#include "core/IStorageManager.hpp"
+#include "core/index_config.hpp"
+
+#include "lmd_b200.h"
+
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace diskann {
+namespace b200 {
+
+// Thrown for any non-OK status of the C ABI that has no closer reference exception.
+std::string LastError();
+
+// ---------------------------------------------------------------------------------------------------------------
+// DeviceNodeStore: RAII owner of one lmd_store.
+// ---------------------------------------------------------------------------------------------------------------
+class DeviceNodeStore {
+public:
+	// block_bytes = 0: AlignValue<SECTOR_SIZE>(total_node_size), db/LmDiskannIndex.cpp:161-162
+	DeviceNodeStore(const core::LmDiskannConfig &config, common::idx_t capacity_nodes, int device = 0,
+	                common::idx_t block_bytes = 0);
+	~DeviceNodeStore();
+	DeviceNodeStore(const DeviceNodeStore &) = delete;
+	DeviceNodeStore &operator=(const DeviceNodeStore &) = delete;
+
+	// Streams the blocks of `row_ids` to HBM: TryGetNodePointer -> GetNodeBlockData -> pinned-staged upload, in
+	// batches of `batch_nodes` blocks. Row ids that do not resolve are skipped (the reference skips them at search
+	// time, core/Searcher.cpp:120-122). Returns the number of blocks mirrored.
+	common::idx_t MirrorFrom(const core::IStorageManager &storage, const core::IGraphManager &graph,
+	                         const std::vector<common::row_t> &row_ids, common::idx_t batch_nodes = 4096);
+	// Direct bulk load of n contiguous blocks (row_ids == nullptr: row id = position).
+	void Upload(const common::row_t *row_ids, common::const_data_ptr_t blocks, common::idx_t n);
+	// core/IStorageManager.hpp:177 MarkBlockDirty: re-mirror one block after the host changed it.
+	void RefreshBlock(const core::IStorageManager &storage, const core::IGraphManager &graph, common::row_t row_id);
+	// core/GraphManager.cpp:468-474: entry point = whatever the graph manager reports now.
+	void SyncEntryPoint(const core::IGraphManager &graph);
+	void SetEntryPoint(common::row_t row_id);
+
+	common::idx_t NodeCount() const;
+	common::idx_t DeviceBytes() const;
+	common::idx_t BlockBytes() const {
+		return block_bytes_;
+	}
+	lmd_store *Handle() const {
+		return store_;
+	}
+	const core::LmDiskannConfig &Config() const {
+		return config_;
+	}
+
+private:
+	core::LmDiskannConfig config_;
+	common::idx_t block_bytes_ = 0;
+	lmd_store *store_ = nullptr;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// GpuSearcher: drop-in for core::Searcher behind core::ISearcher.
+// ---------------------------------------------------------------------------------------------------------------
+class GpuSearcher : public core::ISearcher {
+public:
+	enum class Route : uint32_t { EXACT = LMD_ROUTE_EXACT, TERNARY = LMD_ROUTE_TERNARY };
+
+	explicit GpuSearcher(std::shared_ptr<DeviceNodeStore> store, Route route = Route::EXACT);
+
+	// core/ISearcher.hpp:30-34. `graph_manager` is used only to keep the device entry point equal to the graph's
+	// (the traversal itself reads the mirror). One query = a batch of one.
+	void Search(const float *query_vector, const core::LmDiskannConfig &config, core::IGraphManager *graph_manager,
+	            common::idx_t k_neighbors, std::vector<common::row_t> &result_row_ids,
+	            common::idx_t search_list_size = 0) override;
+
+	// core/ISearcher.hpp:43
+	common::idx_t GetInMemorySize() const override;
+
+	// core/ISearcher.hpp:68-73. The reference's implementation (core/Searcher.cpp:275-294) calls PerformSearch with
+	// final_pass = false and therefore returns nothing; this one returns the
+	// num_candidates_to_find closest nodes, which is what GraphManager::AddNode expects to receive.
+	void SearchForInitialCandidates(const float *new_node_vector, common::idx_t dimensions,
+	                                const core::LmDiskannConfig &config, core::IGraphManager *graph_manager,
+	                                common::idx_t num_candidates_to_find, common::IndexPointer current_entry_point,
+	                                std::vector<common::row_t> &candidate_row_ids_out) override;
+
+	// The batched entry core/ISearcher.hpp:36-37 anticipates. queries [nq][dims]; out_ids [nq][k] (-1 padded),
+	// out_dist [nq][k] (may be null), out_count [nq] (may be null). Host or device pointers (all on one side).
+	void SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors, common::idx_t search_list_size,
+	                 common::row_t *out_ids, float *out_dist, uint32_t *out_count, lmd_stats *stats = nullptr);
+
+	DeviceNodeStore &Store() {
+		return *store_;
+	}
+
+private:
+	std::shared_ptr<DeviceNodeStore> store_;
+	Route route_;
+	common::row_t synced_entry_ = 0;
+	bool entry_synced_ = false;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// Callers, DuckDB types replaced by plain pointers.
+// ---------------------------------------------------------------------------------------------------------------
+// core/Coordinator.cpp:63-102
+void GpuCoordinatorSearch(core::ISearcher *searcher, core::IGraphManager *graph_manager,
+                          const core::LmDiskannConfig &config, bool index_loaded, const float *query_vector,
+                          common::idx_t k_neighbors, std::vector<common::row_t> &result_row_ids,
+                          common::idx_t search_list_size);
+
+// db/LmDiskannScanState.hpp:34-60
+struct GpuScanState {
+	std::vector<float> query_vector_storage;
+	const float *query_vector_ptr = nullptr;
+	common::idx_t k = 0;
+	common::idx_t l_search = 0;
+	std::vector<common::row_t> result_row_ids;
+	bool searched = false; // the reference re-runs the search on every Scan call (db/LmDiskannIndex.cpp:695); one
+	                       // search per scan state returns the same rows for k <= STANDARD_VECTOR_SIZE and pages
+	                       // correctly beyond it
+};
+
+class GpuIndexScan {
+public:
+	static constexpr common::idx_t STANDARD_VECTOR_SIZE = 2048; // DuckDB v1.2.x
+
+	GpuIndexScan(core::ISearcher *searcher, core::IGraphManager *graph_manager, const core::LmDiskannConfig &config)
+	    : searcher_(searcher), graph_(graph_manager), config_(config) {
+	}
+	// db/LmDiskannIndex.cpp:639-667: BinderException on dimension mismatch or k == 0
+	std::unique_ptr<GpuScanState> InitializeScan(const float *query, common::idx_t query_dims, common::idx_t k) const;
+	// db/LmDiskannIndex.cpp:677-724: up to STANDARD_VECTOR_SIZE row ids per call, 0 when drained; errors rewrapped
+	// as IOException("Error during LM_DISKANN scan: ...")
+	common::idx_t Scan(GpuScanState &state, common::row_t *result, common::idx_t result_capacity = STANDARD_VECTOR_SIZE);
+	// Batch form of the template's index join (hnsw_optimize_join.cpp:113-170): nq scans with the same k in one
+	// device launch; out [nq][k], -1 padded.
+	void MultiScan(const float *queries, common::idx_t nq, common::idx_t query_dims, common::idx_t k,
+	               common::row_t *out_ids, uint32_t *out_count);
+
+private:
+	core::ISearcher *searcher_;
+	core::IGraphManager *graph_;
+	core::LmDiskannConfig config_;
+};
+
+} // namespace b200
+} // namespace diskann

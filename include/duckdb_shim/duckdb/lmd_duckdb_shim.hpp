@@ -1,9 +1,11 @@
-// TEST INFRASTRUCTURE ONLY (oracle/). Not part of the product path.
+// BUILD-TIME STAND-IN, not product code: with real DuckDB v1.2.x headers on the include path this directory is
+// simply left out. Used by oracle/Makefile (the reference's own sources) and by duckdb-lm-diskann_b200/host/Makefile
+// (the host adapter written against the reference's interface headers).
 //
 // Minimal stand-in for the handful of DuckDB v1.2.x declarations that the reference's hot-path
 // sources (core/Searcher.cpp, core/index_config.cpp, core/GraphNode.cpp, core/distance.hpp,
 // common/ann.hpp, common/duckdb_types.hpp) name. DuckDB itself is absent from this image
-// (SURVEY.md §0.4), so the reference sources are compiled against this shim by oracle/Makefile.
+// (SURVEY.md §0.4), so those sources are compiled against this shim.
 // Nothing here is copied from DuckDB; each item is the smallest declaration with the same meaning.
 #pragma once
 

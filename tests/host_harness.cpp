@@ -1,0 +1,318 @@
+// TEST CODE. C entry points (for ctypes) that drive the product's host adapter
+// (duckdb-lm-diskann_b200/host/gpu_searcher.{hpp,cpp}) the way the reference drives core::Searcher: through
+// core::ISearcher / core::IStorageManager / core::IGraphManager objects. The reference ships no working
+// implementation of the latter two (StorageManager.cpp:294-348 throws, GraphManager needs AddNode), so this file
+// provides small in-memory ones over a caller-supplied array of node blocks - the "mock for testing" that
+// store/IShadowStorageService.hpp:13-16 anticipates. Built by duckdb-lm-diskann_b200/host/Makefile.
+#include "gpu_searcher.hpp"
+
+#include "core/GraphNode.hpp"
+
+#include <cstring>
+#include <memory>
+#include <string>
+#include <unordered_map>
+
+using namespace diskann;
+
+namespace {
+
+thread_local std::string g_err;
+thread_local int g_err_type = 0; // 0 none, 1 std::runtime_error, 2 Binder, 3 IO, 4 InvalidInput, 5 NotImplemented, 6 other
+
+class MemStorage : public core::IStorageManager {
+public:
+	MemStorage(const uint8_t *blocks, uint64_t n, uint64_t bb) : data_(blocks, blocks + n * bb), n_(n), bb_(bb) {
+	}
+	common::const_data_ptr_t GetNodeBlockData(common::IndexPointer p) const override {
+		uint64_t v = p.Get();
+		return (v == 0 || v > n_) ? nullptr : data_.data() + (v - 1) * bb_;
+	}
+	common::data_ptr_t GetMutableNodeBlockData(common::IndexPointer p) override {
+		uint64_t v = p.Get();
+		return (v == 0 || v > n_) ? nullptr : data_.data() + (v - 1) * bb_;
+	}
+	void LoadIndexContents(const std::string &, core::LmDiskannConfig &, core::IGraphManager *, common::IndexPointer &,
+	                       common::row_t &, common::IndexPointer &) override {
+	}
+	void InitializeNewStorage(const std::string &, const core::LmDiskannConfig &) override {
+	}
+	void SaveIndexContents(const std::string &, const core::LmDiskannConfig &, const core::IGraphManager *,
+	                       common::IndexPointer, common::row_t, common::IndexPointer) override {
+	}
+	common::idx_t GetInMemorySize() const override {
+		return data_.size();
+	}
+	void EnqueueDeletion(common::row_t, common::IndexPointer &) override {
+	}
+	void ProcessDeletionQueue(common::IndexPointer &) override {
+	}
+	bool AllocateNodeBlock(common::row_t, common::IndexPointer &, common::data_ptr_t &) override {
+		return false;
+	}
+	void MarkBlockDirty(common::IndexPointer) override {
+	}
+
+private:
+	std::vector<uint8_t> data_;
+	uint64_t n_, bb_;
+};
+
+class MemGraph : public core::IGraphManager {
+public:
+	MemGraph(const MemStorage *st, const core::NodeLayoutOffsets &lay, const int64_t *row_ids, uint64_t n, int64_t entry)
+	    : st_(st), lay_(lay), n_(n) {
+		for (uint64_t i = 0; i < n; i++) {
+			map_[row_ids ? row_ids[i] : (int64_t)i] = i + 1;
+		}
+		SetEntryByRow(entry);
+	}
+	void SetEntryByRow(int64_t entry) {
+		entry_row_ = entry;
+		if (!TryGetNodePointer(entry, entry_ptr_)) {
+			entry_row_ = common::NumericLimits<common::row_t>::Maximum();
+			entry_ptr_ = common::IndexPointer();
+		}
+	}
+	bool TryGetNodePointer(common::row_t r, common::IndexPointer &out) const override {
+		auto it = map_.find(r);
+		if (it == map_.end()) {
+			out = common::IndexPointer();
+			return false;
+		}
+		out = common::IndexPointer(it->second);
+		return true;
+	}
+	bool GetNeighbors(common::IndexPointer p, std::vector<common::row_t> &out) const override {
+		out.clear();
+		common::const_data_ptr_t blk = st_->GetNodeBlockData(p);
+		if (!blk) {
+			return false;
+		}
+		uint16_t count = core::GraphNode::GetNeighborCount(blk, lay_);
+		const common::row_t *ids = core::GraphNode::GetNeighborIDsPtr(blk, lay_);
+		for (uint16_t i = 0; i < count; i++) {
+			if (ids[i] != common::NumericLimits<common::row_t>::Maximum()) {
+				out.push_back(ids[i]);
+			}
+		}
+		return true;
+	}
+	common::IndexPointer GetEntryPointPointer() const override {
+		return entry_ptr_;
+	}
+	common::row_t GetEntryPointRowId() const override {
+		return entry_row_;
+	}
+	void InitializeEmptyGraph(const core::LmDiskannConfig &, common::IndexPointer &, common::row_t &) override {
+	}
+	bool AddNode(common::row_t, const float *, common::idx_t, common::IndexPointer &) override {
+		return false;
+	}
+	bool GetNodeVector(common::IndexPointer, float *, common::idx_t) const override {
+		return false;
+	}
+	void RobustPrune(common::IndexPointer, const float *, std::vector<common::row_t> &,
+	                 const core::LmDiskannConfig &) override {
+	}
+	void SetEntryPoint(common::IndexPointer p, common::row_t r) override {
+		entry_ptr_ = p;
+		entry_row_ = r;
+	}
+	common::row_t SelectEntryPointForSearch(common::RandomEngine &) override {
+		return entry_row_;
+	}
+	void HandleNodeDeletion(common::row_t) override {
+	}
+	void FreeNode(common::row_t) override {
+	}
+	common::idx_t GetNodeCount() const override {
+		return n_;
+	}
+	common::idx_t GetInMemorySize() const override {
+		return 0;
+	}
+	void Reset() override {
+	}
+
+private:
+	const MemStorage *st_;
+	core::NodeLayoutOffsets lay_;
+	uint64_t n_;
+	int64_t entry_row_ = 0;
+	common::IndexPointer entry_ptr_;
+	std::unordered_map<int64_t, uint64_t> map_;
+};
+
+struct Host {
+	core::LmDiskannConfig cfg;
+	std::unique_ptr<MemStorage> storage;
+	std::unique_ptr<MemGraph> graph;
+	std::shared_ptr<b200::DeviceNodeStore> store;
+	std::unique_ptr<core::ISearcher> searcher; // held through the reference's interface, as Coordinator.hpp:115-118 does
+	std::unique_ptr<b200::GpuIndexScan> scan;
+	bool loaded = true;
+};
+
+template <typename F>
+int Guard(F &&f) {
+	g_err.clear();
+	g_err_type = 0;
+	try {
+		f();
+		return 0;
+	} catch (const ::duckdb::BinderException &e) {
+		g_err_type = 2;
+		g_err = e.what();
+	} catch (const ::duckdb::IOException &e) {
+		g_err_type = 3;
+		g_err = e.what();
+	} catch (const ::duckdb::InvalidInputException &e) {
+		g_err_type = 4;
+		g_err = e.what();
+	} catch (const ::duckdb::NotImplementedException &e) {
+		g_err_type = 5;
+		g_err = e.what();
+	} catch (const ::duckdb::Exception &e) {
+		g_err_type = 6;
+		g_err = e.what();
+	} catch (const std::runtime_error &e) {
+		g_err_type = 1;
+		g_err = e.what();
+	} catch (const std::exception &e) {
+		g_err_type = 6;
+		g_err = e.what();
+	}
+	return g_err_type;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *lmdhost_last_error() {
+	return g_err.c_str();
+}
+
+// Builds: in-memory IStorageManager + IGraphManager over `blocks`, a DeviceNodeStore mirrored THROUGH those two
+// interfaces (batches of `mirror_batch` blocks), a GpuSearcher behind core::ISearcher, and the scan mirror.
+void *lmdhost_create(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const int64_t *row_ids, int64_t entry_row,
+                     int metric, int vec_type, uint64_t dims, uint32_t r, uint32_t l_search, int route,
+                     uint64_t mirror_batch, int device) {
+	Host *h = nullptr;
+	int rc = Guard([&]() {
+		auto host = std::make_unique<Host>();
+		host->cfg.metric_type = static_cast<common::LmDiskannMetricType>(metric);
+		host->cfg.node_vector_type = static_cast<common::LmDiskannVectorType>(vec_type);
+		host->cfg.dimensions = dims;
+		host->cfg.r = r;
+		host->cfg.l_search = l_search;
+		core::NodeLayoutOffsets lay = core::CalculateLayoutInternal(host->cfg);
+		host->storage = std::make_unique<MemStorage>(blocks, n, block_bytes);
+		host->graph = std::make_unique<MemGraph>(host->storage.get(), lay, row_ids, n, entry_row);
+		host->store = std::make_shared<b200::DeviceNodeStore>(host->cfg, n ? n : 1, device, block_bytes);
+		std::vector<common::row_t> all(n);
+		for (uint64_t i = 0; i < n; i++) {
+			all[i] = row_ids ? row_ids[i] : (int64_t)i;
+		}
+		host->store->MirrorFrom(*host->storage, *host->graph, all, mirror_batch ? mirror_batch : 4096);
+		host->store->SyncEntryPoint(*host->graph);
+		host->searcher = std::make_unique<b200::GpuSearcher>(
+		    host->store, route ? b200::GpuSearcher::Route::TERNARY : b200::GpuSearcher::Route::EXACT);
+		host->scan = std::make_unique<b200::GpuIndexScan>(host->searcher.get(), host->graph.get(), host->cfg);
+		h = host.release();
+	});
+	return rc == 0 ? h : nullptr;
+}
+
+void lmdhost_destroy(void *p) {
+	delete static_cast<Host *>(p);
+}
+
+uint64_t lmdhost_in_memory_size(void *p) {
+	return static_cast<Host *>(p)->searcher->GetInMemorySize();
+}
+
+void lmdhost_set_loaded(void *p, int loaded) {
+	static_cast<Host *>(p)->loaded = loaded != 0;
+}
+
+void lmdhost_set_entry(void *p, int64_t entry_row) {
+	static_cast<Host *>(p)->graph->SetEntryByRow(entry_row);
+}
+
+// core::ISearcher::Search through the virtual interface, one query. Returns the error class (0 = ok).
+int lmdhost_isearcher_search(void *p, const float *query, uint64_t k, uint64_t L, int64_t *out_ids, uint64_t *out_n) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		std::vector<common::row_t> res;
+		h->searcher->Search(query, h->cfg, h->graph.get(), k, res, L);
+		*out_n = res.size();
+		std::copy(res.begin(), res.end(), out_ids);
+	});
+}
+
+// Coordinator::Search mirror (guards + clamp), one query.
+int lmdhost_coordinator_search(void *p, const float *query, uint64_t k, uint64_t L, int64_t *out_ids, uint64_t *out_n) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		std::vector<common::row_t> res;
+		b200::GpuCoordinatorSearch(h->searcher.get(), h->graph.get(), h->cfg, h->loaded, query, k, res, L);
+		*out_n = res.size();
+		std::copy(res.begin(), res.end(), out_ids);
+	});
+}
+
+// InitializeScan + Scan until drained; `calls` receives the number of Scan calls that returned rows.
+int lmdhost_scan_all(void *p, const float *query, uint64_t query_dims, uint64_t k, int64_t *out_ids, uint64_t *out_n,
+                     uint64_t *calls) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		auto st = h->scan->InitializeScan(query, query_dims, k);
+		uint64_t total = 0, ncalls = 0;
+		for (;;) {
+			common::idx_t got = h->scan->Scan(*st, out_ids + total);
+			if (got == 0) {
+				break;
+			}
+			total += got;
+			ncalls++;
+		}
+		*out_n = total;
+		*calls = ncalls;
+	});
+}
+
+int lmdhost_multi_scan(void *p, const float *queries, uint64_t nq, uint64_t query_dims, uint64_t k, int64_t *out_ids,
+                       uint32_t *out_count) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() { h->scan->MultiScan(queries, nq, query_dims, k, out_ids, out_count); });
+}
+
+int lmdhost_initial_candidates(void *p, const float *vec, uint64_t dims, uint64_t want, int64_t *out_ids,
+                               uint64_t *out_n) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		std::vector<common::row_t> res;
+		h->searcher->SearchForInitialCandidates(vec, dims, h->cfg, h->graph.get(), want,
+		                                        h->graph->GetEntryPointPointer(), res);
+		*out_n = res.size();
+		std::copy(res.begin(), res.end(), out_ids);
+	});
+}
+
+// MarkBlockDirty path: overwrite one block on the host side, refresh its mirror.
+int lmdhost_rewrite_block(void *p, int64_t row_id, const uint8_t *block, uint64_t block_bytes) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		common::IndexPointer ptr;
+		if (!h->graph->TryGetNodePointer(row_id, ptr)) {
+			throw ::duckdb::InvalidInputException("unknown row id");
+		}
+		std::memcpy(h->storage->GetMutableNodeBlockData(ptr), block, block_bytes);
+		h->storage->MarkBlockDirty(ptr);
+		h->store->RefreshBlock(*h->storage, *h->graph, row_id);
+	});
+}
+
+} // extern "C"

@@ -1,0 +1,253 @@
+"""The C++ host adapter (duckdb-lm-diskann_b200/host/: GpuSearcher : core::ISearcher, DeviceNodeStore fed through
+core::IStorageManager / core::IGraphManager, Coordinator::Search and InitializeScan / Scan mirrors), driven through
+tests/host_harness.cpp the way the reference drives core::Searcher, and checked against the CPU oracle.
+
+The harness and the adapter are compiled against the reference's own interface headers by
+duckdb-lm-diskann_b200/host/Makefile (in the container that has /root/reference; the .so files travel)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from parity import check_parity
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST_DIR = os.path.join(ROOT, "duckdb-lm-diskann_b200", "host", "_build")
+HARNESS = os.path.join(HOST_DIR, "liblmd_host_harness.so")
+P = C.c_void_p
+ERR = {0: None, 1: "runtime_error", 2: "BinderException", 3: "IOException", 4: "InvalidInputException",
+       5: "NotImplementedException", 6: "other"}
+METRIC = {"L2": 1, "COSINE": 2, "IP": 3}
+
+
+def _lib():
+    if not os.path.exists(HARNESS):
+        pytest.fail("%s is missing: run `make -C duckdb-lm-diskann_b200/host` (done by __graft_entry__.build())" % HARNESS)
+    l = C.CDLL(HARNESS)
+    l.lmdhost_last_error.restype = C.c_char_p
+    l.lmdhost_create.restype = P
+    l.lmdhost_create.argtypes = [P, C.c_uint64, C.c_uint64, P, C.c_int64, C.c_int, C.c_int, C.c_uint64, C.c_uint32,
+                                 C.c_uint32, C.c_int, C.c_uint64, C.c_int]
+    l.lmdhost_destroy.argtypes = [P]
+    l.lmdhost_in_memory_size.restype = C.c_uint64
+    l.lmdhost_in_memory_size.argtypes = [P]
+    l.lmdhost_set_loaded.argtypes = [P, C.c_int]
+    l.lmdhost_set_entry.argtypes = [P, C.c_int64]
+    for name in ("lmdhost_isearcher_search", "lmdhost_coordinator_search"):
+        getattr(l, name).argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
+    l.lmdhost_scan_all.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P, P]
+    l.lmdhost_multi_scan.argtypes = [P, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P]
+    l.lmdhost_initial_candidates.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
+    l.lmdhost_rewrite_block.argtypes = [P, C.c_int64, P, C.c_uint64]
+    return l
+
+
+class Host:
+    def __init__(self, lib, blocks, bb, dims, r, metric=1, vec_type=1, row_ids=None, entry=0, l_search=100, route=0,
+                 mirror_batch=257):
+        self.lib = lib
+        self.blocks = np.ascontiguousarray(blocks)
+        n = self.blocks.size // bb
+        rid = None if row_ids is None else np.ascontiguousarray(row_ids, dtype=np.int64)
+        self.h = lib.lmdhost_create(self.blocks.ctypes.data, n, bb, None if rid is None else rid.ctypes.data, entry,
+                                    metric, vec_type, dims, r, l_search, route, mirror_batch, 0)
+        if not self.h:
+            raise RuntimeError("lmdhost_create: " + lib.lmdhost_last_error().decode())
+
+    def close(self):
+        if self.h:
+            self.lib.lmdhost_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _one(self, fn, q, k, L):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        out = np.full(max(k, 1), -1, dtype=np.int64)
+        n = C.c_uint64(0)
+        rc = fn(self.h, q.ctypes.data, k, L, out.ctypes.data, C.addressof(n))
+        return ERR[rc], out[:n.value].copy(), self.lib.lmdhost_last_error().decode()
+
+    def isearcher_search(self, q, k, L=0):
+        return self._one(self.lib.lmdhost_isearcher_search, q, k, L)
+
+    def coordinator_search(self, q, k, L=0):
+        return self._one(self.lib.lmdhost_coordinator_search, q, k, L)
+
+    def scan_all(self, q, k, dims=None):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        out = np.full(max(k, 1) + 8, -1, dtype=np.int64)
+        n, calls = C.c_uint64(0), C.c_uint64(0)
+        rc = self.lib.lmdhost_scan_all(self.h, q.ctypes.data, q.size if dims is None else dims, k, out.ctypes.data,
+                                       C.addressof(n), C.addressof(calls))
+        return ERR[rc], out[:n.value].copy(), calls.value, self.lib.lmdhost_last_error().decode()
+
+    def multi_scan(self, q, k):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        out = np.full((q.shape[0], k), -1, dtype=np.int64)
+        cnt = np.zeros(q.shape[0], dtype=np.uint32)
+        rc = self.lib.lmdhost_multi_scan(self.h, q.ctypes.data, q.shape[0], q.shape[1], k, out.ctypes.data,
+                                         cnt.ctypes.data)
+        return ERR[rc], out, cnt, self.lib.lmdhost_last_error().decode()
+
+
+# ---- CPU: the adapter libraries exist, load, and export the harness entry points ----------------------------
+def test_host_libraries_load():
+    l = _lib()
+    for name in ("lmdhost_create", "lmdhost_isearcher_search", "lmdhost_coordinator_search", "lmdhost_scan_all",
+                 "lmdhost_multi_scan", "lmdhost_initial_candidates", "lmdhost_rewrite_block"):
+        assert hasattr(l, name)
+    # the adapter itself exports the reference-facing classes
+    import subprocess
+    syms = subprocess.run(["nm", "-DC", os.path.join(HOST_DIR, "liblmd_host.so")], capture_output=True, text=True).stdout
+    for s in ("diskann::b200::GpuSearcher::Search(", "diskann::b200::GpuSearcher::SearchBatch(",
+              "diskann::b200::DeviceNodeStore::MirrorFrom(", "diskann::b200::GpuIndexScan::Scan(",
+              "diskann::b200::GpuCoordinatorSearch("):
+        assert s in syms, s
+    assert "typeinfo for diskann::core::ISearcher" in syms  # GpuSearcher derives from the reference's interface
+
+
+def test_no_device_is_an_error_not_a_fallback(fixtures_mod):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without a GPU")
+    ix = fixtures_mod.build_index(300, 16, 8, device="cpu")
+    with pytest.raises(RuntimeError) as e:
+        Host(_lib(), ix["blocks"].numpy(), ix["layout"]["block_bytes"], 16, 8)
+    assert "cuda" in str(e.value).lower() or "device" in str(e.value).lower()
+
+
+# ---- GPU: behaviour through the reference's interfaces -------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric,dims,r,sparse_ids", [("L2", 128, 32, False), ("COSINE", 96, 16, True),
+                                                       ("IP", 100, 24, True)])
+def test_isearcher_search_matches_oracle(oracle, make_index, fixtures_mod, metric, dims, r, sparse_ids):
+    n, k, L = 2000, 10, 48
+    row_ids = None
+    if sparse_ids:
+        row_ids = np.random.default_rng(5).choice(np.arange(3, 40 * n, dtype=np.int64), size=n, replace=False)
+    ix = make_index(n, dims, r, metric=metric, kind="iid", nq=24, row_ids=row_ids)
+    entry = 0 if row_ids is None else int(row_ids[0])
+    o_ids, o_dist, o_cnt, _ = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, ix["queries"], k, L,
+                                            metric=METRIC[metric], row_ids=row_ids, entry_row_id=entry)
+    with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, metric=METRIC[metric], row_ids=row_ids,
+              entry=entry) as h:
+        assert h.lib.lmdhost_in_memory_size(h.h) >= n * ix["block_bytes"]  # ISearcher::GetInMemorySize
+        for qi, q in enumerate(ix["queries"]):
+            err, ids, _ = h.isearcher_search(q, k, L)
+            assert err is None
+            assert len(ids) == int(o_cnt[qi])
+            same = ids == o_ids[qi, :len(ids)]
+            if not same.all():  # only inside a distance tie
+                j = int(np.argmin(same))
+                assert abs(o_dist[qi, j] - o_dist[qi, min(j + 1, k - 1)]) <= 1e-5 * abs(o_dist[qi, j]) + 1e-12
+        # the batch entry returns the same rows as nq single searches
+        err, mids, mcnt, _ = h.multi_scan(ix["queries"], k)
+        assert err is None
+
+
+@pytest.mark.gpu
+def test_coordinator_guards_and_l_clamp(oracle, make_index):
+    dims, r = 128, 32
+    ix = make_index(2000, dims, r, metric="L2", kind="clustered", nq=8)
+    q = ix["queries"][0]
+    with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, l_search=30) as h:
+        err, _, msg = h.coordinator_search(q, 0)
+        assert err == "runtime_error" and "k_neighbors cannot be 0" in msg  # core/Coordinator.cpp:72-74
+        h.lib.lmdhost_set_loaded(h.h, 0)
+        err, _, msg = h.coordinator_search(q, 5)
+        assert err == "runtime_error" and "Index not loaded" in msg        # :66-68
+        h.lib.lmdhost_set_loaded(h.h, 1)
+        # L = 0 -> cfg.l_search = 30; k = 50 > L -> L clamped up to k (:80-85)
+        for k, L, l_eff in ((10, 0, 30), (50, 0, 50), (10, 64, 64)):
+            err, ids, _ = h.coordinator_search(q, k, L)
+            o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q[None, :], k, l_eff, entry_row_id=0)
+            assert err is None and np.array_equal(ids, o[0][0, :int(o[2][0])])
+        # entry point gone (deleted, core/GraphManager.cpp) -> empty result, no error (core/Searcher.cpp:74-77)
+        h.lib.lmdhost_set_entry(h.h, 987654321)
+        err, ids, _ = h.coordinator_search(q, 10)
+        assert err is None and len(ids) == 0
+        h.lib.lmdhost_set_entry(h.h, 7)
+        err, ids, _ = h.coordinator_search(q, 10)
+        o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q[None, :], 10, 30, entry_row_id=7)
+        assert err is None and np.array_equal(ids, o[0][0, :int(o[2][0])])
+
+
+@pytest.mark.gpu
+def test_scan_paging_and_binder_errors(oracle, make_index):
+    dims, r = 96, 32
+    ix = make_index(3000, dims, r, metric="L2", kind="clustered", nq=4)
+    q = ix["queries"][1]
+    with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, l_search=64) as h:
+        err, ids, calls, _ = h.scan_all(q, 10)
+        o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q[None, :], 10, 64, entry_row_id=0)
+        assert err is None and calls == 1 and np.array_equal(ids, o[0][0])
+        # k beyond STANDARD_VECTOR_SIZE pages over several Scan calls (db/LmDiskannIndex.cpp:699-713)
+        big_k = 2500
+        with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, l_search=64) as h2:
+            err, ids, calls, msg = h2.scan_all(q, big_k)
+            # L is clamped to k = 2500 > this build's list limit (512): the scan reports it as the reference
+            # reports any search failure, an IOException naming the scan (db/LmDiskannIndex.cpp:718-721)
+            assert err == "IOException" and "Error during LM_DISKANN scan" in msg
+        err, ids, calls, _ = h.scan_all(q, 400)
+        o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q[None, :], 400, 400, entry_row_id=0)
+        assert err is None and calls == 1 and np.array_equal(ids, o[0][0, :int(o[2][0])])
+        # db/LmDiskannIndex.cpp:651-658
+        err, _, _, msg = h.scan_all(q[:50], 10)
+        assert err == "BinderException" and "does not match index dimension" in msg
+        err, _, _, msg = h.scan_all(q, 0)
+        assert err == "BinderException" and "k=0" in msg
+
+
+@pytest.mark.gpu
+def test_multi_scan_equals_single_scans(oracle, make_index):
+    dims, r, k = 128, 32, 10
+    ix = make_index(3000, dims, r, metric="L2", kind="clustered", nq=96)
+    o_ids, o_dist, o_cnt, _ = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, ix["queries"], k, 100,
+                                            entry_row_id=0)
+    with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, l_search=100) as h:
+        err, ids, cnt, _ = h.multi_scan(ix["queries"], k)
+        assert err is None
+        assert np.array_equal(cnt, o_cnt)
+        assert (ids == o_ids).all(axis=1).mean() >= 0.98
+        for qi in (0, 17, 95):
+            err, one, _, _ = h.scan_all(ix["queries"][qi], k)
+            assert np.array_equal(one, ids[qi, :len(one)])
+
+
+@pytest.mark.gpu
+def test_mark_block_dirty_refreshes_the_mirror(oracle, make_index, fixtures_mod):
+    dims, r = 64, 16
+    ix = make_index(1500, dims, r, metric="L2", kind="iid", nq=16)
+    lay = ix["layout"]
+    blocks = ix["blocks_np"].copy()
+    with Host(_lib(), blocks, ix["block_bytes"], dims, r, l_search=40) as h:
+        # move node 0 (the entry point) far away and cut its edges down to one
+        b = blocks[0].copy()
+        vec = b[lay["vector_off"]:lay["vector_off"] + 4 * dims].view(np.float32)
+        vec[:] = 50.0
+        b[0:2] = np.array([1], dtype=np.uint16).view(np.uint8)
+        assert h.lib.lmdhost_rewrite_block(h.h, 0, b.ctypes.data, b.size) == 0
+        blocks[0] = b
+        o = oracle.search(blocks, ix["block_bytes"], dims, r, ix["queries"], 10, 40, entry_row_id=0)
+        err, ids, cnt, _ = h.multi_scan(ix["queries"], 10)
+        assert err is None and np.array_equal(cnt, o[2]) and np.array_equal(ids, o[0])
+
+
+@pytest.mark.gpu
+def test_search_for_initial_candidates(oracle, make_index):
+    dims, r = 128, 32
+    ix = make_index(2000, dims, r, metric="L2", kind="clustered", nq=4)
+    with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r) as h:
+        q = np.ascontiguousarray(ix["queries"][2])
+        out = np.full(64, -1, dtype=np.int64)
+        n = C.c_uint64(0)
+        assert h.lib.lmdhost_initial_candidates(h.h, q.ctypes.data, dims, 40, out.ctypes.data, C.addressof(n)) == 0
+        # L = max(l_insert = 128, 40) (core/Searcher.cpp:281-282); the 40 closest of that list
+        o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q[None, :], 40, 128, entry_row_id=0)
+        assert n.value == 40 and np.array_equal(out[:40], o[0][0])
