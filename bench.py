@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--L", type=int, default=0, help="0 = smallest L of the sweep reaching the recall target")
     ap.add_argument("--recall", type=float, default=0.95)
     ap.add_argument("--kind", default="clustered")
+    ap.add_argument("--metric", default="L2", choices=["L2", "COSINE", "IP"])
+    ap.add_argument("--route", default="exact", choices=["exact", "ternary"],
+                    help="ternary = LM-DiskANN compressed-neighbour routing + exact rerank (COSINE / IP only)")
     ap.add_argument("--sweep", action="store_true", help="also print the whole L sweep (stderr)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
@@ -62,14 +65,14 @@ N_BATCHES = 4  # distinct query batches rotated through the steps
 def load_or_build_index(a, fx, device):
     """x [n, dims] f32, nbrs [n, r] (slots, -1 empty), counts. Cached on local disk so that the reference arm and
     the other ranks of the same box reuse the graph (graph provenance is free: parity is same graph, same queries)."""
-    tag = "n%d_d%d_r%d_%s_v2" % (a.n, a.dims, a.r, a.kind)
+    tag = "n%d_d%d_r%d_%s%s_v2" % (a.n, a.dims, a.r, a.kind, "" if a.metric == "L2" else "_" + a.metric)
     path = os.path.join(CACHE, tag + ".npz")
     if os.path.exists(path):
         z = np.load(path)
         log("index cache hit", path)
         return z["x"], z["nbrs"].astype(np.int64), z["counts"].astype(np.int64)
     t0 = time.time()
-    x = fx.make_dataset(a.n, a.dims, kind=a.kind, seed=42)
+    x = fx.make_dataset(a.n, a.dims, kind=a.kind, seed=42, normalize=(a.metric == "COSINE"))
     nbrs, counts = fx.build_graph(x, a.r, device=device, log=log)
     nbrs, counts = nbrs.numpy(), counts.numpy()
     log("graph built in %.1f s" % (time.time() - t0))
@@ -84,11 +87,12 @@ def load_or_build_index(a, fx, device):
 
 
 def load_or_build_truth(a, fx, x, queries, device):
-    tag = "truth_n%d_d%d_%s_q%d_k%d_v2" % (a.n, a.dims, a.kind, queries.shape[0], a.k)
+    tag = "truth_n%d_d%d_%s%s_q%d_k%d_v2" % (a.n, a.dims, a.kind, "" if a.metric == "L2" else "_" + a.metric,
+                                             queries.shape[0], a.k)
     path = os.path.join(CACHE, tag + ".npy")
     if os.path.exists(path):
         return np.load(path)
-    t = fx.brute_force_topk(x, queries, a.k, "L2", device=device)
+    t = fx.brute_force_topk(x, queries, a.k, a.metric, device=device)
     try:
         os.makedirs(CACHE, exist_ok=True)
         np.save(path + ".%d.tmp.npy" % os.getpid(), t)
@@ -146,8 +150,9 @@ def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0
     (the parity / recall sample)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle
-    kind = "reference" if pyoracle.have_ref("fixed") else "port"
-    impl = "fixed" if kind == "reference" else "port"
+    kind = "reference" if pyoracle.have_ref("fixed") and a.route == "exact" else "port"
+    impl = "fixed" if kind == "reference" else "port"  # the reference never executes ternary routing
+    metric = {"L2": 1, "COSINE": 2, "IP": 3}[a.metric]
     cores = os.cpu_count() or 1
     if nthreads <= 0:
         nthreads = cores
@@ -155,8 +160,8 @@ def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0
     while dt < seconds:
         q = batches[i % len(batches)]
         t0 = time.perf_counter()
-        ids, _, _, _ = pyoracle.search(blocks_np, block_bytes, a.dims, a.r, q, a.k, L, entry_row_id=0,
-                                       nthreads=nthreads, impl=impl)
+        ids, _, _, _ = pyoracle.search(blocks_np, block_bytes, a.dims, a.r, q, a.k, L, metric=metric, entry_row_id=0,
+                                       route=1 if a.route == "ternary" else 0, nthreads=nthreads, impl=impl)
         dt += time.perf_counter() - t0
         done += q.shape[0]
         if ids0 is None:
@@ -208,10 +213,11 @@ def main():
             x, nbrs, counts = load_or_build_index(a, fx, dev)
     lay = fx.layout(a.dims, a.r)
     bb = lay["block_bytes"]
-    batches = [fx.make_dataset(a.nq, a.dims, kind=a.kind, seed=43 + 1000 * rank + 17 * b) for b in range(N_BATCHES)]
+    batches = [fx.make_dataset(a.nq, a.dims, kind=a.kind, seed=43 + 1000 * rank + 17 * b,
+                               normalize=(a.metric == "COSINE")) for b in range(N_BATCHES)]
     truth = load_or_build_truth(a, fx, x, batches[0], dev) if rank == 0 else None
-    workload = "synthetic %dx%d float32 L2 (%s, seed 42), R=%d, %d-query batch per GPU, k=%d" % (
-        a.n, a.dims, a.kind, a.r, a.nq, a.k)
+    workload = "synthetic %dx%d float32 %s (%s, seed 42), R=%d, %d-query batch per GPU, k=%d" % (
+        a.n, a.dims, a.metric, a.kind, a.r, a.nq, a.k)
 
     if a.impl == "reference":
         return run_reference(a, fx, x, nbrs, counts, batches, truth, workload, bb)
@@ -219,7 +225,8 @@ def main():
     lmd = importlib.import_module("duckdb-lm-diskann_b200")
     t0 = time.time()
     blocks_dev = fx.pack_blocks(x, nbrs, counts, a.r, device=dev)  # node blocks, reference layout, built in HBM
-    store = lmd.Store(a.dims, a.r, metric=lmd.METRIC_L2, capacity=a.n, device=local, l_search=100)
+    store = lmd.Store(a.dims, a.r, metric=lmd.METRIC_BY_NAME[a.metric], capacity=a.n, device=local, l_search=100)
+    route = lmd.ROUTE_TERNARY if a.route == "ternary" else lmd.ROUTE_EXACT
     store.upload(blocks_dev)
     store.set_entry(0)
     store.finalize()
@@ -235,8 +242,8 @@ def main():
     L = a.L
     if rank == 0 and (a.L == 0 or a.sweep):
         for l in L_SWEEP:
-            store.search(batches[1], a.k, l)  # warm-up launch of this L's kernel variant
-            ids, _, _, st = store.search(batches[0], a.k, l)
+            store.search(batches[1], a.k, l, route=route)  # warm-up launch of this L's kernel variant
+            ids, _, _, st = store.search(batches[0], a.k, l, route=route)
             rec = fx.recall_at_k(ids, truth)
             gbps = st.algorithmic_bytes / (st.traverse_ms * 1e-3) / 1e9
             sweep.append({"L": l, "recall": round(rec, 4), "traverse_ms": round(st.traverse_ms, 4),
@@ -272,23 +279,25 @@ def main():
         torch.cuda.synchronize()
 
     for i in range(a.warmup):
-        store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, flags=lmd.SEARCH_ASYNC, out_ids=d_ids, out_dist=d_dist,
+        store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_ids, out_dist=d_dist,
                          out_count=d_cnt)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
         e0.record(stream)
         for i in range(a.steps):
-            store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, flags=lmd.SEARCH_ASYNC, out_ids=d_ids, out_dist=d_dist,
+            store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_ids, out_dist=d_dist,
                              out_count=d_cnt)
         e1.record(stream)
         barrier()
         dev_ms = e0.elapsed_time(e1)
         # per-kernel numbers for the roofline: same batches, synchronous calls with statistics
-        kern_ms, alg_bytes, launches, E, V = 0.0, 0, 0, 0, 0
+        kern_ms, rerank_ms, alg_bytes, launches, E, V = 0.0, 0.0, 0, 0, 0, 0
         for i in range(a.steps):
-            st = store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, out_ids=d_ids, out_dist=d_dist, out_count=d_cnt)
+            st = store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=d_ids, out_dist=d_dist,
+                                  out_count=d_cnt)
             kern_ms += st.traverse_ms
+            rerank_ms += st.rerank_ms
             alg_bytes += st.algorithmic_bytes
             launches += st.launches
             E += st.expansions
@@ -299,11 +308,11 @@ def main():
         h_ids = torch.empty((a.nq, a.k), dtype=torch.int64).pin_memory()
         h_dist = torch.empty((a.nq, a.k), dtype=torch.float32).pin_memory()
         for i in range(max(a.warmup, 3)):
-            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, out_ids=h_ids, out_dist=h_dist)
+            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist)
         barrier()
         t0 = time.perf_counter()
         for i in range(a.steps):
-            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, out_ids=h_ids, out_dist=h_dist)
+            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist)
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
     if dist_on:
@@ -317,7 +326,7 @@ def main():
         return 0
 
     # ---- rank 0: recall at the chosen L, CPU baseline, report ------------------------------------------------------
-    ids0, dist0, cnt0, st0 = store.search(batches[0], a.k, L)
+    ids0, dist0, cnt0, st0 = store.search(batches[0], a.k, L, route=route)
     recall = fx.recall_at_k(ids0, truth)
     peaks = {}
     try:
@@ -338,7 +347,7 @@ def main():
         "value": total_q / (dev_ms * 1e-3), "unit": "queries/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": dev_ms / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload, "L": L, "recall_at_10": round(recall, 4), "route": "exact",
+        "config": {"workload": workload, "L": L, "recall_at_10": round(recall, 4), "route": a.route,
                    "entry": "slot 0", "query_batches_rotated": N_BATCHES,
                    "l2_note": "node store %.1f GB >> 126 MB L2; every step gathers ~%.1f GB of it" % (
                        store.device_bytes / 1e9, alg_bytes / a.steps / 1e9),
@@ -347,7 +356,7 @@ def main():
                 "d2h_bytes_per_step": a.nq * a.k * 12, "ms_per_step": e2e_s * 1e3 / a.steps},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": profiled_traffic(a, L), "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps,
+                     "traffic": profiled_traffic(a, L), "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps, "rerank_kernel_ms": rerank_ms / a.steps,
                      "algorithmic_bytes_per_launch": alg_bytes // a.steps,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
                      "E_per_query": E / (a.nq * a.steps), "V_per_query": V / (a.nq * a.steps)},
@@ -373,30 +382,33 @@ def run_reference(a, fx, x, nbrs, counts, batches, truth, workload, bb):
     blocks_np = fx.pack_blocks(x, nbrs, counts, a.r, device="cpu").numpy()
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle
-    impl = "fixed" if pyoracle.have_ref("fixed") else "port"
+    impl = "fixed" if pyoracle.have_ref("fixed") and a.route == "exact" else "port"
+    metric = {"L2": 1, "COSINE": 2, "IP": 3}[a.metric]
+
+    def S(q, l):
+        return pyoracle.search(blocks_np, bb, a.dims, a.r, q, a.k, l, metric=metric, entry_row_id=0,
+                               route=1 if a.route == "ternary" else 0, impl=impl)
     cores = os.cpu_count() or 1
     if L == 0:  # same rule as our arm: smallest L of the sweep with recall >= target (on a 1000-query sample)
         for l in L_SWEEP:
-            ids, _, _, _ = pyoracle.search(blocks_np, bb, a.dims, a.r, batches[0][:1000], a.k, l, entry_row_id=0,
-                                           impl=impl)
+            ids, _, _, _ = S(batches[0][:1000], l)
             if fx.recall_at_k(ids, truth[:1000]) >= a.recall:
                 L = l
                 break
         L = L or L_SWEEP[-1]
     # size the per-step sample so that warmup + steps stay within a few minutes
     t0 = time.perf_counter()
-    pyoracle.search(blocks_np, bb, a.dims, a.r, batches[0][:512], a.k, L, entry_row_id=0, impl=impl)
+    S(batches[0][:512], L)
     per_q = (time.perf_counter() - t0) / 512
     budget = 120.0 / max(1, a.steps + a.warmup)
     nsamp = int(max(256, min(a.nq, budget / per_q)))
     for i in range(a.warmup):
-        pyoracle.search(blocks_np, bb, a.dims, a.r, batches[i % N_BATCHES][:nsamp], a.k, L, entry_row_id=0, impl=impl)
+        S(batches[i % N_BATCHES][:nsamp], L)
     t0 = time.perf_counter()
     for i in range(a.steps):
-        ids, _, _, _ = pyoracle.search(blocks_np, bb, a.dims, a.r, batches[i % N_BATCHES][:nsamp], a.k, L,
-                                       entry_row_id=0, impl=impl)
+        ids, _, _, _ = S(batches[i % N_BATCHES][:nsamp], L)
     dt = time.perf_counter() - t0
-    ids, _, _, _ = pyoracle.search(blocks_np, bb, a.dims, a.r, batches[0][:nsamp], a.k, L, entry_row_id=0, impl=impl)
+    ids, _, _, _ = S(batches[0][:nsamp], L)
     qps = nsamp * a.steps / dt
     sample = "%d-query sample of each 10k batch, L=%d, %d host threads" % (nsamp, L, cores)
     out = {
@@ -406,7 +418,7 @@ def run_reference(a, fx, x, nbrs, counts, batches, truth, workload, bb):
         "ms_per_step": dt * 1e3 / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload, "L": L, "recall_at_10": round(fx.recall_at_k(ids, truth[:nsamp]), 4),
-                   "route": "exact", "entry": "slot 0", "sample": sample,
+                   "route": a.route, "entry": "slot 0", "sample": sample,
                    "code": "reference core/Searcher.cpp + oracle/patches/searcher_fixed.patch (oracle/_ref)"
                    if impl == "fixed" else "oracle/lmd_oracle.c port"},
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores,

@@ -70,7 +70,8 @@ __host__ __device__ __forceinline__ float key_dist(uint64_t k) {
 
 // ---- the store ---------------------------------------------------------------------------------
 struct Tuning {
-	int filter_log2 = 0;   // 0 = heuristic
+	int filter_log2 = 0;   // log2(entries of the visited filter), 0 = heuristic
+	int filter_mode = -1;  // -1 = auto (1 when the store is small enough), 0 = u32 open addressing, 1 = 16-bit buckets
 	int warps_per_cta = 4;
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
 	int tie_slots = -1;    // -1 = default (64 for ternary routing, 0 for exact)

@@ -42,7 +42,10 @@ struct KParams {
 	uint32_t nq, dims, row_floats, r, words;
 	uint32_t L, k, metric, list_cap, merge_min;
 	uint32_t entry_slot, has_entry;
-	uint32_t filter_mask, filter_shift;
+	uint32_t filter_mask, filter_shift; // filter_mode 0: slots - 1, 32 - log2(slots)
+	uint32_t filter_mode;               // 0 = u32 open addressing, 1 = two-choice buckets of 8 x 16-bit entries
+	uint32_t filter_bmask, filter_hmask; // mode 1: buckets - 1, 2^(log2(buckets) + 15) - 1
+	uint32_t filter_bytes;              // bytes of the table (either mode)
 	uint32_t warp_smem_bytes;
 };
 
@@ -227,13 +230,15 @@ __device__ __forceinline__ float finish_batch(const float *s_a, const float *s_b
 }
 
 // Pulls the m rows that compute_batch() is about to read into L2, every 128-byte line of every row at once, so that
-// the passes of compute_batch() wait for L2 instead of one HBM round trip each.
+// the passes of compute_batch() wait for L2 instead of one HBM round trip each. LPR = 128-byte lines per row when the
+// shape is specialised (0 = read it from the parameters).
+template <int LPR>
 __device__ __forceinline__ void prefetch_rows(const KParams &p, const uint32_t *s_nb, int m, int lane) {
-	const uint32_t lines_per_row = p.row_floats / 32; // row_floats is a multiple of 32 floats = 128 bytes
+	const uint32_t lines_per_row = LPR > 0 ? (uint32_t)LPR : p.row_floats / 32; // row_floats is a multiple of 32 floats
 	const uint32_t total = (uint32_t)m * lines_per_row;
 	for (uint32_t t = lane; t < total; t += 32) {
 		const uint32_t j = t / lines_per_row, l = t - j * lines_per_row;
-		const float *a = p.vecs + (uint64_t)s_nb[j] * p.row_floats + l * 32;
+		const float *a = p.vecs + (uint64_t)s_nb[j] * (LPR > 0 ? (uint32_t)LPR * 32u : p.row_floats) + l * 32;
 		asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
 	}
 }
@@ -257,6 +262,96 @@ __device__ __forceinline__ bool filter_test_and_set(uint32_t *tab, uint32_t mask
 	tab[home] = id; // window full: forget whoever lived at the home slot
 	evictions++;
 	return true;
+}
+
+// ---- visited filter, mode 1: two-choice buckets of eight 16-bit entries -----------------------------------------
+// Same contract as filter_test_and_set() at half the bytes per remembered node and a much higher usable load.
+// slot -> h = xorshift(slot * odd mod 2^m), m = log2(buckets) + 15: a BIJECTION on [0, 2^m), so (home bucket =
+// h >> 15, tag = h & 0x7FFF) identifies the node exactly for every store with fewer than 2^m nodes (the host checks).
+// An entry is (tag << 1 | c): c = 0 in the node's home bucket, c = 1 in its alternate bucket home ^ x(tag); a node
+// goes to the alternate bucket only when its home bucket is full, and buckets never lose entries except by being
+// overwritten while full, so "home has a free entry" proves the node is absent. Entry 0 = free; nodes whose tag is 0
+// (1 in 32768) are simply never remembered. When both buckets are full one entry of the home bucket is forgotten -
+// which, as in mode 0, can only cost a re-evaluation.
+__device__ __forceinline__ bool has16(uint4 v, uint32_t e) {
+	const uint32_t t = e * 0x10001u;
+	return (__vcmpeq2(v.x, t) | __vcmpeq2(v.y, t) | __vcmpeq2(v.z, t) | __vcmpeq2(v.w, t)) != 0u;
+}
+__device__ __forceinline__ int first_free16(uint4 v, uint32_t &word) {
+	uint32_t z;
+	if ((z = __vcmpeq2(v.x, 0u)) != 0u) {
+		word = v.x;
+		return (z & 0xFFFFu) ? 0 : 1;
+	}
+	if ((z = __vcmpeq2(v.y, 0u)) != 0u) {
+		word = v.y;
+		return (z & 0xFFFFu) ? 2 : 3;
+	}
+	if ((z = __vcmpeq2(v.z, 0u)) != 0u) {
+		word = v.z;
+		return (z & 0xFFFFu) ? 4 : 5;
+	}
+	if ((z = __vcmpeq2(v.w, 0u)) != 0u) {
+		word = v.w;
+		return (z & 0xFFFFu) ? 6 : 7;
+	}
+	return -1;
+}
+__device__ __forceinline__ uint4 lds_bucket(const uint32_t *tab, uint32_t b) {
+	uint4 v;
+	const uint32_t a = (uint32_t)__cvta_generic_to_shared(tab + b * 4);
+	asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+	return v;
+}
+__device__ __forceinline__ bool bucket_test_and_set(uint32_t *tab, uint32_t bmask, uint32_t hmask, uint32_t id,
+                                                    uint32_t &evictions) {
+	uint32_t h = (id * 0x9E3779B1u) & hmask;
+	h ^= h >> 15;
+	const uint32_t tag = h & 0x7FFFu;
+	if (tag == 0u) {
+		return true;
+	}
+	const uint32_t home = h >> 15;
+	uint32_t x = (tag * 0x2545u) & bmask;
+	x = x ? x : 1u;
+	const uint32_t alt = home ^ x;
+	const uint32_t e0 = tag << 1, e1 = e0 | 1u;
+#pragma unroll 1
+	for (int attempt = 0; attempt < 12; attempt++) {
+		const uint4 v = lds_bucket(tab, home);
+		if (has16(v, e0)) {
+			return false;
+		}
+		uint32_t old, entry = e0, bucket = home;
+		int way = first_free16(v, old);
+		if (way < 0) {
+			const uint4 u = lds_bucket(tab, alt);
+			if (has16(u, e1)) {
+				return false;
+			}
+			way = first_free16(u, old);
+			if (way < 0) {
+				reinterpret_cast<uint16_t *>(tab + home * 4)[(id + evictions) & 7u] = (uint16_t)e0;
+				evictions++;
+				return true;
+			}
+			entry = e1;
+			bucket = alt;
+		}
+		uint32_t *w = tab + bucket * 4 + (way >> 1);
+		if (atomicCAS(w, old, old | (entry << ((way & 1) * 16))) == old) {
+			return true;
+		}
+	}
+	evictions++; // pathological contention inside one bucket: evaluate the node without remembering it
+	return true;
+}
+
+__device__ __forceinline__ bool visited_test_and_set(const KParams &p, uint32_t *tab, uint32_t id, uint32_t &evictions) {
+	if (p.filter_mode) {
+		return bucket_test_and_set(tab, p.filter_bmask, p.filter_hmask, id, evictions);
+	}
+	return filter_test_and_set(tab, p.filter_mask, p.filter_shift, id, evictions);
 }
 
 // Sorted insert of one key (warp-uniform) into s_list[0..n). The list holds the top-L entries in [0, L) and, behind
@@ -489,7 +584,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 	uint64_t *s_bk = reinterpret_cast<uint64_t *>(s_nb); // the sorted batch of list_merge_batch() reuses s_nb + s_d
 	float *s_d2 = s_d + 32;
 	uint32_t *s_filter = reinterpret_cast<uint32_t *>(s_d2 + 32);
-	uint8_t *extra = reinterpret_cast<uint8_t *>(s_filter + p.filter_mask + 1);
+	uint8_t *extra = reinterpret_cast<uint8_t *>(s_filter) + p.filter_bytes;
 	float *s_q = reinterpret_cast<float *>(extra); // generic shape only
 	uint32_t *s_qp = reinterpret_cast<uint32_t *>(extra + (CH == 0 ? p.row_floats * 4 : 0));
 	uint32_t *s_qn = s_qp + p.words * 2;
@@ -509,9 +604,10 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		uint32_t n_exp = 0, n_eval = 0, n_evict = 0, n_tie_ovf = 0, n_fallback = 0;
 		int n = 0;
 		{
-			uint4 e4 = make_uint4(FILTER_EMPTY, FILTER_EMPTY, FILTER_EMPTY, FILTER_EMPTY);
+			const uint32_t fill = p.filter_mode ? 0u : FILTER_EMPTY;
+			uint4 e4 = make_uint4(fill, fill, fill, fill);
 			uint4 *f4 = reinterpret_cast<uint4 *>(s_filter);
-			for (uint32_t i = lane; i < (p.filter_mask + 1) / 4; i += 32) {
+			for (uint32_t i = lane; i < p.filter_bytes / 16; i += 32) {
 				f4[i] = e4;
 			}
 		}
@@ -525,7 +621,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		if (p.has_entry) { // core/Searcher.cpp:70-103
 			if (lane == 0) {
 				s_nb[0] = p.entry_slot;
-				filter_test_and_set(s_filter, p.filter_mask, p.filter_shift, p.entry_slot, n_evict);
+				visited_test_and_set(p, s_filter, p.entry_slot, n_evict);
 			}
 			__syncwarp();
 			compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, 1, lane);
@@ -571,7 +667,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				}
 				bool isnew = false;
 				if (id != LMD_INVALID_SLOT) {
-					isnew = filter_test_and_set(s_filter, p.filter_mask, p.filter_shift, id, n_evict);
+					isnew = visited_test_and_set(p, s_filter, id, n_evict);
 				}
 				const uint32_t mask = __ballot_sync(FULL, isnew);
 				const int m = __popc(mask);
@@ -588,7 +684,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 						s_nb[pos] = id;
 					}
 					__syncwarp();
-					prefetch_rows(p, s_nb, m, lane);
+					prefetch_rows<(CH > 0 ? CH * TEAM / 8 : 0)>(p, s_nb, m, lane);
 					compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, m, lane);
 					__syncwarp();
 					have = lane < m;
@@ -717,7 +813,7 @@ __global__ void __launch_bounds__(128) rerank_kernel(const KParams p) {
 				s_nb[lane] = key_slot(ck);
 			}
 			__syncwarp();
-			prefetch_rows(p, s_nb, m, lane);
+			prefetch_rows<(CH > 0 ? CH * TEAM / 8 : 0)>(p, s_nb, m, lane);
 			compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, m, lane);
 			__syncwarp();
 			const float dd = finish_batch<METRIC>(s_d, s_d2, Q.na, m, lane);

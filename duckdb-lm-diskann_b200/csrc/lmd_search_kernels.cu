@@ -92,22 +92,43 @@ static int lpl_for(uint32_t L) {
 	return L <= 32 ? 1 : L <= 64 ? 2 : L <= 96 ? 3 : L <= 128 ? 4 : L <= 192 ? 6 : L <= 256 ? 8 : L <= 384 ? 12 : L <= 512 ? 16 : 0;
 }
 
-// visited-filter size: room for the nodes a search is expected to discover, shrunk until at least 16 warps
-// fit on an SM (the gathers need that many warps in flight far more than they need a perfect filter)
-static uint32_t pick_filter_log2(const lmd_store *s, uint32_t L, size_t fixed_bytes) {
-	if (s->tune.filter_log2 >= 6 && s->tune.filter_log2 <= 15) {
-		return (uint32_t)s->tune.filter_log2;
+// Visited-filter sizing. `lg` = log2(entries). Mode 1 (two-choice buckets of 8 x 16-bit entries, 2 bytes per entry) is
+// used whenever the store is small enough for its exact (bucket, tag) identification, i.e. nodes < 2^(lg - 3 + 15);
+// mode 0 (u32 open addressing, 4 bytes per entry) otherwise. The table is sized for the nodes a search is expected to
+// discover (about 0.8 R new neighbours per expansion, ~1.05 L expansions) at a load of 0.7 (mode 1) / 0.45 (mode 0), then
+// shrunk until at least `min_warps` warps fit on an SM: the gathers need warps in flight more than a perfect filter.
+struct FilterPlan {
+	uint32_t mode, lg, bytes;
+};
+static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes) {
+	FilterPlan f;
+	const double expect = 0.8 * (double)s->cfg.r * 1.05 * (double)L;
+	int mode = s->tune.filter_mode;
+	if (mode != 0 && mode != 1) {
+		mode = 1;
 	}
-	double expect = 0.6 * 1.3 * (double)L * (double)s->cfg.r * 1.5;
-	uint32_t lg = 8;
-	while (lg < 14 && (double)(1u << lg) < expect) {
-		lg++;
+	auto fits_exact = [&](uint32_t lg) { return lg >= 4 && (uint64_t)s->n < (1ull << (lg - 3 + 15)); };
+	uint32_t lg;
+	if (s->tune.filter_log2 >= 6 && s->tune.filter_log2 <= 16) {
+		lg = (uint32_t)s->tune.filter_log2;
+	} else {
+		const double load = mode == 1 ? 0.7 : 0.45;
+		lg = 9;
+		while (lg < 15 && (double)(1u << lg) * load < expect) {
+			lg++;
+		}
+		const size_t budget = (size_t)227 * 1024 / 16;
+		while (lg > 9 && fixed_bytes + ((size_t)(mode == 1 ? 2 : 4) << lg) > budget) {
+			lg--;
+		}
 	}
-	const size_t budget = (size_t)227 * 1024 / 16;
-	while (lg > 8 && fixed_bytes + ((size_t)4 << lg) > budget) {
-		lg--;
+	if (mode == 1 && !fits_exact(lg)) {
+		mode = 0;
 	}
-	return lg;
+	f.mode = (uint32_t)mode;
+	f.lg = lg;
+	f.bytes = (uint32_t)((mode == 1 ? 2u : 4u) << lg);
+	return f;
 }
 
 static lmd_status dispatch_traverse(KParams &p, const lmd_store *s, uint32_t nq, int lpl, uint32_t route,
@@ -170,10 +191,14 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	const bool generic = !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	size_t fixed = (size_t)lpl * 32 * 8 + 384 + (generic ? (size_t)p.row_floats * 4 : 0) +
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0);
-	uint32_t lg = pick_filter_log2(s, a.L, fixed);
-	p.filter_mask = (1u << lg) - 1;
-	p.filter_shift = 32 - lg;
-	p.warp_smem_bytes = (uint32_t)((fixed + ((size_t)4 << lg) + 15) / 16 * 16);
+	const FilterPlan fp = pick_filter(s, a.L, fixed);
+	p.filter_mode = fp.mode;
+	p.filter_bytes = fp.bytes;
+	p.filter_mask = (1u << fp.lg) - 1;
+	p.filter_shift = 32 - fp.lg;
+	p.filter_bmask = (1u << (fp.lg - 3)) - 1;
+	p.filter_hmask = (uint32_t)((1ull << (fp.lg - 3 + 15)) - 1);
+	p.warp_smem_bytes = (uint32_t)((fixed + fp.bytes + 15) / 16 * 16);
 	return dispatch_traverse(p, s, a.nq, lpl, a.route, st);
 }
 

@@ -602,6 +602,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 	std::string k(key);
 	if (k == "filter_log2") {
 		s->tune.filter_log2 = (int)value;
+	} else if (k == "filter_mode") {
+		s->tune.filter_mode = (int)value;
 	} else if (k == "warps_per_cta") {
 		s->tune.warps_per_cta = (int)value;
 	} else if (k == "ctas_per_sm") {
