@@ -146,9 +146,12 @@ class Store:
         self.device = device
 
     def close(self):
-        if self._h:
-            lib().lmd_store_destroy(self._h)
-            self._h = _P()
+        try:
+            if self._h:
+                lib().lmd_store_destroy(self._h)
+                self._h = _P()
+        except TypeError:  # interpreter shutdown: module globals are already gone
+            pass
 
     __del__ = close
 

@@ -23,6 +23,7 @@ void set_error(const char *fmt, ...);
 	do {                                                                                                               \
 		cudaError_t _e = (expr);                                                                                       \
 		if (_e != cudaSuccess) {                                                                                       \
+			cudaGetLastError(); /* a non-sticky error must not be reported again by the next call */                  \
 			lmd::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__);                \
 			return (_e == cudaErrorMemoryAllocation) ? LMD_ERR_OOM : LMD_ERR_CUDA;                                     \
 		}                                                                                                              \
@@ -72,9 +73,10 @@ __host__ __device__ __forceinline__ float key_dist(uint64_t k) {
 struct Tuning {
 	int filter_log2 = 0;   // log2(entries of the visited filter), 0 = heuristic
 	int filter_mode = -1;  // -1 = auto (1 when the store is small enough), 0 = u32 open addressing, 1 = 16-bit buckets
-	int warps_per_cta = 4;
+	int warps_per_cta = 0; // 0 = whichever of 4 / 2 / 1 packs the most warps on an SM
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
 	int tie_slots = -1;    // -1 = default (64 for ternary routing, 0 for exact)
+	int prefetch_planes = 1; // ternary routing: prefetch the plane region of the likely next expansion into L2
 	int merge_min = 0;     // batch-merge new candidates when at least this many pass the threshold (0 = default 5)
 };
 

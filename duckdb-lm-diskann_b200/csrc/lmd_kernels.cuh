@@ -24,6 +24,8 @@
 #pragma once
 #include "lmd_common.cuh"
 
+#include <algorithm>
+
 namespace lmd {
 
 struct KParams {
@@ -46,6 +48,7 @@ struct KParams {
 	uint32_t filter_mode;               // 0 = u32 open addressing, 1 = two-choice buckets of 8 x 16-bit entries
 	uint32_t filter_bmask, filter_hmask; // mode 1: buckets - 1, 2^(log2(buckets) + 15) - 1
 	uint32_t filter_bytes;              // bytes of the table (either mode)
+	uint32_t prefetch_planes;           // ternary routing: also prefetch the runner-up's plane region
 	uint32_t warp_smem_bytes;
 };
 
@@ -365,29 +368,36 @@ __device__ __forceinline__ bool visited_test_and_set(const KParams &p, uint32_t 
 template <int LPL>
 __device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, int cap, uint64_t key, int lane,
                                            uint32_t &overflow) {
-	uint64_t e[LPL];
+	// pass 1 (reads only): insert position and duplicate test
 	int pos = 0;
 	bool dup = false;
 	const uint64_t k1 = key >> 1;
 #pragma unroll
 	for (int c = 0; c < LPL; c++) {
-		int i = c * 32 + lane;
-		e[c] = i < n ? s_list[i] : LMD_KEY_NONE;
-		uint64_t e1 = e[c] >> 1;
-		pos += __popc(__ballot_sync(FULL, e1 < k1));
-		dup |= __any_sync(FULL, e1 == k1);
+		if (c * 32 < n) {
+			const int i = c * 32 + lane;
+			const uint64_t e1 = (i < n ? s_list[i] : LMD_KEY_NONE) >> 1;
+			pos += __popc(__ballot_sync(FULL, e1 < k1));
+			dup |= __any_sync(FULL, e1 == k1);
+		}
 	}
 	if (dup || pos >= cap) {
 		return n;
 	}
-	__syncwarp();
 	// entry that falls off the end of the array (only when n == cap)
 	const uint64_t last = n == cap ? s_list[cap - 1] : LMD_KEY_NONE;
+	__syncwarp();
+	// pass 2: shift [pos, n) right by one, top chunk first so that one chunk at a time lives in registers
 #pragma unroll
-	for (int c = 0; c < LPL; c++) {
-		int i = c * 32 + lane;
-		if (i < n && i >= pos && i + 1 < cap) {
-			s_list[i + 1] = e[c];
+	for (int c = LPL - 1; c >= 0; c--) {
+		if (c * 32 < n && (c + 1) * 32 > pos) {
+			const int i = c * 32 + lane;
+			const uint64_t e = i < n ? s_list[i] : LMD_KEY_NONE;
+			__syncwarp();
+			if (i < n && i >= pos && i + 1 < cap) {
+				s_list[i + 1] = e;
+			}
+			__syncwarp();
 		}
 	}
 	if (lane == 0) {
@@ -401,9 +411,11 @@ __device__ __forceinline__ int list_insert(uint64_t *s_list, int n, int L, int c
 		int keep = L;
 #pragma unroll
 		for (int c = 0; c < LPL; c++) {
-			int i = c * 32 + lane;
-			bool tie = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
-			keep += __popc(__ballot_sync(FULL, tie));
+			if ((c + 1) * 32 > L && c * 32 < nn) {
+				const int i = c * 32 + lane;
+				const bool tie = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
+				keep += __popc(__ballot_sync(FULL, tie));
+			}
 		}
 		if (last != LMD_KEY_NONE && keep == cap && (uint32_t)(last >> 32) == wd && !(last & 1ull)) {
 			overflow++;
@@ -441,31 +453,7 @@ __device__ __forceinline__ int list_merge_batch(uint64_t *s_list, uint64_t *s_bk
 	constexpr int CAPP2 = LPL <= 1 ? 32 : LPL <= 2 ? 64 : LPL <= 4 ? 128 : LPL <= 8 ? 256 : 512;
 	s_bk[lane] = bkey;
 	__syncwarp();
-	// list entries: how many batch keys sort before each
-	uint64_t e[LPL];
-	int shift_by[LPL];
-#pragma unroll
-	for (int c = 0; c < LPL; c++) {
-		const int i = c * 32 + lane;
-		e[c] = LMD_KEY_NONE;
-		shift_by[c] = 0;
-		if (c * 32 < n) {
-			e[c] = i < n ? s_list[i] : LMD_KEY_NONE;
-			const uint64_t e1 = e[c] >> 1;
-			int lo = 0;
-#pragma unroll
-			for (int step = 16; step > 0; step >>= 1) {
-				if ((s_bk[lo + step - 1] >> 1) < e1) {
-					lo += step;
-				}
-			}
-			if ((s_bk[lo] >> 1) < e1) {
-				lo++;
-			}
-			shift_by[c] = lo;
-		}
-	}
-	// batch keys: how many list entries sort before each
+	// batch keys: how many list entries sort before each (reads only), and the tie test
 	const uint64_t b1 = bkey >> 1;
 	const uint32_t bhi = (uint32_t)(bkey >> 32);
 	int lo = 0;
@@ -489,12 +477,35 @@ __device__ __forceinline__ int list_merge_batch(uint64_t *s_list, uint64_t *s_bk
 		fallback = true;
 		return n;
 	}
-	__syncwarp(); // every read of the old list is done
+	__syncwarp(); // every read of the old list by the batch side is done
+	// list entries, top chunk first: each moves up by the number of batch keys that sort before it (<= 32), so a chunk
+	// only ever writes into itself and the chunk above, whose entries have already moved. One chunk in registers.
+	uint64_t e_push = LMD_KEY_NONE; // the entry of this lane pushed past `cap` (top chunk only: cap is a multiple of 32)
 #pragma unroll
-	for (int c = 0; c < LPL; c++) {
-		const int i = c * 32 + lane;
-		if (i < n && i + shift_by[c] < cap) {
-			s_list[i + shift_by[c]] = e[c];
+	for (int c = LPL - 1; c >= 0; c--) {
+		if (c * 32 < n) {
+			const int i = c * 32 + lane;
+			const uint64_t e = i < n ? s_list[i] : LMD_KEY_NONE;
+			const uint64_t e1 = e >> 1;
+			int sh = 0;
+#pragma unroll
+			for (int step = 16; step > 0; step >>= 1) {
+				if ((s_bk[sh + step - 1] >> 1) < e1) {
+					sh += step;
+				}
+			}
+			if ((s_bk[sh] >> 1) < e1) {
+				sh++;
+			}
+			__syncwarp();
+			if (i < n) {
+				if (i + sh < cap) {
+					s_list[i + sh] = e;
+				} else {
+					e_push = e;
+				}
+			}
+			__syncwarp();
 		}
 	}
 	if (lane < cnt && lane + lo < cap) {
@@ -507,14 +518,15 @@ __device__ __forceinline__ int list_merge_batch(uint64_t *s_list, uint64_t *s_bk
 		// as overflow
 		const uint32_t wd = (uint32_t)(s_list[L - 1] >> 32);
 		int keep = L;
-		bool lost = false;
 #pragma unroll
 		for (int c = 0; c < LPL; c++) {
-			const int i = c * 32 + lane;
-			const bool tie_kept = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
-			keep += __popc(__ballot_sync(FULL, tie_kept));
-			lost |= i < n && i + shift_by[c] >= cap && (uint32_t)(e[c] >> 32) == wd && !(e[c] & 1ull);
+			if ((c + 1) * 32 > L && c * 32 < nn) {
+				const int i = c * 32 + lane;
+				const bool tie_kept = i >= L && i < nn && (uint32_t)(s_list[i] >> 32) == wd;
+				keep += __popc(__ballot_sync(FULL, tie_kept));
+			}
 		}
+		const bool lost = e_push != LMD_KEY_NONE && (uint32_t)(e_push >> 32) == wd && !(e_push & 1ull);
 		overflow += __popc(__ballot_sync(FULL, lost));
 		nn = keep;
 	}
@@ -556,17 +568,36 @@ __device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t q
 	__syncwarp();
 }
 
-// core/ternary_quantization.hpp:269-296 (Dot_scalar) + core/distance.hpp:229-235 for neighbour j of block `blk`
+// core/ternary_quantization.hpp:269-296 (Dot_scalar) + core/distance.hpp:229-235 for neighbour j of block `blk`.
+// WORDS = u64 words per plane when the shape is specialised (every load of the neighbour's two planes is issued before
+// the first popcount), 0 = read it from the parameters.
+template <int WORDS>
 __device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_t *blk, uint32_t j,
                                                   const uint32_t *s_qp, const uint32_t *s_qn) {
-	const uint2 *vp = reinterpret_cast<const uint2 *>(blk + p.pos_off) + (uint64_t)j * p.words;
-	const uint2 *vn = reinterpret_cast<const uint2 *>(blk + p.neg_off) + (uint64_t)j * p.words;
+	const uint32_t words = WORDS > 0 ? (uint32_t)WORDS : p.words;
+	const uint2 *vp = reinterpret_cast<const uint2 *>(blk + p.pos_off) + (uint64_t)j * words;
+	const uint2 *vn = reinterpret_cast<const uint2 *>(blk + p.neg_off) + (uint64_t)j * words;
 	int score = 0;
-	for (uint32_t w = 0; w < p.words; w++) {
-		uint2 a = __ldg(vp + w), b = __ldg(vn + w);
-		uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
-		score += __popc(qp0 & a.x) + __popc(qp1 & a.y) + __popc(qn0 & b.x) + __popc(qn1 & b.y);
-		score -= __popc(qp0 & b.x) + __popc(qp1 & b.y) + __popc(qn0 & a.x) + __popc(qn1 & a.y);
+	if (WORDS > 0) {
+		uint2 a[WORDS > 0 ? WORDS : 1], b[WORDS > 0 ? WORDS : 1];
+#pragma unroll
+		for (int w = 0; w < WORDS; w++) {
+			a[w] = __ldg(vp + w);
+			b[w] = __ldg(vn + w);
+		}
+#pragma unroll
+		for (int w = 0; w < WORDS; w++) {
+			const uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
+			score += __popc(qp0 & a[w].x) + __popc(qp1 & a[w].y) + __popc(qn0 & b[w].x) + __popc(qn1 & b[w].y);
+			score -= __popc(qp0 & b[w].x) + __popc(qp1 & b[w].y) + __popc(qn0 & a[w].x) + __popc(qn1 & a[w].y);
+		}
+	} else {
+		for (uint32_t w = 0; w < words; w++) {
+			uint2 a = __ldg(vp + w), b = __ldg(vn + w);
+			uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
+			score += __popc(qp0 & a.x) + __popc(qp1 & a.y) + __popc(qn0 & b.x) + __popc(qn1 & b.y);
+			score -= __popc(qp0 & b.x) + __popc(qp1 & b.y) + __popc(qn0 & a.x) + __popc(qn1 & a.y);
+		}
 	}
 	float sim = (float)score;
 	float d = p.metric == LMD_METRIC_IP ? -sim : 1.0f - sim;
@@ -591,6 +622,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 	const int L = (int)p.L;
 	const int cap = (int)p.list_cap;
 	const uint32_t nbr_lines = (p.r * 4 + 127) / 128;
+	const uint32_t entry_guard = p.has_entry ? p.entry_slot : LMD_INVALID_SLOT;
 
 	for (;;) {
 		uint32_t qi = 0;
@@ -658,6 +690,14 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 					const uint32_t *nx = p.nbrs + (uint64_t)key_slot(s_list[idx2]) * p.r + lane * 32;
 					asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
 				}
+				if (ROUTE == LMD_ROUTE_TERNARY && idx2 >= 0 && p.prefetch_planes) {
+					// ... and its block's plane region (positive planes, padding, negative planes: one span)
+					const uint8_t *b2 = p.blocks + (uint64_t)key_slot(s_list[idx2]) * p.block_bytes + (p.pos_off & ~127ull);
+					const uint32_t span = (uint32_t)(p.neg_off - (p.pos_off & ~127ull)) + p.r * p.words * 8;
+					for (uint32_t o = lane * 128; o < span; o += 32 * 128) {
+						asm volatile("prefetch.global.L2 [%0];" ::"l"(b2 + o));
+					}
+				}
 			}
 			for (uint32_t base = 0; base < p.r; base += 32) {
 				const uint32_t j = base + lane;
@@ -666,7 +706,10 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 					id_next = j + 32 < p.r ? __ldg(nrow + j + 32) : LMD_INVALID_SLOT;
 				}
 				bool isnew = false;
-				if (id != LMD_INVALID_SLOT) {
+				// The entry point is the one node whose list key does not come from this loop (its distance is always
+				// exact, core/Searcher.cpp:90-99, while ternary routing would give it a different one here), so it must
+				// never be "forgotten" by the filter: it is tested by value.
+				if (id != LMD_INVALID_SLOT && id != entry_guard) {
 					isnew = visited_test_and_set(p, s_filter, id, n_evict);
 				}
 				const uint32_t mask = __ballot_sync(FULL, isnew);
@@ -695,7 +738,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 					__syncwarp();
 				} else {
 					if (isnew) {
-						d = ternary_distance(p, blk, j, s_qp, s_qn);
+						d = ternary_distance<(CH > 0 && ROUTE == LMD_ROUTE_TERNARY ? (CH * TEAM * 4 + 63) / 64 : 0)>(p, blk, j, s_qp, s_qn);
 					}
 				}
 				// core/Searcher.cpp:175-185, candidates taken in neighbour order with a moving threshold
@@ -866,24 +909,46 @@ __global__ void __launch_bounds__(128) rerank_kernel(const KParams p) {
 template <typename K>
 static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, uint32_t nq, cudaStream_t st,
                                     const char *what) {
-	const int warps = 4; // __launch_bounds__(128)
-	size_t smem = (size_t)p.warp_smem_bytes * warps;
-	LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	int per_sm = 0;
-	LMD_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, warps * 32, smem));
-	if (per_sm < 1) {
-		set_error("%s: kernel does not fit on an SM with %zu bytes of shared memory per CTA", what, smem);
+	// Warps are independent (one query each), so the CTA size is only a packing choice: take the warps-per-CTA in
+	// {4, 2, 1} that puts the most warps on an SM (shared memory is granted per CTA; smaller CTAs waste less of it).
+	if ((size_t)p.warp_smem_bytes > (size_t)227 * 1024) {
+		set_error("%s: %u bytes of shared memory per query exceed the 227 KB an sm_100a CTA can have (list size / "
+		          "filter size too large)", what, p.warp_smem_bytes);
 		return LMD_ERR_UNSUPPORTED;
 	}
-	if (s->tune.ctas_per_sm > 0 && s->tune.ctas_per_sm < per_sm) {
-		per_sm = s->tune.ctas_per_sm;
+	LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+	                                 (int)std::min<size_t>((size_t)p.warp_smem_bytes * 4, (size_t)227 * 1024)));
+	int best_w = 0, best_ctas = 0;
+	for (int w = 4; w >= 1; w >>= 1) {
+		const int forced = s->tune.warps_per_cta;
+		if ((forced == 1 || forced == 2 || forced == 4) && w != forced) {
+			continue;
+		}
+		const size_t smem = (size_t)p.warp_smem_bytes * w;
+		if (smem > (size_t)227 * 1024) {
+			continue;
+		}
+		int per_sm = 0;
+		LMD_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, w * 32, smem));
+		if (per_sm * w > best_w * best_ctas) {
+			best_w = w;
+			best_ctas = per_sm;
+		}
 	}
-	uint32_t grid = (nq + warps - 1) / warps;
-	uint32_t cap = (uint32_t)(per_sm * s->sm_count);
+	if (best_ctas < 1) {
+		set_error("%s: kernel does not fit on an SM with %u bytes of shared memory per warp", what, p.warp_smem_bytes);
+		return LMD_ERR_UNSUPPORTED;
+	}
+	int warps_per_sm = best_w * best_ctas;
+	if (s->tune.ctas_per_sm > 0 && s->tune.ctas_per_sm * 4 < warps_per_sm) {
+		best_ctas = std::max(1, s->tune.ctas_per_sm * 4 / best_w); // the knob keeps its meaning: CTAs of 4 warps
+	}
+	uint32_t grid = (nq + best_w - 1) / best_w;
+	const uint32_t cap = (uint32_t)(best_ctas * s->sm_count);
 	if (grid > cap) {
 		grid = cap;
 	}
-	kernel<<<grid, warps * 32, smem, st>>>(p);
+	kernel<<<grid, best_w * 32, (size_t)p.warp_smem_bytes * best_w, st>>>(p);
 	LMD_CUDA_OK(cudaGetLastError());
 	return LMD_OK;
 }

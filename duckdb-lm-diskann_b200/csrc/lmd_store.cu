@@ -318,6 +318,7 @@ lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity
 			return fail(LMD_ERR_CUDA);
 		}
 	}
+	cudaGetLastError(); // start from a clean error state
 	fill_i64_kernel<<<(unsigned)((s->map_cap + 255) / 256), 256, 0, s->stream>>>((long long *)s->d_map_keys, s->map_cap,
 	                                                                              LMD_MAP_EMPTY);
 	if (cudaGetLastError() != cudaSuccess || cudaMemsetAsync(s->d_map_vals, 0, s->map_cap * 4, s->stream) != cudaSuccess ||
@@ -602,6 +603,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 	std::string k(key);
 	if (k == "filter_log2") {
 		s->tune.filter_log2 = (int)value;
+	} else if (k == "prefetch_planes") {
+		s->tune.prefetch_planes = (int)value;
 	} else if (k == "filter_mode") {
 		s->tune.filter_mode = (int)value;
 	} else if (k == "warps_per_cta") {

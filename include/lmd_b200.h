@@ -142,7 +142,7 @@ lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uin
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
 uint32_t lmd_abi_version(void);
 /* Tuning knobs for experiments (not needed for correct use): "filter_log2", "filter_mode", "warps_per_cta",
- * "ctas_per_sm", "tie_slots", "merge_min". */
+ * "ctas_per_sm", "tie_slots", "merge_min", "prefetch_planes". */
 lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value);
 
 #ifdef __cplusplus

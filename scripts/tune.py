@@ -25,15 +25,20 @@ ap.add_argument("--L", type=int, nargs="+", default=[64])
 ap.add_argument("--kind", default="clustered")
 ap.add_argument("--grid", default="filter_log2=0,10,11,12,13;ctas_per_sm=0")
 ap.add_argument("--oracle-sample", type=int, default=256)
+ap.add_argument("--metric", default="L2")
+ap.add_argument("--route", default="exact")
 a = ap.parse_args()
 fx = importlib.import_module("duckdb-lm-diskann_b200.fixtures")
 lmd = importlib.import_module("duckdb-lm-diskann_b200")
 x, nbrs, counts = bench.load_or_build_index(a, fx, "cuda")
 blocks = fx.pack_blocks(x, nbrs, counts, a.r, device="cuda")
-store = lmd.Store(a.dims, a.r, capacity=a.n)
+store = lmd.Store(a.dims, a.r, metric=lmd.METRIC_BY_NAME[a.metric], capacity=a.n)
+route = 1 if a.route == "ternary" else 0
+if route:
+    a.oracle_sample = 0
 store.upload(blocks)
 store.set_entry(0)
-q = [fx.make_dataset(a.nq, a.dims, kind=a.kind, seed=43 + 17 * b) for b in range(3)]
+q = [fx.make_dataset(a.nq, a.dims, kind=a.kind, seed=43 + 17 * b, normalize=(a.metric == "COSINE")) for b in range(3)]
 dq = [torch.from_numpy(b).cuda() for b in q]
 d_ids = torch.empty((a.nq, a.k), dtype=torch.int64, device="cuda")
 d_dist = torch.empty((a.nq, a.k), dtype=torch.float32, device="cuda")
@@ -60,10 +65,15 @@ for L in a.L:
         for k, v in zip(keys, combo):
             store.set_tuning(k, v)
         ms = []
-        for it in range(6):
-            st = store.search_raw(dq[it % 3], a.nq, a.k, L, out_ids=d_ids, out_dist=d_dist)
-            if it >= 2:
-                ms.append(st.traverse_ms)
+        try:
+            for it in range(6):
+                st = store.search_raw(dq[it % 3], a.nq, a.k, L, route=route, out_ids=d_ids, out_dist=d_dist)
+                if it >= 2:
+                    ms.append(st.traverse_ms)
+        except Exception as e:
+            print("L=%d %s  FAILED: %s" % (L, dict(zip(keys, combo)), e), flush=True)
+            continue
+        print("L=%d %s  rerank %.4f ms" % (L, dict(zip(keys, combo)), st.rerank_ms), flush=True) if route else None
         print("L=%d %s  traverse %.4f ms (min %.4f)  V/q %.1f evict/q %.1f fallbacks %d  alg GB/s %.0f" % (
             L, dict(zip(keys, combo)), np.mean(ms), min(ms), st.distance_evals / a.nq, st.filter_evictions / a.nq,
             st.merge_fallbacks, st.algorithmic_bytes / (np.mean(ms) * 1e-3) / 1e9), flush=True)

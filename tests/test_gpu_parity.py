@@ -187,20 +187,27 @@ def test_int8_nodes(lmd, oracle, fixtures_mod):
     check_parity(g[0], g[1], g[2], o[0], o[1], o[2], what="int8")
 
 
-def test_filter_size_does_not_change_results(lmd, make_index):
-    """The visited filter may forget: results must not depend on its size."""
-    ix = make_index(3000, 128, 32, metric="L2", kind="iid", nq=96)
+@pytest.mark.parametrize("metric,route", [("L2", 0), ("COSINE", 1), ("IP", 1)])
+def test_filter_size_does_not_change_results(lmd, make_index, metric, route):
+    """The visited filter may forget: results must not depend on its size or kind (u32 open addressing /
+    two-choice 16-bit buckets), for exact and for ternary routing (where the entry point, whose key is an exact
+    distance, must never be re-admitted with a routing distance)."""
+    ix = make_index(3000, 128, 32, metric=metric, kind="iid", nq=96)
     outs = []
-    with _store(lmd, ix, 128, 32, "L2") as s:
+    with _store(lmd, ix, 128, 32, metric) as s:
         s.upload(ix["blocks_np"])
         s.set_entry(0)
-        for lg in (6, 8, 11, 13):
-            s.set_tuning("filter_log2", lg)
-            outs.append(s.search(ix["queries"], 10, 128))
+        for mode in (0, 1):
+            s.set_tuning("filter_mode", mode)
+            for lg in (6, 8, 11, 13):
+                s.set_tuning("filter_log2", lg)
+                outs.append(s.search(ix["queries"], 10, 128, route=route))
     for o in outs[1:]:
         assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1])
-    assert outs[0][3].filter_evictions > 0  # the 64-entry filter really did forget
-    assert outs[0][3].distance_evals >= outs[-1][3].distance_evals
+    assert outs[0][3].filter_evictions > 0 and outs[4][3].filter_evictions > 0  # the 64-entry filters really did forget
+    assert outs[0][3].distance_evals >= outs[3][3].distance_evals
+    assert outs[4][3].distance_evals >= outs[7][3].distance_evals
+    assert outs[7][3].filter_evictions <= outs[3][3].filter_evictions
 
 
 def test_batch_merge_equals_one_by_one(lmd, oracle, make_index):
