@@ -10,6 +10,31 @@ using namespace lmd;
 
 namespace {
 
+// Where a caller's buffer lives, and the address the kernels can use for it. Pinned (page-locked) host memory is
+// mapped into the device's address space under UVA: the kernels read the queries and write the results straight
+// through PCIe / NVLink-C2C ("zero copy", 512 B in and 120 B out per query at k = 10), so the host-buffer path needs
+// no staging copy and no extra stream round trip. Pageable memory goes through the store's device scratch.
+enum BufKind { BUF_DEVICE, BUF_PINNED, BUF_PAGEABLE };
+BufKind classify(const void *p, void **dev_alias) {
+	*dev_alias = const_cast<void *>(p);
+	if (!p) {
+		return BUF_DEVICE;
+	}
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+		cudaGetLastError();
+		return BUF_PAGEABLE;
+	}
+	if (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) {
+		return BUF_DEVICE;
+	}
+	if (at.type == cudaMemoryTypeHost && at.devicePointer) {
+		*dev_alias = at.devicePointer;
+		return BUF_PINNED;
+	}
+	return BUF_PAGEABLE;
+}
+
 bool on_device(const void *p) {
 	cudaPointerAttributes at;
 	if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
@@ -98,25 +123,34 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	cudaStream_t st = s->stream;
 	const uint32_t q32 = (uint32_t)nq;
-	const bool dev_io = on_device(queries);
+	void *a_q, *a_ids, *a_dist, *a_count, *a_qstats;
+	const BufKind kq = classify(queries, &a_q), ki = classify(out_ids, &a_ids), kd = classify(out_dist, &a_dist),
+	              kc = classify(out_count, &a_count), ks = classify(out_qstats, &a_qstats);
+	const bool stage_q = kq == BUF_PAGEABLE;
+	const bool stage_out = ki == BUF_PAGEABLE; // outputs are staged together or not at all
+	if (!stage_out && (kd == BUF_PAGEABLE || kc == BUF_PAGEABLE || ks == BUF_PAGEABLE)) {
+		set_error("lmd_search_batch: out_ids is device / pinned memory but another output is pageable host memory");
+		return LMD_ERR_INVALID_ARG;
+	}
+	const bool dev_io = !stage_q && !stage_out; // nothing to copy: device-resident or zero-copy pinned buffers
 	const bool separate = route == LMD_ROUTE_TERNARY || (flags & LMD_SEARCH_SEPARATE_RERANK);
 	const bool want_qstats = (flags & LMD_SEARCH_PER_QUERY_STATS) && out_qstats;
 	const bool async = (flags & LMD_SEARCH_ASYNC) != 0;
 	lmd_status rc;
 	if (async && (!dev_io || stats)) {
-		set_error("LMD_SEARCH_ASYNC needs device-resident buffers and stats == NULL");
+		set_error("LMD_SEARCH_ASYNC needs device-resident or pinned buffers and stats == NULL");
 		return LMD_ERR_INVALID_ARG;
 	}
 
 	if (!async) {
 		LMD_CUDA_OK(cudaEventRecord(s->ev[0], st));
 	}
-	const float *d_q = queries;
-	int64_t *d_ids = out_ids;
-	float *d_dist = out_dist;
-	uint32_t *d_count = out_count;
-	uint32_t *d_qstats = want_qstats ? out_qstats : nullptr;
-	if (!dev_io) {
+	const float *d_q = static_cast<const float *>(a_q);
+	int64_t *d_ids = static_cast<int64_t *>(a_ids);
+	float *d_dist = static_cast<float *>(a_dist);
+	uint32_t *d_count = static_cast<uint32_t *>(a_count);
+	uint32_t *d_qstats = want_qstats ? static_cast<uint32_t *>(a_qstats) : nullptr;
+	if (stage_q) {
 		uint64_t need_q = nq * (uint64_t)s->cfg.dims;
 		uint64_t have_q = s->scratch_q;
 		if ((rc = grow(s->d_q, have_q, need_q, s)) != LMD_OK) {
@@ -124,6 +158,10 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 			return rc;
 		}
 		s->scratch_q = have_q;
+		LMD_CUDA_OK(cudaMemcpyAsync(s->d_q, queries, need_q * sizeof(float), cudaMemcpyHostToDevice, st));
+		d_q = s->d_q;
+	}
+	if (stage_out) {
 		uint64_t need_k = nq * (uint64_t)k;
 		if (s->scratch_k < need_k || !s->d_out_ids) {
 			uint64_t a = 0, b = 0, c = 0, d = 0;
@@ -135,8 +173,6 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 			}
 			s->scratch_k = need_k;
 		}
-		LMD_CUDA_OK(cudaMemcpyAsync(s->d_q, queries, need_q * sizeof(float), cudaMemcpyHostToDevice, st));
-		d_q = s->d_q;
 		d_ids = s->d_out_ids;
 		d_dist = s->d_out_dist; // always computed on the device; copied back only when asked for
 		d_count = s->d_out_count;
@@ -197,7 +233,7 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 		return LMD_OK;
 	}
 	LMD_CUDA_OK(cudaEventRecord(s->ev[3], st));
-	if (!dev_io) {
+	if (stage_out) {
 		LMD_CUDA_OK(cudaMemcpyAsync(out_ids, d_ids, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
 		if (out_dist) {
 			LMD_CUDA_OK(cudaMemcpyAsync(out_dist, d_dist, nq * k * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -234,8 +270,10 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 			cudaEventElapsedTime(&stats->rerank_ms, s->ev[2], s->ev[3]);
 		}
 		cudaEventElapsedTime(&stats->total_ms, s->ev[0], s->ev[4]);
-		if (!dev_io) {
+		if (stage_q) {
 			cudaEventElapsedTime(&stats->h2d_ms, s->ev[0], s->ev[1]);
+		}
+		if (stage_out) {
 			cudaEventElapsedTime(&stats->d2h_ms, s->ev[3], s->ev[4]);
 		}
 		// SURVEY.md section 8d. The sidecar holds uint32 slots, so an expansion reads 4R bytes of ids

@@ -46,8 +46,8 @@ enum { LMD_ROUTE_EXACT = 0, LMD_ROUTE_TERNARY = 1 };
 enum {
 	LMD_SEARCH_SEPARATE_RERANK = 1u << 0, /* run the rerank kernel even when traversal distances are already exact */
 	LMD_SEARCH_PER_QUERY_STATS = 1u << 1, /* fill out_qstats */
-	LMD_SEARCH_ASYNC = 1u << 2            /* device-resident buffers only: enqueue on the store's stream and return
-	                                         without synchronising; `stats` must be NULL */
+	LMD_SEARCH_ASYNC = 1u << 2            /* device-resident or pinned buffers only: enqueue on the store's stream and
+	                                         return without synchronising; `stats` must be NULL */
 };
 
 #define LMD_EMPTY_ROW_ID INT64_MAX /* empty neighbour slot, core/GraphManager.cpp:154-156,451-453 */
@@ -122,10 +122,12 @@ uint64_t lmd_store_device_bytes(const lmd_store *s); /* core/ISearcher.hpp:43 Ge
 
 /* --- search: replaces core/ISearcher.hpp:30-34 Search -> core/Searcher.cpp:256-272 -> PerformSearch :45-246,
  *     batched (ISearcher.hpp:36-37 anticipates it) ---
- * queries  [nq][dims] fp32, host or device.
+ * queries  [nq][dims] fp32: device memory, pinned host memory (read in place over PCIe - no staging copy) or pageable
+ *          host memory (staged through the store's device scratch).
  * k, L     as Searcher::Search: L == 0 -> cfg.l_search, then (k > 20 ? k + 20 : 40) if still 0, then max(L, k).
  * out_ids  [nq][k] row ids ascending by (distance, id), padded with -1; out_dist [nq][k] exact distances (may be
- *          NULL); out_count [nq] (may be NULL). Host or device (all outputs on the same side as `queries`).
+ *          NULL); out_count [nq] (may be NULL). Device, pinned host (written in place) or pageable host memory; the
+ *          outputs must all be pageable or all be device / pinned.
  * out_qstats [nq][2] = {expansions, distance evals} when LMD_SEARCH_PER_QUERY_STATS (may be NULL).
  * Thread-safety: concurrent searches on one store are serialised internally; uploads must not overlap searches. */
 lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
