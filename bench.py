@@ -202,6 +202,8 @@ def main():
     if dist_on:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device(dev))
 
     # ---- workload: one index (replicated), N_BATCHES query batches per rank -------------------------------------
@@ -307,14 +309,22 @@ def main():
         h_q = [torch.from_numpy(b).pin_memory() for b in batches]
         h_ids = torch.empty((a.nq, a.k), dtype=torch.int64).pin_memory()
         h_dist = torch.empty((a.nq, a.k), dtype=torch.float32).pin_memory()
+        # each call is synchronous: it returns when ids + distances of the step are in the caller's host buffers
         for i in range(max(a.warmup, 3)):
-            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist)
+            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist, stats=False)
         barrier()
         t0 = time.perf_counter()
         for i in range(a.steps):
-            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist)
+            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist, stats=False)
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
+        # what one `ORDER BY array_distance(...) LIMIT k` statement costs: a batch of ONE through the same call
+        lat = []
+        for i in range(220):
+            t1 = time.perf_counter()
+            store.search_raw(h_q[0][i:i + 1], 1, a.k, L, route=route, out_ids=h_ids[:1], out_dist=h_dist[:1], stats=False)
+            lat.append(time.perf_counter() - t1)
+        lat_us = sorted(lat[20:])[100] * 1e6
     if dist_on:
         t = torch.tensor([dev_ms, e2e_s], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -349,6 +359,7 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload, "L": L, "recall_at_10": round(recall, 4), "route": a.route,
                    "entry": "slot 0", "query_batches_rotated": N_BATCHES,
+                   "single_query_latency_us": round(lat_us, 1),
                    "l2_note": "node store %.1f GB >> 126 MB L2; every step gathers ~%.1f GB of it" % (
                        store.device_bytes / 1e9, alg_bytes / a.steps / 1e9),
                    "parallelism": "queries sharded, graph replicated (%d x %d queries per step)" % (world, a.nq)},

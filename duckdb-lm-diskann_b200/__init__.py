@@ -198,9 +198,10 @@ class Store:
         return int(lib().lmd_store_device_bytes(self._h))
 
     def search_raw(self, queries, nq, k, L=0, route=ROUTE_EXACT, flags=0, out_ids=None, out_dist=None, out_count=None,
-                   out_qstats=None):
-        """Thin call: any mix of numpy arrays / torch tensors / raw addresses, all on the same side."""
-        if flags & SEARCH_ASYNC:
+                   out_qstats=None, stats=True):
+        """Thin call: any mix of numpy arrays / torch tensors / raw addresses. stats=False passes a NULL lmd_stats
+        (the call still synchronises unless SEARCH_ASYNC is set) and returns None."""
+        if (flags & SEARCH_ASYNC) or not stats:
             _check(lib().lmd_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids),
                                           _ptr(out_dist), _ptr(out_count), _ptr(out_qstats), None))
             return None

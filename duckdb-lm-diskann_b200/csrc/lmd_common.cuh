@@ -11,6 +11,8 @@
 #include <cstdio>
 #include <mutex>
 #include <string>
+#include <unordered_map>
+#include <utility>
 
 #define LMD_INVALID_SLOT 0xFFFFFFFFu
 #define LMD_KEY_NONE 0xFFFFFFFFFFFFFFFFull
@@ -123,6 +125,7 @@ struct lmd_store {
 	cudaStream_t stream = nullptr, own_stream = nullptr, copy_stream = nullptr; // stream = the active one
 	cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 	lmd::Tuning tune;
+	mutable std::unordered_map<uint64_t, std::pair<int, int>> launch_cache; // (kernel, smem) -> (warps per CTA, CTAs per SM)
 	std::mutex mu;
 };
 

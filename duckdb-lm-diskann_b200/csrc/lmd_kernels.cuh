@@ -916,28 +916,37 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		          "filter size too large)", what, p.warp_smem_bytes);
 		return LMD_ERR_UNSUPPORTED;
 	}
-	LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-	                                 (int)std::min<size_t>((size_t)p.warp_smem_bytes * 4, (size_t)227 * 1024)));
+	// the occupancy queries cost several microseconds each: remember the answer per (kernel, shared memory) pair
+	const uint64_t cache_key = (uint64_t)(uintptr_t)kernel * 0x9E3779B97F4A7C15ull + p.warp_smem_bytes;
 	int best_w = 0, best_ctas = 0;
-	for (int w = 4; w >= 1; w >>= 1) {
-		const int forced = s->tune.warps_per_cta;
-		if ((forced == 1 || forced == 2 || forced == 4) && w != forced) {
-			continue;
+	auto hit = s->launch_cache.find(cache_key);
+	if (hit != s->launch_cache.end()) {
+		best_w = hit->second.first;
+		best_ctas = hit->second.second;
+	} else {
+		LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                                 (int)std::min<size_t>((size_t)p.warp_smem_bytes * 4, (size_t)227 * 1024)));
+		for (int w = 4; w >= 1; w >>= 1) {
+			const int forced = s->tune.warps_per_cta;
+			if ((forced == 1 || forced == 2 || forced == 4) && w != forced) {
+				continue;
+			}
+			const size_t smem = (size_t)p.warp_smem_bytes * w;
+			if (smem > (size_t)227 * 1024) {
+				continue;
+			}
+			int per_sm = 0;
+			LMD_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, w * 32, smem));
+			if (per_sm * w > best_w * best_ctas) {
+				best_w = w;
+				best_ctas = per_sm;
+			}
 		}
-		const size_t smem = (size_t)p.warp_smem_bytes * w;
-		if (smem > (size_t)227 * 1024) {
-			continue;
+		if (best_ctas < 1) {
+			set_error("%s: kernel does not fit on an SM with %u bytes of shared memory per warp", what, p.warp_smem_bytes);
+			return LMD_ERR_UNSUPPORTED;
 		}
-		int per_sm = 0;
-		LMD_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, w * 32, smem));
-		if (per_sm * w > best_w * best_ctas) {
-			best_w = w;
-			best_ctas = per_sm;
-		}
-	}
-	if (best_ctas < 1) {
-		set_error("%s: kernel does not fit on an SM with %u bytes of shared memory per warp", what, p.warp_smem_bytes);
-		return LMD_ERR_UNSUPPORTED;
+		s->launch_cache[cache_key] = std::make_pair(best_w, best_ctas);
 	}
 	int warps_per_sm = best_w * best_ctas;
 	if (s->tune.ctas_per_sm > 0 && s->tune.ctas_per_sm * 4 < warps_per_sm) {

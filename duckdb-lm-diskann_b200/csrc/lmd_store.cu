@@ -601,6 +601,7 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		return LMD_ERR_INVALID_ARG;
 	}
 	std::string k(key);
+	s->launch_cache.clear();
 	if (k == "filter_log2") {
 		s->tune.filter_log2 = (int)value;
 	} else if (k == "prefetch_planes") {

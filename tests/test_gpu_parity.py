@@ -273,6 +273,39 @@ def test_device_resident_io(lmd, make_index):
     assert st.h2d_ms == 0 and st.d2h_ms == 0
 
 
+def test_pinned_host_io_is_zero_copy(lmd, make_index):
+    """Pinned host buffers are read / written in place by the kernels (no staging copies), in every mix with device
+    buffers, for both routes; pageable outputs next to pinned ones are rejected."""
+    import torch
+    ix = make_index(3000, 128, 32, metric="COSINE", kind="clustered", nq=96)
+    nq, k = 96, 10
+    with _store(lmd, ix, 128, 32, "COSINE") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        for route in (0, 1):
+            ref = s.search(ix["queries"], k, 64, route=route)  # pageable numpy arrays: staged
+            assert ref[3].h2d_ms > 0 and ref[3].d2h_ms > 0
+            hq = torch.from_numpy(ix["queries"]).pin_memory()
+            h_ids = torch.full((nq, k), -7, dtype=torch.int64).pin_memory()
+            h_dist = torch.zeros((nq, k), dtype=torch.float32).pin_memory()
+            h_cnt = torch.zeros(nq, dtype=torch.int32).pin_memory()
+            st = s.search_raw(hq, nq, k, 64, route=route, out_ids=h_ids, out_dist=h_dist, out_count=h_cnt)
+            assert st.h2d_ms == 0 and st.d2h_ms == 0
+            assert np.array_equal(h_ids.numpy(), ref[0]) and np.array_equal(h_dist.numpy(), ref[1])
+            assert np.array_equal(h_cnt.numpy().astype(np.uint32), ref[2])
+            # pinned queries, device outputs
+            d_ids = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+            s.search_raw(hq, nq, k, 64, route=route, out_ids=d_ids)
+            assert np.array_equal(d_ids.cpu().numpy(), ref[0])
+            # pageable queries, pinned outputs
+            h_ids.fill_(-7)
+            st = s.search_raw(ix["queries"], nq, k, 64, route=route, out_ids=h_ids)
+            assert st.h2d_ms > 0 and st.d2h_ms == 0 and np.array_equal(h_ids.numpy(), ref[0])
+        with pytest.raises(lmd.LmdError) as e:
+            s.search_raw(hq, nq, k, 64, out_ids=h_ids, out_dist=np.zeros((nq, k), dtype=np.float32))
+        assert e.value.status == lmd.ERR_INVALID_ARG
+
+
 def test_merge_topk(lmd):
     rng = np.random.default_rng(0)
     G, nq, k = 8, 257, 10
