@@ -371,9 +371,9 @@ static float exact_to_slot(const index_t *ix, scratch_t *s, const float *q, uint
 	return lmdo_distance(q, s->tmp, ix->dims, ix->metric, NULL);            /* :172-173 */
 }
 
-/* Returns number of ids written to res (<= k). */
-static uint64_t search_one(const index_t *ix, scratch_t *s, const float *q, uint64_t k, uint64_t l_param,
-                           int64_t *res) {
+/* Returns number of ids written to res (<= k; <= L when final_pass == 0). */
+static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uint64_t k, uint64_t l_param,
+                            int64_t *res, int final_pass) {
 	/* Searcher.cpp:261-265 */
 	uint64_t L = l_param > 0 ? l_param : ix->cfg_l_search;
 	if (L == 0) {
@@ -461,6 +461,14 @@ static uint64_t search_one(const index_t *ix, scratch_t *s, const float *q, uint
 		}
 	}
 
+	if (!final_pass) {
+		/* Searcher.cpp:189 + H5: SearchForInitialCandidates gets the top list itself, worst first (heap pop order) */
+		uint64_t cnt = 0;
+		while (s->top.n) {
+			res[cnt++] = heap_pop(&s->top).id;
+		}
+		return cnt;
+	}
 	/* :189-245 final pass: exact distance of every listed candidate, keep k smallest, ascending */
 	while (s->top.n) {
 		cand_t c = heap_pop(&s->top);
@@ -479,6 +487,11 @@ static uint64_t search_one(const index_t *ix, scratch_t *s, const float *q, uint
 		res[j] = heap_pop(&s->fin).id; /* max-heap pops descending; fill from the back (H3) */
 	}
 	return cnt;
+}
+
+static uint64_t search_one(const index_t *ix, scratch_t *s, const float *q, uint64_t k, uint64_t l_param,
+                           int64_t *res) {
+	return search_core(ix, s, q, k, l_param, res, 1);
 }
 
 typedef struct {
@@ -613,5 +626,273 @@ int lmdo_search(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const i
 	if (row_ids) {
 		map_free(&rowmap);
 	}
+	return 0;
+}
+
+/* ================================================================================================
+ * Graph write side: GraphManager::RobustPrune and GraphManager::AddNode.
+ * ================================================================================================ */
+typedef struct {
+	float d;
+	int64_t id;
+	uint64_t slot;
+} pcand_t;
+
+static int pcand_cmp(const void *a, const void *b) { /* std::sort of pair<float,row_t>, GraphManager.cpp:300 */
+	const pcand_t *x = (const pcand_t *)a, *y = (const pcand_t *)b;
+	if (x->d < y->d) {
+		return -1;
+	}
+	if (y->d < x->d) {
+		return 1;
+	}
+	return x->id < y->id ? -1 : (x->id > y->id ? 1 : 0);
+}
+
+/* GraphManager.cpp:259-457. node_vec = the float vector handed to RobustPrune (AddNode passes the caller's vector
+ * for the new node, :140, and the block's converted vector for a neighbour, :185-197). Writes count + ids
+ * (INT64_MAX padded) into the node's block (:388-452) and returns the selected ids in cand[0..count). */
+static uint32_t robust_prune(index_t *ix, uint8_t *blocks, uint64_t node_slot, const float *node_vec, int64_t *cand,
+                             uint64_t ncand, float alpha, pcand_t *work, float *sel_vecs, float *tmp) {
+	if (ncand == 0) {
+		return 0; /* :262-264: returns before touching the block */
+	}
+	const uint64_t dims = ix->dims;
+	uint64_t m = 0;
+	for (uint64_t i = 0; i < ncand; i++) { /* :272-297 */
+		uint64_t slot;
+		if (!try_get_slot(ix, cand[i], &slot)) {
+			continue;
+		}
+		if (slot == node_slot) {
+			continue; /* :280-282 self */
+		}
+		lmdo_convert_raw(blocks + slot * ix->block_bytes + ix->lay.vector_off, tmp, dims, ix->vec_type);
+		work[m].d = lmdo_distance(node_vec, tmp, dims, ix->metric, NULL);
+		work[m].id = cand[i];
+		work[m].slot = slot;
+		m++;
+	}
+	qsort(work, m, sizeof(pcand_t), pcand_cmp); /* :300 */
+	uint64_t u = 0;
+	for (uint64_t i = 0; i < m; i++) { /* :302-305 std::unique on row id */
+		if (u == 0 || work[u - 1].id != work[i].id) {
+			work[u++] = work[i];
+		}
+	}
+	m = u;
+	uint32_t nsel = 0;
+	float *pvec = tmp;
+	for (uint64_t i = 0; i < m && nsel < ix->r; i++) { /* :320-379 */
+		lmdo_convert_raw(blocks + work[i].slot * ix->block_bytes + ix->lay.vector_off, pvec, dims, ix->vec_type);
+		int keep = 1;
+		for (uint32_t j = 0; j < nsel; j++) {
+			float dpr = lmdo_distance(pvec, sel_vecs + (size_t)j * dims, dims, ix->metric, NULL);
+			if (alpha * dpr < work[i].d) { /* :359 */
+				keep = 0;
+				break;
+			}
+		}
+		if (keep) {
+			memcpy(sel_vecs + (size_t)nsel * dims, pvec, dims * sizeof(float));
+			cand[nsel++] = work[i].id;
+		}
+	}
+	uint8_t *blk = blocks + node_slot * ix->block_bytes; /* :388-452 */
+	uint16_t c16 = (uint16_t)nsel;
+	memcpy(blk + ix->lay.count_off, &c16, 2);
+	for (uint32_t j = 0; j < ix->r; j++) {
+		int64_t v = j < nsel ? cand[j] : LMDO_EMPTY_ID;
+		memcpy(blk + ix->lay.ids_off + (size_t)j * 8, &v, 8);
+	}
+	return nsel;
+}
+
+typedef struct {
+	index_t ix;
+	i64map_t rowmap;
+	scratch_t s;
+	pcand_t *work;
+	float *sel_vecs, *tmp2, *nvec;
+	int64_t *cand;
+	uint64_t cand_cap;
+} builder_t;
+
+static int builder_init(builder_t *b, uint8_t *blocks, uint64_t block_bytes, int metric, int vec_type, uint64_t dims,
+                        uint32_t r, uint32_t l_insert, int use_map) {
+	memset(b, 0, sizeof(*b));
+	if (lmdo_layout_calc(dims, vec_type, r, &b->ix.lay)) {
+		return 2;
+	}
+	b->ix.blocks = blocks;
+	b->ix.block_bytes = block_bytes;
+	b->ix.metric = metric;
+	b->ix.vec_type = vec_type;
+	b->ix.route = LMDO_ROUTE_EXACT;
+	b->ix.dims = dims;
+	b->ix.r = r;
+	b->ix.cfg_l_search = l_insert;
+	b->ix.entry_row = LMDO_EMPTY_ID;
+	if (use_map) {
+		map_init(&b->rowmap, 1024);
+		b->ix.rowmap = &b->rowmap;
+	}
+	map_init(&b->s.visited, 4096);
+	b->s.tmp = (float *)malloc(dims * sizeof(float));
+	b->s.qplanes = (uint64_t *)malloc(lmdo_words_per_plane(dims) * 16);
+	b->cand_cap = (uint64_t)l_insert + r + 8;
+	b->work = (pcand_t *)malloc(b->cand_cap * sizeof(pcand_t));
+	b->cand = (int64_t *)malloc(b->cand_cap * sizeof(int64_t));
+	b->sel_vecs = (float *)malloc((size_t)r * dims * sizeof(float));
+	b->tmp2 = (float *)malloc(dims * sizeof(float));
+	b->nvec = (float *)malloc(dims * sizeof(float));
+	return 0;
+}
+
+static void builder_free(builder_t *b) {
+	if (b->ix.rowmap) {
+		map_free(&b->rowmap);
+	}
+	map_free(&b->s.visited);
+	free(b->s.tmp);
+	free(b->s.qplanes);
+	free(b->s.top.a);
+	free(b->s.beam.a);
+	free(b->s.fin.a);
+	free(b->work);
+	free(b->cand);
+	free(b->sel_vecs);
+	free(b->tmp2);
+	free(b->nvec);
+}
+
+/* GraphManager.cpp:65-121: allocate + zero the block, store the vector, register the row id, first node = entry */
+static void builder_add_vector(builder_t *b, uint8_t *blocks, uint64_t slot, int64_t row, const float *vec) {
+	index_t *ix = &b->ix;
+	uint8_t *blk = blocks + slot * ix->block_bytes;
+	memset(blk, 0, ix->block_bytes); /* GraphNode.cpp:12-24 */
+	if (ix->vec_type == LMDO_VEC_FLOAT32) {
+		memcpy(blk + ix->lay.vector_off, vec, ix->dims * 4); /* :97-98 */
+	} else {
+		for (uint64_t i = 0; i < ix->dims; i++) {
+			((int8_t *)(blk + ix->lay.vector_off))[i] = (int8_t)vec[i]; /* :104-107 plain cast */
+		}
+	}
+	if (ix->rowmap) {
+		/* rowid_to_node_ptr_map_[row_id] = ptr (:116): the latest mapping wins */
+		uint64_t old;
+		if (map_find(&b->rowmap, row, &old)) {
+			size_t p = mix64((uint64_t)row) & (b->rowmap.cap - 1);
+			while (b->rowmap.keys[p] != row || !b->rowmap.used[p]) {
+				p = (p + 1) & (b->rowmap.cap - 1);
+			}
+			b->rowmap.vals[p] = slot;
+		} else {
+			map_put(&b->rowmap, row, slot);
+		}
+	}
+	ix->n = slot + 1;
+	if (slot == 0) { /* :119-121 */
+		ix->entry_row = row;
+		ix->entry_slot = 0;
+		ix->entry_ok = 1;
+	}
+}
+
+int lmdo_build_serial(const float *vectors, uint64_t n, uint64_t dims, int metric, int vec_type, uint32_t r,
+                      uint32_t l_insert, float alpha, const int64_t *row_ids, uint64_t block_bytes, uint8_t *out_blocks,
+                      int64_t *entry_row_out) {
+	builder_t b;
+	if (builder_init(&b, out_blocks, block_bytes, metric, vec_type, dims, r, l_insert, row_ids != NULL)) {
+		return 2;
+	}
+	index_t *ix = &b.ix;
+	for (uint64_t i = 0; i < n; i++) {
+		const int64_t row = row_ids ? row_ids[i] : (int64_t)i;
+		const float *vec = vectors + i * dims;
+		builder_add_vector(&b, out_blocks, i, row, vec);
+		/* :124-136 candidates: SearchForInitialCandidates(L = max(l_insert, l_insert)), Searcher.cpp:281-293 */
+		uint64_t nc = 0;
+		if (ix->entry_ok) {
+			nc = search_core(ix, &b.s, vec, l_insert, l_insert, b.cand, 0);
+			if (nc > l_insert) {
+				nc = l_insert;
+			}
+		}
+		/* :140 RobustPrune with the caller's float vector; :143-157 write the list (RobustPrune already did) */
+		uint32_t deg = robust_prune(ix, out_blocks, i, vec, b.cand, nc, alpha, b.work, b.sel_vecs, b.tmp2);
+		if (nc == 0) {
+			/* RobustPrune returned early; AddNode still writes count 0 and INT64_MAX ids (:143-157) */
+			uint8_t *blk = out_blocks + i * block_bytes;
+			for (uint32_t j = 0; j < r; j++) {
+				int64_t v = LMDO_EMPTY_ID;
+				memcpy(blk + ix->lay.ids_off + (size_t)j * 8, &v, 8);
+			}
+		}
+		/* :171-200 interconnect: every selected neighbour is re-pruned over its own list + the new node */
+		int64_t *mine = (int64_t *)malloc((deg ? deg : 1) * sizeof(int64_t));
+		memcpy(mine, b.cand, deg * sizeof(int64_t));
+		for (uint32_t t = 0; t < deg; t++) {
+			uint64_t vslot;
+			if (!try_get_slot(ix, mine[t], &vslot)) {
+				continue;
+			}
+			uint8_t *vblk = out_blocks + vslot * block_bytes;
+			lmdo_convert_raw(vblk + ix->lay.vector_off, b.nvec, dims, vec_type); /* GetNodeVector */
+			uint16_t cnt;
+			memcpy(&cnt, vblk + ix->lay.count_off, 2);
+			uint64_t m = 0;
+			for (uint16_t j = 0; j < cnt; j++) { /* GetNeighbors, GraphManager.cpp:230-257 */
+				int64_t id;
+				memcpy(&id, vblk + ix->lay.ids_off + (size_t)j * 8, 8);
+				if (id != LMDO_EMPTY_ID) {
+					b.cand[m++] = id;
+				}
+			}
+			b.cand[m++] = row;
+			robust_prune(ix, out_blocks, vslot, b.nvec, b.cand, m, alpha, b.work, b.sel_vecs, b.tmp2);
+		}
+		free(mine);
+	}
+	if (entry_row_out) {
+		*entry_row_out = ix->entry_ok ? ix->entry_row : LMDO_EMPTY_ID;
+	}
+	builder_free(&b);
+	return 0;
+}
+
+int lmdo_robust_prune(const float *vectors, uint64_t n, uint64_t dims, int metric, int vec_type, uint32_t r, float alpha,
+                      const int64_t *row_ids, uint64_t m, const uint64_t *node_idx, const int64_t *cands, uint64_t c,
+                      int64_t *out_ids, uint32_t *out_count) {
+	lmdo_layout lay;
+	if (lmdo_layout_calc(dims, vec_type, r, &lay)) {
+		return 2;
+	}
+	const uint64_t bb = lmdo_block_bytes(lay.total_node_size);
+	uint8_t *blocks = (uint8_t *)malloc(n * bb);
+	builder_t b;
+	if (!blocks || builder_init(&b, blocks, bb, metric, vec_type, dims, r, (uint32_t)c, row_ids != NULL)) {
+		free(blocks);
+		return 2;
+	}
+	for (uint64_t i = 0; i < n; i++) {
+		builder_add_vector(&b, blocks, i, row_ids ? row_ids[i] : (int64_t)i, vectors + i * dims);
+	}
+	for (uint64_t j = 0; j < m; j++) {
+		uint64_t nc = 0;
+		for (uint64_t t = 0; t < c; t++) {
+			if (cands[j * c + t] != LMDO_EMPTY_ID) {
+				b.cand[nc++] = cands[j * c + t];
+			}
+		}
+		lmdo_convert_raw(blocks + node_idx[j] * bb + lay.vector_off, b.nvec, dims, vec_type);
+		uint32_t deg = robust_prune(&b.ix, blocks, node_idx[j], b.nvec, b.cand, nc, alpha, b.work, b.sel_vecs, b.tmp2);
+		out_count[j] = deg;
+		for (uint32_t t = 0; t < r; t++) {
+			out_ids[j * r + t] = t < deg ? b.cand[t] : LMDO_EMPTY_ID;
+		}
+	}
+	builder_free(&b);
+	free(blocks);
 	return 0;
 }

@@ -57,6 +57,15 @@ int lmdo_search(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const i
                 uint64_t nq, uint64_t k, uint64_t l_param, int route, int64_t *out_ids, float *out_dist,
                 uint32_t *out_count, uint64_t *out_stats, int nthreads);
 
+/* Graph write side, same contracts as lmdref_build_serial / lmdref_robust_prune in
+ * ref_build_harness.cpp. core/GraphManager.cpp:65-203 (AddNode) and :259-457 (RobustPrune). */
+int lmdo_build_serial(const float *vectors, uint64_t n, uint64_t dims, int metric, int vec_type, uint32_t r,
+                      uint32_t l_insert, float alpha, const int64_t *row_ids, uint64_t block_bytes, uint8_t *out_blocks,
+                      int64_t *entry_row_out);
+int lmdo_robust_prune(const float *vectors, uint64_t n, uint64_t dims, int metric, int vec_type, uint32_t r, float alpha,
+                      const int64_t *row_ids, uint64_t m, const uint64_t *node_idx, const int64_t *cands, uint64_t c,
+                      int64_t *out_ids, uint32_t *out_count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -50,6 +50,10 @@ def port():
         _sig(l.lmdo_search, C.c_int, [_P, C.c_uint64, C.c_uint64, _P, C.c_int64, C.c_int, C.c_int, C.c_uint64,
                                       C.c_uint32, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, _P, _P,
                                       _P, _P, C.c_int])
+        _sig(l.lmdo_build_serial, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_uint32,
+                                            C.c_float, _P, C.c_uint64, _P, _P])
+        _sig(l.lmdo_robust_prune, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_float, _P,
+                                            C.c_uint64, _P, _P, C.c_uint64, _P, _P])
         _libs["port"] = l
     return _libs["port"]
 
@@ -76,6 +80,10 @@ def ref(kind="fixed"):
         _sig(l.lmdref_search, C.c_int, [_P, C.c_uint64, C.c_uint64, _P, C.c_int64, C.c_int, C.c_int, C.c_uint64,
                                         C.c_uint32, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64, _P, _P, _P, _P,
                                         C.c_int])
+        _sig(l.lmdref_build_serial, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_uint32,
+                                              C.c_float, _P, C.c_uint64, _P, _P])
+        _sig(l.lmdref_robust_prune, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_float, _P,
+                                              C.c_uint64, _P, _P, C.c_uint64, _P, _P])
         _libs[key] = l
     return _libs[key]
 
@@ -164,3 +172,44 @@ def search(blocks, block_bytes, dims, r, queries, k, L=0, metric=1, vec_type=1, 
     if rc:
         raise RuntimeError("oracle search failed (%d)" % rc)
     return ids, dist, cnt, st
+
+
+INT64_MAX = np.iinfo(np.int64).max
+
+
+def build_serial(x, r, l_insert=128, alpha=1.2, metric=1, vec_type=1, row_ids=None, impl="port"):
+    """Serial Vamana build, one AddNode per row in order (core/GraphManager.cpp:65-203). x: [n, dims] float32 (for
+    INT8 nodes the values are cast on write, as the reference does). -> (blocks [n, block_bytes] uint8, entry row id).
+    impl: "port" (C restatement), "fixed" / "literal" (the reference's own GraphManager.cpp + Searcher.cpp)."""
+    x = _np(x, np.float32)
+    n, dims = x.shape
+    lay = layout(dims, vec_type, r)
+    bb = (lay["total_node_size"] + 4095) // 4096 * 4096
+    blocks = np.zeros((n, bb), dtype=np.uint8)
+    rid = None if row_ids is None else _np(row_ids, np.int64)
+    entry = C.c_int64(INT64_MAX)
+    args = (x.ctypes.data, n, dims, metric, vec_type, r, l_insert, alpha, None if rid is None else rid.ctypes.data, bb,
+            blocks.ctypes.data, C.addressof(entry))
+    rc = port().lmdo_build_serial(*args) if impl == "port" else ref(impl).lmdref_build_serial(*args)
+    if rc:
+        raise RuntimeError("oracle build failed (%d)" % rc)
+    return blocks, int(entry.value)
+
+
+def robust_prune(x, r, alpha, node_idx, cands, metric=1, vec_type=1, row_ids=None, impl="port"):
+    """RobustPrune (core/GraphManager.cpp:259-457) of m nodes. node_idx [m] positions in x; cands [m, c] candidate ROW
+    ids, INT64_MAX = none. -> (ids [m, r] INT64_MAX padded, count [m])."""
+    x = _np(x, np.float32)
+    n, dims = x.shape
+    node_idx = _np(node_idx, np.uint64)
+    cands = _np(cands, np.int64)
+    m, c = cands.shape
+    rid = None if row_ids is None else _np(row_ids, np.int64)
+    out = np.full((m, r), INT64_MAX, dtype=np.int64)
+    cnt = np.zeros(m, dtype=np.uint32)
+    args = (x.ctypes.data, n, dims, metric, vec_type, r, alpha, None if rid is None else rid.ctypes.data, m,
+            node_idx.ctypes.data, cands.ctypes.data, c, out.ctypes.data, cnt.ctypes.data)
+    rc = port().lmdo_robust_prune(*args) if impl == "port" else ref(impl).lmdref_robust_prune(*args)
+    if rc:
+        raise RuntimeError("oracle robust_prune failed (%d)" % rc)
+    return out, cnt

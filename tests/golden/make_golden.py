@@ -128,8 +128,55 @@ def make_arith():
     print("arith.npz written")
 
 
+BUILD_CASES = [
+    # name, n, dims, r, l_insert, alpha, metric, kind, vec_type, sparse row ids
+    ("l2_d24_r8", 400, 24, 8, 24, 1.2, "L2", "iid", 1, False),
+    ("cos_d32_r12", 350, 32, 12, 40, 1.2, "COSINE", "iid", 1, True),
+    ("l2_d16_r6_int8", 300, 16, 6, 20, 1.0, "L2", "iid", 2, False),
+]
+
+
+def make_build_case(name, n, dims, r, l_insert, alpha, metric, kind, vec_type, sparse):
+    """GraphManager::AddNode x n (serial build) and GraphManager::RobustPrune on random candidate lists, by the
+    reference's own GraphManager.cpp + Searcher.cpp (+ H1-H5). Stored: inputs, neighbour ids / counts of every block."""
+    x = fx.make_dataset(n, dims, kind=kind, seed=52, normalize=(metric == "COSINE"))
+    if vec_type == 2:
+        x = np.round(x * 40).astype(np.float32)
+    rid = None
+    if sparse:
+        rid = np.random.default_rng(13).choice(np.arange(5, 30 * n, dtype=np.int64), size=n, replace=False)
+    lay = fx.layout(dims, r, vec_type)
+    out = {"x": x, "meta": np.array([n, dims, r, l_insert, METRIC[metric], vec_type], dtype=np.int64),
+           "alpha": np.float32(alpha)}
+    if rid is not None:
+        out["row_ids"] = rid
+    for impl in ("fixed", "literal"):
+        blocks, entry = pyoracle.build_serial(x, r, l_insert, alpha, metric=METRIC[metric], vec_type=vec_type,
+                                              row_ids=rid, impl=impl)
+        out[impl + "_counts"] = blocks[:, 0:2].copy().view(np.uint16)[:, 0]
+        out[impl + "_ids"] = blocks[:, lay["ids_off"]:lay["ids_off"] + 8 * r].copy().view(np.int64)
+        out[impl + "_entry"] = np.int64(entry)
+    rng = np.random.default_rng(17)
+    m, c = 64, 3 * r + 5
+    node_idx = rng.integers(0, n, m).astype(np.uint64)
+    ids = np.arange(n, dtype=np.int64) if rid is None else rid
+    cands = ids[rng.integers(0, n, (m, c))]
+    cands[:, ::7] = np.iinfo(np.int64).max      # holes
+    cands[:, 3] = cands[:, 4]                   # duplicates
+    cands[:, 5] = ids[node_idx.astype(np.int64)]  # the node itself
+    cands[:, 6] = 10 ** 15                      # a row id that does not exist
+    p_ids, p_cnt = pyoracle.robust_prune(x, r, alpha, node_idx, cands, metric=METRIC[metric], vec_type=vec_type,
+                                         row_ids=rid, impl="fixed")
+    out["prune_node_idx"], out["prune_cands"], out["prune_ids"], out["prune_count"] = node_idx, cands, p_ids, p_cnt
+    np.savez_compressed(os.path.join(HERE, "build_" + name + ".npz"), **out)
+    print("build_%s: mean degree %.2f (literal build: %d edges)" % (name, out["fixed_counts"].mean(),
+                                                                     int(out["literal_counts"].sum())))
+
+
 if __name__ == "__main__":
     assert pyoracle.have_ref("fixed") and pyoracle.have_ref("literal"), "run `make -C oracle ref` first"
     make_arith()
     for c in SEARCH_CASES:
         make_search_case(*c)
+    for c in BUILD_CASES:
+        make_build_case(*c)

@@ -191,3 +191,69 @@ def test_golden_matches_reference_live(oracle, fixtures_mod):
                                               nthreads=1, impl=impl)
             assert np.array_equal(ids, z[impl + "_ids"]) and np.array_equal(cnt, z[impl + "_count"])
             assert np.array_equal(_bits(dist), _bits(z[impl + "_dist"]))
+
+
+# ---- graph write side: core/GraphManager.cpp:65-203 (AddNode), :259-457 (RobustPrune) ----------------------------
+BUILD_FILES = sorted(glob.glob(os.path.join(GOLDEN, "build_*.npz")))
+
+
+def _build_case(path):
+    z = np.load(path)
+    n, dims, r, l_insert, metric, vec_type = (int(v) for v in z["meta"])
+    rid = z["row_ids"] if "row_ids" in z.files else None
+    return z, dict(n=n, dims=dims, r=r, l_insert=l_insert, metric=metric, vec_type=vec_type, row_ids=rid,
+                   alpha=float(z["alpha"]))
+
+
+@pytest.mark.parametrize("path", BUILD_FILES, ids=[os.path.basename(p)[6:-4] for p in BUILD_FILES])
+def test_serial_build_golden(oracle, fixtures_mod, path):
+    """The C restatement of AddNode + RobustPrune reproduces the graph the reference's own GraphManager.cpp builds
+    (with Searcher.cpp + H1-H5): every neighbour id, every count, the entry point."""
+    z, c = _build_case(path)
+    blocks, entry = oracle.build_serial(z["x"], c["r"], c["l_insert"], c["alpha"], metric=c["metric"],
+                                        vec_type=c["vec_type"], row_ids=c["row_ids"])
+    lay = fixtures_mod.layout(c["dims"], c["r"], c["vec_type"])
+    counts = blocks[:, 0:2].copy().view(np.uint16)[:, 0]
+    ids = blocks[:, lay["ids_off"]:lay["ids_off"] + 8 * c["r"]].copy().view(np.int64)
+    assert entry == int(z["fixed_entry"])
+    assert np.array_equal(counts, z["fixed_counts"]) and np.array_equal(ids, z["fixed_ids"])
+    # shape of a usable graph: no self loops, no duplicates, unused slots hold INT64_MAX
+    row = np.arange(c["n"], dtype=np.int64) if c["row_ids"] is None else c["row_ids"]
+    for i in range(c["n"]):
+        live = ids[i, :counts[i]]
+        assert row[i] not in live and len(set(live.tolist())) == len(live)
+        assert np.all(ids[i, counts[i]:] == np.iinfo(np.int64).max)
+    assert counts.mean() > 0.5 * c["r"]
+    # SURVEY.md section 0.2: the untouched reference connects nothing (SearchForInitialCandidates returns no ids)
+    assert int(z["literal_counts"].sum()) == 0
+
+
+@pytest.mark.parametrize("path", BUILD_FILES, ids=[os.path.basename(p)[6:-4] for p in BUILD_FILES])
+def test_robust_prune_golden(oracle, path):
+    z, c = _build_case(path)
+    ids, cnt = oracle.robust_prune(z["x"], c["r"], c["alpha"], z["prune_node_idx"], z["prune_cands"],
+                                   metric=c["metric"], vec_type=c["vec_type"], row_ids=c["row_ids"])
+    assert np.array_equal(cnt, z["prune_count"]) and np.array_equal(ids, z["prune_ids"])
+
+
+def test_serial_build_equals_reference_live(oracle, fixtures_mod):
+    _need_ref(oracle, "fixed")
+    for (n, d, r, L, metric, vt) in [(700, 32, 16, 48, 1, 1), (500, 40, 10, 30, 3, 1), (400, 24, 8, 30, 1, 2)]:
+        x = fixtures_mod.make_dataset(n, d, kind="iid", seed=77, normalize=False)
+        if vt == 2:
+            x = np.round(x * 40).astype(np.float32)
+        a = oracle.build_serial(x, r, L, 1.2, metric=metric, vec_type=vt, impl="fixed")
+        b = oracle.build_serial(x, r, L, 1.2, metric=metric, vec_type=vt, impl="port")
+        assert a[1] == b[1] and np.array_equal(a[0], b[0])  # whole blocks, byte for byte
+
+
+def test_serial_build_is_searchable(oracle, fixtures_mod):
+    """recall of the fixed search on the serially built graph: the bar the GPU builder is compared with."""
+    n, d, r = 2500, 32, 16
+    x = fixtures_mod.make_dataset(n, d, kind="clustered", seed=3)
+    q = fixtures_mod.make_dataset(64, d, kind="clustered", seed=4)
+    blocks, entry = oracle.build_serial(x, r, 64, 1.2)
+    bb = fixtures_mod.layout(d, r)["block_bytes"]
+    ids, _, _, _ = oracle.search(blocks, bb, d, r, q, 10, 64, entry_row_id=entry)
+    truth = fixtures_mod.brute_force_topk(x, q, 10, "L2", device="cpu")
+    assert fixtures_mod.recall_at_k(ids, truth) >= 0.9
