@@ -54,6 +54,21 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class BuildParams(C.Structure):
+    _fields_ = [("l_insert", C.c_uint32), ("alpha", C.c_float), ("max_batch", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class BuildStats(C.Structure):
+    _fields_ = [("nodes", C.c_uint64), ("rounds", C.c_uint64), ("search_expansions", C.c_uint64),
+                ("search_evals", C.c_uint64), ("prune_evals", C.c_uint64), ("backlink_prunes", C.c_uint64),
+                ("inbox_overflows", C.c_uint64), ("search_ms", C.c_float), ("prune_ms", C.c_float),
+                ("backlink_ms", C.c_float), ("finalize_ms", C.c_float), ("total_ms", C.c_float),
+                ("launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
 # every symbol include/lmd_b200.h declares: (name, restype, argtypes)
 _P = C.c_void_p
 SYMBOLS = [
@@ -72,6 +87,10 @@ SYMBOLS = [
     ("lmd_search_batch", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P,
                                     _P, C.POINTER(Stats)]),
     ("lmd_merge_topk", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P]),
+    ("lmd_store_upload_vectors", C.c_int32, [_P, _P, _P, C.c_uint64]),
+    ("lmd_build_graph", C.c_int32, [_P, C.POINTER(BuildParams), C.POINTER(BuildStats)]),
+    ("lmd_robust_prune_batch", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_float, _P, _P]),
+    ("lmd_store_download_blocks", C.c_int32, [_P, C.c_uint64, C.c_uint64, _P]),
     ("lmd_last_error", C.c_char_p, []),
     ("lmd_abi_version", C.c_uint32, []),
     ("lmd_set_tuning", C.c_int32, [_P, C.c_char_p, C.c_int64]),
@@ -180,6 +199,38 @@ class Store:
     def download_block(self, row_id):
         out = np.empty(self.block_bytes, dtype=np.uint8)
         _check(lib().lmd_store_download_block(self._h, int(row_id), _ptr(out)))
+        return out
+
+    # ---- graph write side (core/GraphManager.cpp:65-203, :259-457) ----
+    def upload_vectors(self, vectors, row_ids=None):
+        """Appends nodes given only their fp32 vectors [n, dims] (blocks get neighbour count 0)."""
+        v = vectors if hasattr(vectors, "data_ptr") else np.ascontiguousarray(vectors, dtype=np.float32)
+        if row_ids is not None and isinstance(row_ids, np.ndarray):
+            row_ids = np.ascontiguousarray(row_ids, dtype=np.int64)
+        _check(lib().lmd_store_upload_vectors(self._h, _ptr(row_ids), _ptr(v), v.shape[0]))
+
+    def build_graph(self, l_insert=128, alpha=1.2, max_batch=0):
+        """Batch-parallel Vamana build over every node in the store -> BuildStats."""
+        bp = BuildParams(l_insert, alpha, max_batch, 0)
+        st = BuildStats()
+        _check(lib().lmd_build_graph(self._h, C.byref(bp), C.byref(st)))
+        return st
+
+    def robust_prune(self, node_row_ids, cand_row_ids, alpha=1.2):
+        """RobustPrune of m nodes: cand_row_ids [m, c] (INT64_MAX = none) -> (ids [m, r] INT64_MAX padded, count [m])."""
+        nodes = np.ascontiguousarray(node_row_ids, dtype=np.int64)
+        cands = np.ascontiguousarray(cand_row_ids, dtype=np.int64)
+        m, c = cands.shape
+        out = np.full((m, self.cfg.r), EMPTY_ROW_ID, dtype=np.int64)
+        cnt = np.zeros(m, dtype=np.uint32)
+        _check(lib().lmd_robust_prune_batch(self._h, _ptr(nodes), _ptr(cands), m, c, alpha, _ptr(out), _ptr(cnt)))
+        return out, cnt
+
+    def download_blocks(self, first_slot=0, n=None, out=None):
+        n = self.node_count - first_slot if n is None else n
+        if out is None:
+            out = np.empty((n, self.block_bytes), dtype=np.uint8)
+        _check(lib().lmd_store_download_blocks(self._h, first_slot, n, _ptr(out)))
         return out
 
     def set_stream(self, cuda_stream):

@@ -122,6 +122,11 @@ struct lmd_store {
 	uint32_t entry_slot = LMD_INVALID_SLOT;
 	bool dirty = true; // views need (re)building
 
+	// graph-build scratch (lmd_build.cu), allocated on first use and kept
+	uint32_t *d_inbox = nullptr, *d_inbox_cnt = nullptr, *d_touched = nullptr;
+	uint64_t *d_planes = nullptr; // [capacity][2 * words] ternary planes of every node
+	uint32_t inbox_cap = 0;
+
 	cudaStream_t stream = nullptr, own_stream = nullptr, copy_stream = nullptr; // stream = the active one
 	cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 	lmd::Tuning tune;
@@ -131,10 +136,16 @@ struct lmd_store {
 
 namespace lmd {
 
+// Store internals shared with lmd_build.cu (the caller holds s->mu).
+lmd_status store_copy_to_device(lmd_store *s, void *dst, const void *src, size_t bytes);
+lmd_status store_ingest(lmd_store *s, const int64_t *row_ids, uint64_t base, uint64_t n);
+lmd_status store_lookup_slot(lmd_store *s, int64_t row_id, uint32_t *slot);
+
 // Kernel launchers (each returns a status and has set_error() on failure).
 struct TraverseArgs {
 	const lmd_store *s;
 	const float *d_queries; // [nq][dims]
+	uint32_t q_stride = 0;  // floats between queries, 0 = dims
 	uint32_t nq, k, L, route;
 	int64_t *d_out_ids;   // [nq][k] or null when the separate rerank writes them
 	float *d_out_dist;    // [nq][k] or null

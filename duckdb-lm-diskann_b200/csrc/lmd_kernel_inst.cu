@@ -1,8 +1,9 @@
 // One translation unit per kernel family: compiled by build.py with
 //   -DLMD_INST_KIND=0 -DLMD_INST_METRIC=<1|2|3> -DLMD_INST_ROUTE=<0|1>   traversal kernels of one metric and route
 //   -DLMD_INST_KIND=1 -DLMD_INST_METRIC=<1|2|3>                          rerank kernels of one metric
+//   -DLMD_INST_KIND=2 -DLMD_INST_METRIC=<1|2|3>                          RobustPrune kernels of one metric
 // so that the shape x list-size variants of each family build in parallel with the others.
-#include "lmd_kernels.cuh"
+#include "lmd_build_kernels.cuh"
 
 #define LMD_CAT2(a, b) a##b
 #define LMD_CAT(a, b) LMD_CAT2(a, b)
@@ -15,6 +16,10 @@ lmd_status LMD_CAT(LMD_CAT(dispatch_traverse_m, LMD_INST_METRIC), LMD_CAT(_r, LM
 	LMD_DISPATCH_SHAPE(traverse_kernel, LMD_INST_METRIC, LMD_INST_ROUTE)
 	set_error("no traversal kernel for this configuration (L=%u)", p.L);
 	return LMD_ERR_UNSUPPORTED;
+}
+#elif LMD_INST_KIND == 2
+lmd_status LMD_CAT(dispatch_prune_m, LMD_INST_METRIC)(PruneParams &p, const lmd_store *s, cudaStream_t st) {
+	LMD_DISPATCH_PRUNE_SHAPE(LMD_INST_METRIC)
 }
 #else
 lmd_status LMD_CAT(dispatch_rerank_m, LMD_INST_METRIC)(KParams &p, const lmd_store *s, uint32_t nq, int lpl,

@@ -42,6 +42,7 @@ struct KParams {
 	unsigned long long *counters; // [0] next query, [1] E, [2] V, [3] filter evictions, [4] reranked, [5] tie overflows, [6] merge fallbacks
 	uint64_t block_bytes, pos_off, neg_off;
 	uint32_t nq, dims, row_floats, r, words;
+	uint32_t q_stride; // floats between consecutive queries (dims for a caller's batch, row_floats for store rows)
 	uint32_t L, k, metric, list_cap, merge_min;
 	uint32_t entry_slot, has_entry;
 	uint32_t filter_mask, filter_shift; // filter_mode 0: slots - 1, 32 - log2(slots)
@@ -123,10 +124,10 @@ struct QueryRegs {
 	float na;
 };
 
-template <int TEAM, int CH, int METRIC>
-__device__ __forceinline__ void load_query(QueryRegs<TEAM, CH> &Q, const KParams &p, uint32_t qi, int lane,
-                                           float *s_q) {
-	const float *src = p.queries + (uint64_t)qi * p.dims;
+// Loads one vector (dims floats at src; row_floats = dims padded to a multiple of 32) into the warp's query view.
+template <int TEAM, int CH>
+__device__ __forceinline__ void load_vec(QueryRegs<TEAM, CH> &Q, const float *src, uint32_t dims, uint32_t row_floats,
+                                         int lane, float *s_q) {
 	float na = 0.0f;
 	if (CH > 0) {
 		const int tl = lane % TEAM;
@@ -134,17 +135,18 @@ __device__ __forceinline__ void load_query(QueryRegs<TEAM, CH> &Q, const KParams
 		for (int c = 0; c < (CH > 0 ? CH : 1); c++) {
 			uint32_t f = (uint32_t)(c * TEAM + tl) * 4;
 			float4 v;
-			v.x = f + 0 < p.dims ? __ldg(src + f + 0) : 0.0f;
-			v.y = f + 1 < p.dims ? __ldg(src + f + 1) : 0.0f;
-			v.z = f + 2 < p.dims ? __ldg(src + f + 2) : 0.0f;
-			v.w = f + 3 < p.dims ? __ldg(src + f + 3) : 0.0f;
+			v.x = f + 0 < dims ? __ldg(src + f + 0) : 0.0f;
+			v.y = f + 1 < dims ? __ldg(src + f + 1) : 0.0f;
+			v.z = f + 2 < dims ? __ldg(src + f + 2) : 0.0f;
+			v.w = f + 3 < dims ? __ldg(src + f + 3) : 0.0f;
 			Q.q[c] = v;
 			na = fmaf(v.x, v.x, fmaf(v.y, v.y, fmaf(v.z, v.z, fmaf(v.w, v.w, na))));
 		}
 		na = team_sum<TEAM>(na);
 	} else {
-		for (uint32_t f = lane; f < p.row_floats; f += 32) {
-			float v = f < p.dims ? __ldg(src + f) : 0.0f;
+		__syncwarp();
+		for (uint32_t f = lane; f < row_floats; f += 32) {
+			float v = f < dims ? __ldg(src + f) : 0.0f;
 			s_q[f] = v;
 			na = fmaf(v, v, na);
 		}
@@ -153,6 +155,12 @@ __device__ __forceinline__ void load_query(QueryRegs<TEAM, CH> &Q, const KParams
 		__syncwarp();
 	}
 	Q.na = na;
+}
+
+template <int TEAM, int CH, int METRIC>
+__device__ __forceinline__ void load_query(QueryRegs<TEAM, CH> &Q, const KParams &p, uint32_t qi, int lane,
+                                           float *s_q) {
+	load_vec<TEAM, CH>(Q, p.queries + (uint64_t)qi * p.q_stride, p.dims, p.row_floats, lane, s_q);
 }
 
 // Raw partial results of the exact distance from the query to the m (1..32) nodes whose slots are in s_nb[0..m):
@@ -554,7 +562,7 @@ __device__ __forceinline__ int find_unexpanded(const uint64_t *s_list, int n, in
 // s_qp[g] holds bits [32g, 32g+32) of the positive plane, s_qn likewise.
 __device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t qi, int lane, uint32_t *s_qp,
                                                     uint32_t *s_qn) {
-	const float *src = p.queries + (uint64_t)qi * p.dims;
+	const float *src = p.queries + (uint64_t)qi * p.q_stride;
 	for (uint32_t g = 0; g < p.words * 2; g++) {
 		uint32_t f = g * 32 + lane;
 		float v = f < p.dims ? __ldg(src + f) : 0.0f;
@@ -924,8 +932,8 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		best_w = hit->second.first;
 		best_ctas = hit->second.second;
 	} else {
-		LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                                 (int)std::min<size_t>((size_t)p.warp_smem_bytes * 4, (size_t)227 * 1024)));
+		// opt in to the full 227 KB once: the same kernel is launched with different list / filter sizes
+		LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
 		for (int w = 4; w >= 1; w >>= 1) {
 			const int forced = s->tune.warps_per_cta;
 			if ((forced == 1 || forced == 2 || forced == 4) && w != forced) {

@@ -76,6 +76,7 @@ static KParams base_params(const lmd_store *s, const float *d_queries, uint32_t 
 	p.pos_off = s->lay.pos_off;
 	p.neg_off = s->lay.neg_off;
 	p.nq = nq;
+	p.q_stride = s->cfg.dims;
 	p.dims = s->cfg.dims;
 	p.row_floats = s->row_floats;
 	p.r = s->cfg.r;
@@ -175,6 +176,9 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.out_count = a.d_out_count;
 	p.qstats = a.d_qstats;
 	p.cand = a.d_cand;
+	if (a.q_stride) {
+		p.q_stride = a.q_stride;
+	}
 	// room behind the top L for distance ties (see list_insert): integer ternary distances tie all the time, fp32
 	// distances only for duplicate vectors
 	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots : (a.route == LMD_ROUTE_TERNARY ? 64u : 0u);

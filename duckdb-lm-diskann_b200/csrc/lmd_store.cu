@@ -352,6 +352,10 @@ lmd_status lmd_store_destroy(lmd_store *s) {
 	cudaFree(s->d_out_count);
 	cudaFree(s->d_qstats);
 	cudaFree(s->d_cand);
+	cudaFree(s->d_inbox);
+	cudaFree(s->d_inbox_cnt);
+	cudaFree(s->d_touched);
+	cudaFree(s->d_planes);
 	if (s->h_stage) {
 		cudaFreeHost(s->h_stage);
 	}
@@ -433,27 +437,19 @@ static lmd_status copy_to_device(lmd_store *s, void *dst, const void *src, size_
 	return LMD_OK;
 }
 
-lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n) {
-	if (!s || (!blocks && n)) {
-		set_error("lmd_store_upload: null argument");
-		return LMD_ERR_INVALID_ARG;
-	}
-	if (n == 0) {
-		return LMD_OK;
-	}
-	std::lock_guard<std::mutex> g(s->mu);
-	if (s->n + n > s->capacity) {
-		set_error("lmd_store_upload: %llu + %llu nodes exceed the store capacity %llu", (unsigned long long)s->n,
-		          (unsigned long long)n, (unsigned long long)s->capacity);
-		return LMD_ERR_INVALID_ARG;
-	}
-	LMD_CUDA_OK(cudaSetDevice(s->device));
+} // extern "C"
+
+namespace lmd {
+
+lmd_status store_copy_to_device(lmd_store *s, void *dst, const void *src, size_t bytes) {
+	return copy_to_device(s, dst, src, bytes);
+}
+
+// Everything lmd_store_upload does after the blocks [base, base + n) are in d_blocks: row ids, row-id map, packed
+// vectors, entry-point resolution. The caller holds s->mu.
+lmd_status store_ingest(lmd_store *s, const int64_t *row_ids, uint64_t base, uint64_t n) {
 	const uint64_t bb = s->cfg.block_bytes;
-	const uint64_t base = s->n;
-	lmd_status st = copy_to_device(s, s->d_blocks + base * bb, blocks, n * bb);
-	if (st != LMD_OK) {
-		return st;
-	}
+	lmd_status st = LMD_OK;
 	const int64_t *d_rid = nullptr;
 	if (row_ids) {
 		// stage the row ids in the slot->row table itself, then let the kernel read them from there
@@ -494,6 +490,38 @@ lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *bl
 		s->has_entry = slot != LMD_INVALID_SLOT;
 	}
 	return LMD_OK;
+}
+
+lmd_status store_lookup_slot(lmd_store *s, int64_t row_id, uint32_t *slot) {
+	return lookup_slot(s, row_id, slot);
+}
+
+} // namespace lmd
+
+extern "C" {
+
+lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n) {
+	if (!s || (!blocks && n)) {
+		set_error("lmd_store_upload: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (n == 0) {
+		return LMD_OK;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	if (s->n + n > s->capacity) {
+		set_error("lmd_store_upload: %llu + %llu nodes exceed the store capacity %llu", (unsigned long long)s->n,
+		          (unsigned long long)n, (unsigned long long)s->capacity);
+		return LMD_ERR_INVALID_ARG;
+	}
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	const uint64_t bb = s->cfg.block_bytes;
+	const uint64_t base = s->n;
+	lmd_status st = copy_to_device(s, s->d_blocks + base * bb, blocks, n * bb);
+	if (st != LMD_OK) {
+		return st;
+	}
+	return lmd::store_ingest(s, row_ids, base, n);
 }
 
 lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block) {

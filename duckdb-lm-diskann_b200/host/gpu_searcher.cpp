@@ -135,6 +135,54 @@ void DeviceNodeStore::SetEntryPoint(common::row_t row_id) {
 	Check(lmd_store_set_entry(store_, row_id), "DeviceNodeStore::SetEntryPoint");
 }
 
+void DeviceNodeStore::UploadVectors(const common::row_t *row_ids, const float *vectors, common::idx_t n) {
+	Check(lmd_store_upload_vectors(store_, row_ids, vectors, n), "DeviceNodeStore::UploadVectors");
+}
+
+lmd_build_stats DeviceNodeStore::BuildGraph(common::idx_t max_batch) {
+	lmd_build_params bp;
+	std::memset(&bp, 0, sizeof(bp));
+	bp.l_insert = config_.l_insert;
+	bp.alpha = config_.alpha;
+	bp.max_batch = static_cast<uint32_t>(max_batch);
+	lmd_build_stats st;
+	Check(lmd_build_graph(store_, &bp, &st), "DeviceNodeStore::BuildGraph");
+	return st;
+}
+
+common::idx_t DeviceNodeStore::WriteBack(core::IStorageManager &storage, core::IGraphManager &graph,
+                                         const std::vector<common::row_t> &row_ids, common::idx_t batch_nodes) {
+	if (batch_nodes == 0) {
+		batch_nodes = 1;
+	}
+	std::vector<uint8_t> stage(static_cast<size_t>(batch_nodes) * block_bytes_);
+	common::idx_t written = 0;
+	for (common::idx_t first = 0; first < row_ids.size(); first += batch_nodes) {
+		const common::idx_t now = std::min<common::idx_t>(batch_nodes, row_ids.size() - first);
+		Check(lmd_store_download_blocks(store_, first, now, stage.data()), "DeviceNodeStore::WriteBack");
+		for (common::idx_t i = 0; i < now; i++) {
+			common::IndexPointer ptr;
+			if (!graph.TryGetNodePointer(row_ids[first + i], ptr)) {
+				continue;
+			}
+			common::data_ptr_t dst = storage.GetMutableNodeBlockData(ptr);
+			if (!dst) {
+				continue;
+			}
+			std::memcpy(dst, stage.data() + static_cast<size_t>(i) * block_bytes_, block_bytes_);
+			storage.MarkBlockDirty(ptr);
+			written++;
+		}
+	}
+	if (!row_ids.empty()) {
+		common::IndexPointer first_ptr;
+		if (graph.TryGetNodePointer(row_ids[0], first_ptr)) {
+			graph.SetEntryPoint(first_ptr, row_ids[0]);
+		}
+	}
+	return written;
+}
+
 common::idx_t DeviceNodeStore::NodeCount() const {
 	return lmd_store_node_count(store_);
 }

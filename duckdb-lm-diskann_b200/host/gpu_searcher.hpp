@@ -58,6 +58,18 @@ public:
 	void SyncEntryPoint(const core::IGraphManager &graph);
 	void SetEntryPoint(common::row_t row_id);
 
+	// ---- graph write side ----
+	// Appends nodes from raw fp32 vectors (what GraphManager::AddNode stores, core/GraphManager.cpp:81-121).
+	void UploadVectors(const common::row_t *row_ids, const float *vectors, common::idx_t n);
+	// Batch-parallel replacement of the AddNode loop (core/GraphManager.cpp:65-203 + RobustPrune :259-457) over every
+	// node in the store; config.l_insert / config.alpha / config.r as the reference reads them.
+	lmd_build_stats BuildGraph(common::idx_t max_batch = 0);
+	// Copies the built blocks (neighbour ids, counts, ternary planes) into the host's blocks:
+	// TryGetNodePointer -> GetMutableNodeBlockData -> memcpy -> MarkBlockDirty, and moves the graph's entry point to
+	// the first node as AddNode does (:119-121). `row_ids` in upload order. Returns the number of blocks written.
+	common::idx_t WriteBack(core::IStorageManager &storage, core::IGraphManager &graph,
+	                        const std::vector<common::row_t> &row_ids, common::idx_t batch_nodes = 4096);
+
 	common::idx_t NodeCount() const;
 	common::idx_t DeviceBytes() const;
 	common::idx_t BlockBytes() const {

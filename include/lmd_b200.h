@@ -140,6 +140,42 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq, uint32_t k,
                           int64_t *out_ids, float *out_dist);
 
+/* --- graph write side: replaces core/GraphManager.cpp:65-203 (AddNode, one row at a
+ *     time) and :259-457 (RobustPrune) by a batch-parallel build on the device. Writes the same node blocks, including
+ *     the ternary planes of every neighbour, which nothing in the reference writes (GraphManager.cpp:402-444). --- */
+typedef struct {
+	uint32_t l_insert;  /* config.l_insert (core/index_config.hpp:33-38 default 128): candidate list per inserted node */
+	float alpha;        /* config.alpha (default 1.2) */
+	uint32_t max_batch; /* nodes inserted per round, 0 = automatic; a round sees the graph of all earlier rounds */
+	uint32_t reserved;  /* must be 0 */
+} lmd_build_params;
+
+typedef struct {
+	uint64_t nodes, rounds;
+	uint64_t search_expansions, search_evals; /* candidate searches (traversal kernel) */
+	uint64_t prune_evals;                     /* distances computed by the prune kernel */
+	uint64_t backlink_prunes;                 /* neighbour lists re-pruned because a new node chose them */
+	uint64_t inbox_overflows;                 /* back-link candidates dropped (more than 2R new nodes chose one node in a round) */
+	float search_ms, prune_ms, backlink_ms, finalize_ms, total_ms; /* CUDA-event times */
+	uint32_t launches;
+	uint32_t reserved;
+} lmd_build_stats;
+
+/* Appends n nodes given only their vectors (fp32 [n][dims]; stored as the store's vec_type exactly as AddNode stores
+ * them, GraphManager.cpp:96-108: memcpy or a plain cast to int8). Blocks get neighbour count 0. */
+lmd_status lmd_store_upload_vectors(lmd_store *s, const int64_t *row_ids, const float *vectors, uint64_t n);
+/* (Re)builds the graph over every node in the store; the first node is the entry point (GraphManager.cpp:119-121).
+ * Rewrites count / ids / planes of every mirrored block and the search views. stats may be NULL. */
+lmd_status lmd_build_graph(lmd_store *s, const lmd_build_params *params, lmd_build_stats *stats);
+/* RobustPrune of m nodes in one launch. node_row_ids [m]; cand_row_ids [m][c] (INT64_MAX = no candidate; unknown row
+ * ids, duplicates and the node itself are skipped as the reference skips them); out_ids [m][r] INT64_MAX padded;
+ * out_count [m]. Host buffers. Does not modify the store. */
+lmd_status lmd_robust_prune_batch(lmd_store *s, const int64_t *node_row_ids, const int64_t *cand_row_ids, uint64_t m,
+                                  uint32_t c, float alpha, int64_t *out_ids, uint32_t *out_count);
+/* Reads n mirrored blocks starting at slot `first_slot` back (host or device buffer): how a built graph reaches the
+ * host's storage (IStorageManager::AllocateNodeBlock + memcpy). */
+lmd_status lmd_store_download_blocks(lmd_store *s, uint64_t first_slot, uint64_t n, void *out_blocks);
+
 /* --- misc --- */
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
 uint32_t lmd_abi_version(void);

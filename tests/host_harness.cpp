@@ -301,6 +301,34 @@ int lmdhost_initial_candidates(void *p, const float *vec, uint64_t dims, uint64_
 	});
 }
 
+// Graph write side through the adapter: the host's blocks hold only vectors; BuildGraph on the device, WriteBack
+// through IStorageManager::GetMutableNodeBlockData / MarkBlockDirty; out_blocks = the HOST's blocks afterwards.
+int lmdhost_build_and_write_back(void *p, uint32_t l_insert, float alpha, uint64_t max_batch, uint8_t *out_blocks,
+                                 uint64_t n, uint64_t block_bytes, const int64_t *row_ids, int64_t *entry_out) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		h->cfg.l_insert = l_insert;
+		h->cfg.alpha = alpha;
+		auto store = std::make_shared<b200::DeviceNodeStore>(h->cfg, n, 0, block_bytes);
+		std::vector<common::row_t> all(n);
+		for (uint64_t i = 0; i < n; i++) {
+			all[i] = row_ids ? row_ids[i] : (int64_t)i;
+		}
+		store->MirrorFrom(*h->storage, *h->graph, all, 1000); // vectors only: the blocks have no neighbours yet
+		store->BuildGraph(max_batch);
+		store->WriteBack(*h->storage, *h->graph, all, 777);
+		for (uint64_t i = 0; i < n; i++) {
+			common::IndexPointer ptr;
+			h->graph->TryGetNodePointer(all[i], ptr);
+			std::memcpy(out_blocks + i * block_bytes, h->storage->GetNodeBlockData(ptr), block_bytes);
+		}
+		*entry_out = h->graph->GetEntryPointRowId();
+		h->store = store; // searches now run on the freshly built store
+		h->searcher = std::make_unique<b200::GpuSearcher>(h->store);
+		h->scan = std::make_unique<b200::GpuIndexScan>(h->searcher.get(), h->graph.get(), h->cfg);
+	});
+}
+
 // MarkBlockDirty path: overwrite one block on the host side, refresh its mirror.
 int lmdhost_rewrite_block(void *p, int64_t row_id, const uint8_t *block, uint64_t block_bytes) {
 	Host *h = static_cast<Host *>(p);

@@ -40,6 +40,7 @@ def _lib():
     l.lmdhost_multi_scan.argtypes = [P, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P]
     l.lmdhost_initial_candidates.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
     l.lmdhost_rewrite_block.argtypes = [P, C.c_int64, P, C.c_uint64]
+    l.lmdhost_build_and_write_back.argtypes = [P, C.c_uint32, C.c_float, C.c_uint64, P, C.c_uint64, C.c_uint64, P, P]
     return l
 
 
@@ -255,3 +256,33 @@ def test_search_for_initial_candidates(oracle, make_index):
         # L = max(l_insert = 128, 40) (core/Searcher.cpp:281-282); the 40 closest of that list
         o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q[None, :], 40, 128, entry_row_id=0)
         assert n.value == 40 and np.array_equal(out[:40], o[0][0])
+
+
+@pytest.mark.gpu
+def test_build_graph_and_write_back_through_the_interfaces(oracle, fixtures_mod):
+    """Host blocks that hold only vectors (what AddNode has written before it connects a node,
+    core/GraphManager.cpp:81-121) -> DeviceNodeStore::MirrorFrom -> BuildGraph -> WriteBack through
+    IStorageManager::GetMutableNodeBlockData / MarkBlockDirty. The host's blocks then search like any index."""
+    n, dims, r = 3000, 64, 16
+    x = fixtures_mod.make_dataset(n, dims, kind="clustered", seed=12)
+    q = fixtures_mod.make_dataset(48, dims, kind="clustered", seed=13)
+    rid = np.random.default_rng(2).choice(np.arange(10, 9 * n, dtype=np.int64), size=n, replace=False)
+    lay = fixtures_mod.layout(dims, r)
+    empty = fixtures_mod.pack_blocks(x, np.full((n, r), -1, dtype=np.int64), np.zeros(n, dtype=np.int64), r,
+                                     row_ids=rid).numpy()
+    with Host(_lib(), empty, lay["block_bytes"], dims, r, row_ids=rid, entry=int(rid[0]), l_search=64) as h:
+        out = np.zeros_like(empty)
+        entry = C.c_int64(-1)
+        rc = h.lib.lmdhost_build_and_write_back(h.h, 48, 1.2, 300, out.ctypes.data, n, lay["block_bytes"],
+                                                rid.ctypes.data, C.addressof(entry))
+        assert rc == 0, h.lib.lmdhost_last_error().decode()
+        assert entry.value == int(rid[0])
+        cnt = out[:, 0:2].copy().view(np.uint16)[:, 0]
+        assert cnt.mean() > 0.5 * r
+        # the written-back HOST blocks are a searchable index for the CPU reference semantics ...
+        o = oracle.search(out, lay["block_bytes"], dims, r, q, 10, 64, row_ids=rid, entry_row_id=int(rid[0]))
+        truth = rid[fixtures_mod.brute_force_topk(x, q, 10, "L2", device="cuda")]
+        assert fixtures_mod.recall_at_k(o[0], truth) >= 0.9
+        # ... and the adapter's own searches (now on the built store) return the same rows
+        err, ids, cnt_q, _ = h.multi_scan(q, 10)
+        assert err is None and (ids == o[0]).all(axis=1).mean() >= 0.97
