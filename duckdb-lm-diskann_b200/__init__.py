@@ -78,6 +78,8 @@ SYMBOLS = [
     ("lmd_store_destroy", C.c_int32, [_P]),
     ("lmd_store_upload", C.c_int32, [_P, _P, _P, C.c_uint64]),
     ("lmd_store_update", C.c_int32, [_P, C.c_int64, _P]),
+    ("lmd_store_apply", C.c_int32, [_P, _P, _P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    ("lmd_store_remove", C.c_int32, [_P, _P, C.c_uint64, C.POINTER(C.c_uint64)]),
     ("lmd_store_set_entry", C.c_int32, [_P, C.c_int64]),
     ("lmd_store_finalize", C.c_int32, [_P]),
     ("lmd_store_download_block", C.c_int32, [_P, C.c_int64, _P]),
@@ -189,6 +191,20 @@ class Store:
 
     def update(self, row_id, block):
         _check(lib().lmd_store_update(self._h, int(row_id), _ptr(block)))
+
+    def apply(self, row_ids, blocks):
+        """Batch upsert of dirty / newly allocated blocks (MarkBlockDirty + AllocateNodeBlock) -> nodes appended."""
+        rid = np.ascontiguousarray(row_ids, dtype=np.int64)
+        out = C.c_uint64(0)
+        _check(lib().lmd_store_apply(self._h, _ptr(rid), _ptr(blocks), rid.shape[0], C.byref(out)))
+        return out.value
+
+    def remove(self, row_ids):
+        """HandleNodeDeletion / FreeNode for a batch of row ids -> how many were present."""
+        rid = np.ascontiguousarray(row_ids, dtype=np.int64)
+        out = C.c_uint64(0)
+        _check(lib().lmd_store_remove(self._h, _ptr(rid), rid.shape[0], C.byref(out)))
+        return out.value
 
     def set_entry(self, row_id):
         _check(lib().lmd_store_set_entry(self._h, int(row_id)))

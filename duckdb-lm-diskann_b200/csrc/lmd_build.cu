@@ -388,6 +388,11 @@ lmd_status lmd_build_graph(lmd_store *s, const lmd_build_params *params, lmd_bui
 	if (n == 0) {
 		return LMD_OK;
 	}
+	if (s->removed) {
+		set_error("lmd_build_graph: %llu rows were removed from this store; rebuild into a fresh store",
+		          (unsigned long long)s->removed);
+		return LMD_ERR_UNSUPPORTED;
+	}
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	cudaStream_t st = s->stream;
 	const uint32_t inbox_cap = 2 * r;

@@ -122,6 +122,13 @@ struct lmd_store {
 	uint32_t entry_slot = LMD_INVALID_SLOT;
 	bool dirty = true; // views need (re)building
 
+	// lmd_store_apply scratch: staged dirty blocks, their row ids and resolved slots (grown on demand)
+	uint8_t *d_apply = nullptr;
+	int64_t *d_apply_rids = nullptr;
+	uint32_t *d_apply_slots = nullptr;
+	uint64_t apply_cap = 0; // blocks
+	uint64_t removed = 0;   // row ids taken out by lmd_store_remove (their slots stay allocated)
+
 	// graph-build scratch (lmd_build.cu), allocated on first use and kept
 	uint32_t *d_inbox = nullptr, *d_inbox_cnt = nullptr, *d_touched = nullptr;
 	uint64_t *d_planes = nullptr; // [capacity][2 * words] ternary planes of every node

@@ -15,6 +15,8 @@
 
 #include <cstring>
 #include <new>
+#include <unordered_map>
+#include <vector>
 
 namespace lmd {
 
@@ -39,6 +41,7 @@ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
 }
 
 #define LMD_MAP_EMPTY ((long long)0x8000000000000000LL) // INT64_MIN is never a DuckDB row id
+#define LMD_MAP_TOMB ((long long)0x8000000000000001LL)  // a removed row id: probes walk over it, nothing reuses it
 
 // One thread per uploaded node: record row id, insert row id -> slot.
 // A row id seen twice keeps the LATEST slot (an update of the mapping, like std::map::operator[]).
@@ -75,6 +78,65 @@ __device__ __forceinline__ uint32_t map_lookup(const long long *__restrict__ map
 			return LMD_INVALID_SLOT;
 		}
 		h = (h + 1) & map_mask;
+	}
+}
+
+// row ids -> slots, one thread each (LMD_INVALID_SLOT = not in the store)
+__global__ void lookup_many_kernel(const long long *map_keys, const uint32_t *map_vals, uint64_t map_mask,
+                                   const int64_t *rids, uint64_t n, uint32_t *out) {
+	uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (i < n) {
+		out[i] = map_lookup(map_keys, map_vals, map_mask, rids[i]);
+	}
+}
+
+// core/GraphManager.cpp:476-499 (HandleNodeDeletion / FreeNode): `rowid_to_node_ptr_map_.erase(row_id)`.
+// One thread per row id; counts the ids that were present.
+__global__ void remove_rowids_kernel(long long *map_keys, const uint32_t *map_vals, uint64_t map_mask,
+                                     const int64_t *rids, uint64_t n, int64_t *slot_row,
+                                     unsigned long long *removed) {
+	uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (i >= n) {
+		return;
+	}
+	const long long rid = (long long)rids[i];
+	uint64_t h = mix64((uint64_t)rid) & map_mask;
+	for (;;) {
+		long long k = map_keys[h];
+		if (k == rid) {
+			// two threads may carry the same row id: only the one that swaps the key counts it
+			if ((long long)atomicCAS((unsigned long long *)&map_keys[h], (unsigned long long)rid,
+			                         (unsigned long long)LMD_MAP_TOMB) == rid) {
+				slot_row[map_vals[h]] = -1; // the slot stays allocated but is unreachable
+				atomicAdd(removed, 1ull);
+			}
+			return;
+		}
+		if (k == LMD_MAP_EMPTY) {
+			return;
+		}
+		h = (h + 1) & map_mask;
+	}
+}
+
+// block i of the staging buffer -> slot slots[i] of the mirror (LMD_INVALID_SLOT = superseded inside the batch).
+// One CTA per block, 16-byte pieces (block_bytes is a multiple of 8; the tail goes as 8-byte words).
+__global__ void scatter_blocks_kernel(const uint8_t *__restrict__ stage, const uint32_t *__restrict__ slots,
+                                      uint64_t block_bytes, uint8_t *__restrict__ blocks) {
+	const uint32_t slot = slots[blockIdx.x];
+	if (slot == LMD_INVALID_SLOT) {
+		return;
+	}
+	const uint8_t *src = stage + (uint64_t)blockIdx.x * block_bytes;
+	uint8_t *dst = blocks + (uint64_t)slot * block_bytes;
+	if ((block_bytes & 15) == 0) {
+		for (uint64_t o = threadIdx.x * 16ull; o < block_bytes; o += blockDim.x * 16ull) {
+			*reinterpret_cast<uint4 *>(dst + o) = *reinterpret_cast<const uint4 *>(src + o);
+		}
+	} else {
+		for (uint64_t o = threadIdx.x * 8ull; o < block_bytes; o += blockDim.x * 8ull) {
+			*reinterpret_cast<uint2 *>(dst + o) = *reinterpret_cast<const uint2 *>(src + o);
+		}
 	}
 }
 
@@ -135,6 +197,49 @@ __global__ void build_sidecar_kernel(const uint8_t *__restrict__ blocks, uint64_
 		}
 	}
 	nbrs[node * r + j] = out;
+}
+
+// The two view builders for a LIST of slots (the blocks an lmd_store_apply call overwrote). One warp per slot.
+__global__ void refresh_slots_kernel(const uint8_t *__restrict__ blocks, uint64_t block_bytes, uint64_t vector_off,
+                                     uint64_t count_off, uint64_t ids_off, uint32_t dims, uint32_t vec_type,
+                                     uint32_t row_floats, uint32_t r, const uint32_t *__restrict__ slots, uint64_t m,
+                                     uint64_t n_nodes, int identity, int with_sidecar,
+                                     const long long *__restrict__ map_keys, const uint32_t *__restrict__ map_vals,
+                                     uint64_t map_mask, float *__restrict__ vecs, uint32_t *__restrict__ nbrs) {
+	uint64_t w = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+	uint32_t lane = threadIdx.x & 31;
+	if (w >= m) {
+		return;
+	}
+	const uint32_t slot = slots[w];
+	if (slot == LMD_INVALID_SLOT) {
+		return;
+	}
+	const uint8_t *blk = blocks + (uint64_t)slot * block_bytes;
+	float *dst = vecs + (uint64_t)slot * row_floats;
+	for (uint32_t i = lane; i < row_floats; i += 32) {
+		float v = 0.0f;
+		if (i < dims) {
+			v = vec_type == LMD_VEC_FLOAT32 ? reinterpret_cast<const float *>(blk + vector_off)[i]
+			                                : (float)reinterpret_cast<const int8_t *>(blk + vector_off)[i];
+		}
+		dst[i] = v;
+	}
+	if (!with_sidecar) {
+		return;
+	}
+	const uint32_t count = *reinterpret_cast<const uint16_t *>(blk + count_off);
+	for (uint32_t j = lane; j < r; j += 32) {
+		uint32_t out = LMD_INVALID_SLOT;
+		if (j < count) {
+			int64_t rid = reinterpret_cast<const int64_t *>(blk + ids_off)[j];
+			if (rid != INT64_MAX) {
+				out = identity ? ((rid >= 0 && (uint64_t)rid < n_nodes) ? (uint32_t)rid : LMD_INVALID_SLOT)
+				               : map_lookup(map_keys, map_vals, map_mask, rid);
+			}
+		}
+		nbrs[(uint64_t)slot * r + j] = out;
+	}
 }
 
 __global__ void fill_i64_kernel(long long *p, uint64_t n, long long v) {
@@ -352,6 +457,9 @@ lmd_status lmd_store_destroy(lmd_store *s) {
 	cudaFree(s->d_out_count);
 	cudaFree(s->d_qstats);
 	cudaFree(s->d_cand);
+	cudaFree(s->d_apply);
+	cudaFree(s->d_apply_rids);
+	cudaFree(s->d_apply_slots);
 	cudaFree(s->d_inbox);
 	cudaFree(s->d_inbox_cnt);
 	cudaFree(s->d_touched);
@@ -554,6 +662,183 @@ lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block) {
 	    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->d_nbrs + (uint64_t)slot * s->cfg.r);
 	LMD_CUDA_OK(cudaGetLastError());
 	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+	return LMD_OK;
+}
+
+// Batch form of MarkBlockDirty + AllocateNodeBlock (core/IStorageManager.hpp:142-177): the host hands over every block
+// it changed or created since the last call. Known row ids overwrite their slot, new ones are appended in batch order;
+// a row id that occurs twice keeps its LAST block (what a host that re-dirtied a block means).
+lmd_status lmd_store_apply(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n,
+                           uint64_t *out_appended) {
+	if (out_appended) {
+		*out_appended = 0;
+	}
+	if (!s || ((!blocks || !row_ids) && n)) {
+		set_error("lmd_store_apply: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (n == 0) {
+		return LMD_OK;
+	}
+	if (is_device_ptr(row_ids)) {
+		set_error("lmd_store_apply: row_ids must be host memory");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	const uint64_t bb = s->cfg.block_bytes;
+	const uint64_t chunk = 16384; // blocks staged per pass (64 MiB at 4 KiB blocks)
+	if (s->apply_cap < (n < chunk ? n : chunk)) {
+		uint64_t cap = n < chunk ? (n < 64 ? 64 : n) : chunk;
+		cudaFree(s->d_apply);
+		cudaFree(s->d_apply_rids);
+		cudaFree(s->d_apply_slots);
+		s->d_apply = nullptr;
+		s->d_apply_rids = nullptr;
+		s->d_apply_slots = nullptr;
+		s->apply_cap = 0;
+		LMD_CUDA_OK(cudaMalloc((void **)&s->d_apply, cap * bb));
+		LMD_CUDA_OK(cudaMalloc((void **)&s->d_apply_rids, cap * sizeof(int64_t)));
+		LMD_CUDA_OK(cudaMalloc((void **)&s->d_apply_slots, cap * sizeof(uint32_t)));
+		s->apply_cap = cap;
+	}
+	// 1. resolve every row id (host side for identity stores, else one lookup kernel per chunk)
+	std::vector<uint32_t> slots(n);
+	if (s->identity) {
+		for (uint64_t i = 0; i < n; i++) {
+			slots[i] = (row_ids[i] >= 0 && (uint64_t)row_ids[i] < s->n) ? (uint32_t)row_ids[i] : LMD_INVALID_SLOT;
+		}
+	} else {
+		for (uint64_t first = 0; first < n; first += s->apply_cap) {
+			const uint64_t now = n - first < s->apply_cap ? n - first : s->apply_cap;
+			LMD_CUDA_OK(cudaMemcpyAsync(s->d_apply_rids, row_ids + first, now * sizeof(int64_t), cudaMemcpyHostToDevice,
+			                            s->stream));
+			lookup_many_kernel<<<(unsigned)((now + 255) / 256), 256, 0, s->stream>>>(
+			    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->d_apply_rids, now, s->d_apply_slots);
+			LMD_CUDA_OK(cudaGetLastError());
+			LMD_CUDA_OK(cudaMemcpyAsync(slots.data() + first, s->d_apply_slots, now * sizeof(uint32_t),
+			                            cudaMemcpyDeviceToHost, s->stream));
+			LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+		}
+	}
+	// 2. new row ids get the next slots in batch order; an earlier block of a repeated row id is dropped
+	std::vector<int64_t> new_rids;
+	{
+		std::unordered_map<int64_t, uint64_t> last; // row id -> index of its last occurrence
+		last.reserve(n * 2);
+		for (uint64_t i = 0; i < n; i++) {
+			last[row_ids[i]] = i;
+		}
+		std::unordered_map<int64_t, uint32_t> fresh;
+		for (uint64_t i = 0; i < n; i++) {
+			if (row_ids[i] == INT64_MAX || row_ids[i] == INT64_MIN || row_ids[i] == INT64_MIN + 1) {
+				set_error("lmd_store_apply: row id %lld is reserved", (long long)row_ids[i]);
+				return LMD_ERR_INVALID_ARG;
+			}
+			if (last[row_ids[i]] != i) {
+				slots[i] = LMD_INVALID_SLOT;
+				continue;
+			}
+			if (slots[i] == LMD_INVALID_SLOT) {
+				slots[i] = (uint32_t)(s->n + new_rids.size());
+				new_rids.push_back(row_ids[i]);
+			}
+		}
+	}
+	if (s->n + new_rids.size() > s->capacity) {
+		set_error("lmd_store_apply: %llu + %llu new nodes exceed the store capacity %llu", (unsigned long long)s->n,
+		          (unsigned long long)new_rids.size(), (unsigned long long)s->capacity);
+		return LMD_ERR_INVALID_ARG;
+	}
+	// 3. stage + scatter the blocks, refresh the views of the overwritten slots
+	const bool rebuild_all = s->dirty || !new_rids.empty(); // a new row id may resolve ids other blocks already hold
+	for (uint64_t first = 0; first < n; first += s->apply_cap) {
+		const uint64_t now = n - first < s->apply_cap ? n - first : s->apply_cap;
+		lmd_status st = copy_to_device(s, s->d_apply, (const uint8_t *)blocks + first * bb, now * bb);
+		if (st != LMD_OK) {
+			return st;
+		}
+		LMD_CUDA_OK(cudaMemcpyAsync(s->d_apply_slots, slots.data() + first, now * sizeof(uint32_t),
+		                            cudaMemcpyHostToDevice, s->stream));
+		scatter_blocks_kernel<<<(unsigned)now, 128, 0, s->stream>>>(s->d_apply, s->d_apply_slots, bb, s->d_blocks);
+		LMD_CUDA_OK(cudaGetLastError());
+		// slots >= s->n are new: store_ingest() below unpacks them; harmless to do it here as well
+		refresh_slots_kernel<<<(unsigned)((now * 32 + 255) / 256), 256, 0, s->stream>>>(
+		    s->d_blocks, bb, s->lay.vector_off, s->lay.count_off, s->lay.ids_off, s->cfg.dims, s->cfg.vec_type,
+		    s->row_floats, s->cfg.r, s->d_apply_slots, now, s->n, s->identity ? 1 : 0, rebuild_all ? 0 : 1,
+		    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->d_vecs, s->d_nbrs);
+		LMD_CUDA_OK(cudaGetLastError());
+		LMD_CUDA_OK(cudaStreamSynchronize(s->stream)); // `slots` / the staging buffer are reused by the next pass
+	}
+	// 4. register the new row ids (row-id map, slot -> row id, packed vectors, pending entry point)
+	if (!new_rids.empty()) {
+		lmd_status st = lmd::store_ingest(s, new_rids.data(), s->n, new_rids.size());
+		if (st != LMD_OK) {
+			return st;
+		}
+		if (out_appended) {
+			*out_appended = new_rids.size();
+		}
+	}
+	return LMD_OK;
+}
+
+// core/GraphManager.cpp:476-499 (HandleNodeDeletion + FreeNode): the row ids leave the row-id map, so every neighbour
+// entry that names them is skipped from now on (Searcher.cpp:120-122,146-156), and a deleted entry point leaves the
+// index without one (searches return nothing until the host sets another, Searcher.cpp:74-77).
+lmd_status lmd_store_remove(lmd_store *s, const int64_t *row_ids, uint64_t n, uint64_t *out_removed) {
+	if (out_removed) {
+		*out_removed = 0;
+	}
+	if (!s || (!row_ids && n)) {
+		set_error("lmd_store_remove: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (n == 0) {
+		return LMD_OK;
+	}
+	if (is_device_ptr(row_ids)) {
+		set_error("lmd_store_remove: row_ids must be host memory");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	int64_t *d_rids = nullptr;
+	LMD_CUDA_OK(cudaMalloc((void **)&d_rids, n * sizeof(int64_t)));
+	unsigned long long *d_removed = s->d_counters + 8;
+	cudaError_t e = cudaMemcpyAsync(d_rids, row_ids, n * sizeof(int64_t), cudaMemcpyHostToDevice, s->stream);
+	if (e == cudaSuccess) {
+		e = cudaMemsetAsync(d_removed, 0, sizeof(unsigned long long), s->stream);
+	}
+	unsigned long long removed = 0;
+	if (e == cudaSuccess) {
+		remove_rowids_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(
+		    (long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, d_rids, n, s->d_row_ids, d_removed);
+		e = cudaGetLastError();
+	}
+	if (e == cudaSuccess) {
+		e = cudaMemcpyAsync(&removed, d_removed, sizeof(removed), cudaMemcpyDeviceToHost, s->stream);
+	}
+	if (e == cudaSuccess) {
+		e = cudaStreamSynchronize(s->stream);
+	}
+	cudaFree(d_rids);
+	LMD_CUDA_OK(e);
+	if (removed) {
+		s->removed += removed;
+		s->identity = false; // slot numbers no longer stand for row ids: resolve through the map
+		s->dirty = true;     // neighbour rows that point at the removed slots are rebuilt before the next search
+	}
+	for (uint64_t i = 0; i < n; i++) {
+		if (row_ids[i] == s->entry_row) { // GraphManager.cpp:477-480
+			s->entry_row = INT64_MAX;
+			s->has_entry = false;
+			s->entry_slot = LMD_INVALID_SLOT;
+		}
+	}
+	if (out_removed) {
+		*out_removed = removed;
+	}
 	return LMD_OK;
 }
 

@@ -108,6 +108,18 @@ void DeviceNodeStore::Upload(const common::row_t *row_ids, common::const_data_pt
 	Check(lmd_store_finalize(store_), "DeviceNodeStore::Upload");
 }
 
+common::idx_t DeviceNodeStore::Apply(const common::row_t *row_ids, common::const_data_ptr_t blocks, common::idx_t n) {
+	uint64_t appended = 0;
+	Check(lmd_store_apply(store_, row_ids, blocks, n, &appended), "DeviceNodeStore::Apply");
+	return appended;
+}
+
+common::idx_t DeviceNodeStore::Remove(const common::row_t *row_ids, common::idx_t n) {
+	uint64_t removed = 0;
+	Check(lmd_store_remove(store_, row_ids, n, &removed), "DeviceNodeStore::Remove");
+	return removed;
+}
+
 void DeviceNodeStore::RefreshBlock(const core::IStorageManager &storage, const core::IGraphManager &graph,
                                    common::row_t row_id) {
 	common::IndexPointer ptr;
@@ -192,6 +204,127 @@ common::idx_t DeviceNodeStore::DeviceBytes() const {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+MirroredStorage::MirroredStorage(core::IStorageManager *inner, std::shared_ptr<DeviceNodeStore> store)
+    : inner_(inner), store_(std::move(store)) {
+	if (!inner_ || !store_) {
+		throw ::duckdb::InternalException("MirroredStorage requires a storage manager and a DeviceNodeStore");
+	}
+}
+
+common::idx_t MirroredStorage::MirrorAll(const core::IGraphManager &graph, const std::vector<common::row_t> &row_ids,
+                                         common::idx_t batch_nodes) {
+	for (common::row_t rid : row_ids) {
+		common::IndexPointer ptr;
+		if (graph.TryGetNodePointer(rid, ptr)) {
+			ptr_to_row_[ptr.Get()] = rid;
+			row_to_ptr_[rid] = ptr.Get();
+		}
+	}
+	return store_->MirrorFrom(*inner_, graph, row_ids, batch_nodes);
+}
+
+common::idx_t MirroredStorage::Flush() {
+	common::idx_t sent = 0;
+	if (!deleted_.empty()) {
+		// deletions first: a row id deleted and re-inserted since the last flush must come back as a NEW node
+		store_->Remove(deleted_.data(), deleted_.size());
+		deleted_.clear();
+	}
+	if (!dirty_order_.empty()) {
+		const common::idx_t bb = store_->BlockBytes();
+		stage_.resize(static_cast<size_t>(dirty_order_.size()) * bb);
+		stage_ids_.clear();
+		for (uint64_t p : dirty_order_) {
+			auto it = ptr_to_row_.find(p);
+			if (it == ptr_to_row_.end()) {
+				continue; // a pointer this mirror never saw allocated or mirrored: not a node block of this index
+			}
+			common::const_data_ptr_t blk = inner_->GetNodeBlockData(common::IndexPointer(p));
+			if (!blk) {
+				continue;
+			}
+			std::memcpy(stage_.data() + stage_ids_.size() * bb, blk, bb);
+			stage_ids_.push_back(it->second);
+		}
+		dirty_order_.clear();
+		dirty_.clear();
+		if (!stage_ids_.empty()) {
+			store_->Apply(stage_ids_.data(), stage_.data(), stage_ids_.size());
+			sent = stage_ids_.size();
+		}
+	}
+	flushes_++;
+	blocks_sent_ += sent;
+	return sent;
+}
+
+void MirroredStorage::LoadIndexContents(const std::string &index_path, core::LmDiskannConfig &config_out,
+                                        core::IGraphManager *graph_manager_out, common::IndexPointer &entry_point_ptr_out,
+                                        common::row_t &entry_point_rowid_out,
+                                        common::IndexPointer &delete_queue_head_out) {
+	inner_->LoadIndexContents(index_path, config_out, graph_manager_out, entry_point_ptr_out, entry_point_rowid_out,
+	                          delete_queue_head_out);
+}
+
+void MirroredStorage::InitializeNewStorage(const std::string &index_path, const core::LmDiskannConfig &config) {
+	inner_->InitializeNewStorage(index_path, config);
+}
+
+void MirroredStorage::SaveIndexContents(const std::string &index_path, const core::LmDiskannConfig &config,
+                                        const core::IGraphManager *graph_manager, common::IndexPointer entry_point_ptr,
+                                        common::row_t entry_point_rowid, common::IndexPointer delete_queue_head) {
+	inner_->SaveIndexContents(index_path, config, graph_manager, entry_point_ptr, entry_point_rowid, delete_queue_head);
+}
+
+common::idx_t MirroredStorage::GetInMemorySize() const {
+	return inner_->GetInMemorySize();
+}
+
+void MirroredStorage::ProcessDeletionQueue(common::IndexPointer &delete_queue_head_ptr) {
+	inner_->ProcessDeletionQueue(delete_queue_head_ptr);
+}
+
+common::const_data_ptr_t MirroredStorage::GetNodeBlockData(common::IndexPointer node_ptr) const {
+	return inner_->GetNodeBlockData(node_ptr);
+}
+
+common::data_ptr_t MirroredStorage::GetMutableNodeBlockData(common::IndexPointer node_ptr) {
+	return inner_->GetMutableNodeBlockData(node_ptr);
+}
+
+void MirroredStorage::EnqueueDeletion(common::row_t row_id, common::IndexPointer &delete_queue_head_ptr) {
+	inner_->EnqueueDeletion(row_id, delete_queue_head_ptr);
+	deleted_.push_back(row_id);
+	auto it = row_to_ptr_.find(row_id);
+	if (it != row_to_ptr_.end()) {
+		// a block dirtied and then deleted before the next search is not sent at all
+		if (dirty_.erase(it->second)) {
+			dirty_order_.erase(std::find(dirty_order_.begin(), dirty_order_.end(), it->second));
+		}
+		ptr_to_row_.erase(it->second);
+		row_to_ptr_.erase(it);
+	}
+}
+
+bool MirroredStorage::AllocateNodeBlock(common::row_t row_id, common::IndexPointer &node_ptr_out,
+                                        common::data_ptr_t &node_data_out) {
+	if (!inner_->AllocateNodeBlock(row_id, node_ptr_out, node_data_out)) {
+		return false;
+	}
+	ptr_to_row_[node_ptr_out.Get()] = row_id;
+	row_to_ptr_[row_id] = node_ptr_out.Get();
+	MarkBlockDirty(node_ptr_out); // GraphManager fills the block right after this call; it is read at Flush() time
+	return true;
+}
+
+void MirroredStorage::MarkBlockDirty(common::IndexPointer node_ptr) {
+	inner_->MarkBlockDirty(node_ptr);
+	if (dirty_.insert(node_ptr.Get()).second) {
+		dirty_order_.push_back(node_ptr.Get());
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 GpuSearcher::GpuSearcher(std::shared_ptr<DeviceNodeStore> store, Route route) : store_(std::move(store)), route_(route) {
 	if (!store_) {
 		throw ::duckdb::InternalException("GpuSearcher requires a DeviceNodeStore");
@@ -202,6 +335,9 @@ void GpuSearcher::Search(const float *query_vector, const core::LmDiskannConfig 
                          core::IGraphManager *graph_manager, common::idx_t k_neighbors,
                          std::vector<common::row_t> &result_row_ids, common::idx_t search_list_size) {
 	result_row_ids.clear();
+	if (mirror_ && mirror_->HasPending()) {
+		mirror_->Flush(); // blocks the host allocated / dirtied / deleted since the last search
+	}
 	if (graph_manager) {
 		// the entry point can move between searches (first insert / deletion, core/GraphManager.cpp:119-121)
 		common::row_t rid = graph_manager->GetEntryPointRowId();
@@ -250,6 +386,9 @@ void GpuSearcher::SearchForInitialCandidates(const float *new_node_vector, commo
 void GpuSearcher::SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors,
                               common::idx_t search_list_size, common::row_t *out_ids, float *out_dist,
                               uint32_t *out_count, lmd_stats *stats) {
+	if (mirror_ && mirror_->HasPending()) {
+		mirror_->Flush();
+	}
 	Check(lmd_search_batch(store_->Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
 	                       static_cast<uint32_t>(search_list_size), static_cast<uint32_t>(route_), 0, out_ids, out_dist,
 	                       out_count, nullptr, stats),

@@ -5,6 +5,10 @@
 //   DeviceNodeStore                                  the HBM mirror behind core/IStorageManager.hpp:156 GetNodeBlockData
 //                                                    and core/IGraphManager.hpp:86 TryGetNodePointer, fed THROUGH those
 //                                                    two interfaces (so any storage backend the reference grows works)
+//   MirroredStorage  : core::IStorageManager       decorator over the host's storage manager that keeps the HBM mirror
+//                                                    live: AllocateNodeBlock / MarkBlockDirty
+//                                                    (core/IStorageManager.hpp:142-177) and EnqueueDeletion (:115) are
+//                                                    forwarded AND recorded; Flush() replays them on the device
 //   GpuIndexScan / GpuScanState                      db/LmDiskannIndex.cpp:639-724 InitializeScan / Scan and
 //                                                    db/LmDiskannScanState.hpp:34-60, minus the DuckDB Vector types
 //   GpuCoordinatorSearch                             core/Coordinator.cpp:63-102 Search (guards + L clamp + rethrow)
@@ -25,6 +29,8 @@
 #include <cstdint>
 #include <memory>
 #include <string>
+#include <unordered_map>
+#include <unordered_set>
 #include <vector>
 
 namespace diskann {
@@ -52,6 +58,10 @@ public:
 	                         const std::vector<common::row_t> &row_ids, common::idx_t batch_nodes = 4096);
 	// Direct bulk load of n contiguous blocks (row_ids == nullptr: row id = position).
 	void Upload(const common::row_t *row_ids, common::const_data_ptr_t blocks, common::idx_t n);
+	// Batch upsert (lmd_store_apply): blocks [n][BlockBytes()] of row_ids [n]; returns how many were new.
+	common::idx_t Apply(const common::row_t *row_ids, common::const_data_ptr_t blocks, common::idx_t n);
+	// core/GraphManager.cpp:476-499 HandleNodeDeletion / FreeNode for a batch; returns how many were present.
+	common::idx_t Remove(const common::row_t *row_ids, common::idx_t n);
 	// core/IStorageManager.hpp:177 MarkBlockDirty: re-mirror one block after the host changed it.
 	void RefreshBlock(const core::IStorageManager &storage, const core::IGraphManager &graph, common::row_t row_id);
 	// core/GraphManager.cpp:468-474: entry point = whatever the graph manager reports now.
@@ -89,6 +99,72 @@ private:
 };
 
 // ---------------------------------------------------------------------------------------------------------------
+// MirroredStorage: the live feeder. Wraps the storage manager the host already has (for DuckDB: the one whose
+// GetNodeBlockData pins a FixedSizeAllocator segment through the BufferManager, libsql/lm_diskann.cpp:720-734) and is
+// handed to GraphManager / Coordinator IN ITS PLACE. Every call is forwarded unchanged; the three calls that change what
+// a search may see are also recorded:
+//   AllocateNodeBlock(row_id, ptr, data)  -> (row_id, ptr) becomes known and dirty
+//   MarkBlockDirty(ptr)                   -> ptr dirty
+//   EnqueueDeletion(row_id, head)         -> row_id removed (Coordinator::Delete, core/Coordinator.cpp:186-212)
+// Flush() reads the dirty blocks through the inner GetNodeBlockData and replays them with one lmd_store_apply +
+// one lmd_store_remove. GpuSearcher calls it before a search when attached (AttachLiveMirror), so the reference's own
+// insert loop - AddNode -> SearchForInitialCandidates -> RobustPrune -> MarkBlockDirty - runs against an up-to-date
+// mirror without knowing about it.
+// ---------------------------------------------------------------------------------------------------------------
+class MirroredStorage : public core::IStorageManager {
+public:
+	MirroredStorage(core::IStorageManager *inner, std::shared_ptr<DeviceNodeStore> store);
+
+	// Initial bulk mirror of `row_ids` (DeviceNodeStore::MirrorFrom) + remembers pointer -> row id for later dirty marks.
+	common::idx_t MirrorAll(const core::IGraphManager &graph, const std::vector<common::row_t> &row_ids,
+	                        common::idx_t batch_nodes = 4096);
+	bool HasPending() const {
+		return !dirty_.empty() || !deleted_.empty();
+	}
+	// Replays the recorded changes on the device. Returns the number of blocks sent.
+	common::idx_t Flush();
+	common::idx_t FlushCount() const {
+		return flushes_;
+	}
+	common::idx_t BlocksSent() const {
+		return blocks_sent_;
+	}
+	DeviceNodeStore &Store() {
+		return *store_;
+	}
+
+	// ---- core::IStorageManager: forwarded ----
+	void LoadIndexContents(const std::string &index_path, core::LmDiskannConfig &config_out,
+	                       core::IGraphManager *graph_manager_out, common::IndexPointer &entry_point_ptr_out,
+	                       common::row_t &entry_point_rowid_out, common::IndexPointer &delete_queue_head_out) override;
+	void InitializeNewStorage(const std::string &index_path, const core::LmDiskannConfig &config) override;
+	void SaveIndexContents(const std::string &index_path, const core::LmDiskannConfig &config,
+	                       const core::IGraphManager *graph_manager, common::IndexPointer entry_point_ptr,
+	                       common::row_t entry_point_rowid, common::IndexPointer delete_queue_head) override;
+	common::idx_t GetInMemorySize() const override;
+	void ProcessDeletionQueue(common::IndexPointer &delete_queue_head_ptr) override;
+	common::const_data_ptr_t GetNodeBlockData(common::IndexPointer node_ptr) const override;
+	common::data_ptr_t GetMutableNodeBlockData(common::IndexPointer node_ptr) override;
+	// ---- forwarded and recorded ----
+	void EnqueueDeletion(common::row_t row_id, common::IndexPointer &delete_queue_head_ptr) override;
+	bool AllocateNodeBlock(common::row_t row_id, common::IndexPointer &node_ptr_out,
+	                       common::data_ptr_t &node_data_out) override;
+	void MarkBlockDirty(common::IndexPointer node_ptr) override;
+
+private:
+	core::IStorageManager *inner_;
+	std::shared_ptr<DeviceNodeStore> store_;
+	std::unordered_map<uint64_t, common::row_t> ptr_to_row_; // IndexPointer::Get() -> row id
+	std::unordered_map<common::row_t, uint64_t> row_to_ptr_;
+	std::vector<uint64_t> dirty_order_;                      // first-dirtied order (appends keep insertion order)
+	std::unordered_set<uint64_t> dirty_;
+	std::vector<common::row_t> deleted_;
+	std::vector<uint8_t> stage_;
+	std::vector<common::row_t> stage_ids_;
+	common::idx_t flushes_ = 0, blocks_sent_ = 0;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
 // GpuSearcher: drop-in for core::Searcher behind core::ISearcher.
 // ---------------------------------------------------------------------------------------------------------------
 class GpuSearcher : public core::ISearcher {
@@ -122,9 +198,14 @@ public:
 	DeviceNodeStore &Store() {
 		return *store_;
 	}
+	// Pending changes of `mirror` are flushed to the device before every search (nullptr detaches).
+	void AttachLiveMirror(MirroredStorage *mirror) {
+		mirror_ = mirror;
+	}
 
 private:
 	std::shared_ptr<DeviceNodeStore> store_;
+	MirroredStorage *mirror_ = nullptr;
 	Route route_;
 	common::row_t synced_entry_ = 0;
 	bool entry_synced_ = false;

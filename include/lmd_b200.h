@@ -106,6 +106,19 @@ lmd_status lmd_store_destroy(lmd_store *s);
 lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n);
 /* Re-uploads one block that the host marked dirty (core/IStorageManager.hpp MarkBlockDirty). */
 lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block);
+/* Live mirror. Batch form of what the reference's graph code does to storage between two
+ * searches - AllocateNodeBlock for new rows, GetMutableNodeBlockData + MarkBlockDirty for changed ones
+ * (core/IStorageManager.hpp:142-177; callers core/GraphManager.cpp:81-160,430-444): the host passes every block it
+ * created or dirtied. Known row ids overwrite their mirrored block, unknown ones are appended in batch order
+ * (*out_appended, may be NULL); a row id given twice keeps its last block. row_ids: host memory; blocks: host
+ * (pageable / pinned) or device memory. Only the views of the touched blocks are rebuilt unless a row id was new. */
+lmd_status lmd_store_apply(lmd_store *s, const int64_t *row_ids, const void *blocks, uint64_t n,
+                           uint64_t *out_appended);
+/* core/GraphManager.cpp:476-499 HandleNodeDeletion + FreeNode: the row ids leave the row-id map. Neighbour entries
+ * naming them are skipped from the next search on (core/Searcher.cpp:120-122,146-156); removing the entry point
+ * leaves the store without one (empty results, Searcher.cpp:74-77) until lmd_store_set_entry. Unknown row ids are
+ * ignored; *out_removed (may be NULL) = how many were present. The slots are not reused. row_ids: host memory. */
+lmd_status lmd_store_remove(lmd_store *s, const int64_t *row_ids, uint64_t n, uint64_t *out_removed);
 /* core/GraphManager.cpp:468-474 GetEntryPointRowId/Pointer. Unknown row id => searches return empty
  * results (Searcher.cpp:74-77). */
 lmd_status lmd_store_set_entry(lmd_store *s, int64_t row_id);
@@ -165,7 +178,8 @@ typedef struct {
  * them, GraphManager.cpp:96-108: memcpy or a plain cast to int8). Blocks get neighbour count 0. */
 lmd_status lmd_store_upload_vectors(lmd_store *s, const int64_t *row_ids, const float *vectors, uint64_t n);
 /* (Re)builds the graph over every node in the store; the first node is the entry point (GraphManager.cpp:119-121).
- * Rewrites count / ids / planes of every mirrored block and the search views. stats may be NULL. */
+ * Rewrites count / ids / planes of every mirrored block and the search views. stats may be NULL.
+ * LMD_ERR_UNSUPPORTED on a store that had rows removed (their slots still hold blocks). */
 lmd_status lmd_build_graph(lmd_store *s, const lmd_build_params *params, lmd_build_stats *stats);
 /* RobustPrune of m nodes in one launch. node_row_ids [m]; cand_row_ids [m][c] (INT64_MAX = no candidate; unknown row
  * ids, duplicates and the node itself are skipped as the reference skips them); out_ids [m][r] INT64_MAX padded;

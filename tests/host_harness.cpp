@@ -6,8 +6,10 @@
 // store/IShadowStorageService.hpp:13-16 anticipates. Built by duckdb-lm-diskann_b200/host/Makefile.
 #include "gpu_searcher.hpp"
 
+#include "core/GraphManager.hpp"
 #include "core/GraphNode.hpp"
 
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -152,6 +154,69 @@ struct Host {
 	std::unique_ptr<core::ISearcher> searcher; // held through the reference's interface, as Coordinator.hpp:115-118 does
 	std::unique_ptr<b200::GpuIndexScan> scan;
 	bool loaded = true;
+};
+
+// Growable storage for the live-index test: blocks handed out of one buffer, IndexPointer value = slot + 1.
+class GrowStorage : public core::IStorageManager {
+public:
+	GrowStorage(uint64_t capacity, uint64_t bb) : data_(capacity * bb), cap_(capacity), bb_(bb) {
+	}
+	bool AllocateNodeBlock(common::row_t, common::IndexPointer &ptr_out, common::data_ptr_t &data_out) override {
+		if (used_ >= cap_) {
+			return false;
+		}
+		ptr_out = common::IndexPointer(used_ + 1);
+		data_out = data_.data() + used_ * bb_;
+		used_++;
+		return true;
+	}
+	common::const_data_ptr_t GetNodeBlockData(common::IndexPointer p) const override {
+		uint64_t v = p.Get();
+		return (v == 0 || v > used_) ? nullptr : data_.data() + (v - 1) * bb_;
+	}
+	common::data_ptr_t GetMutableNodeBlockData(common::IndexPointer p) override {
+		uint64_t v = p.Get();
+		return (v == 0 || v > used_) ? nullptr : data_.data() + (v - 1) * bb_;
+	}
+	void MarkBlockDirty(common::IndexPointer) override {
+		marks_++;
+	}
+	void LoadIndexContents(const std::string &, core::LmDiskannConfig &, core::IGraphManager *, common::IndexPointer &,
+	                       common::row_t &, common::IndexPointer &) override {
+	}
+	void InitializeNewStorage(const std::string &, const core::LmDiskannConfig &) override {
+	}
+	void SaveIndexContents(const std::string &, const core::LmDiskannConfig &, const core::IGraphManager *,
+	                       common::IndexPointer, common::row_t, common::IndexPointer) override {
+	}
+	common::idx_t GetInMemorySize() const override {
+		return used_ * bb_;
+	}
+	void EnqueueDeletion(common::row_t, common::IndexPointer &) override {
+		deletions_++;
+	}
+	void ProcessDeletionQueue(common::IndexPointer &) override {
+	}
+	uint64_t marks_ = 0, deletions_ = 0;
+
+private:
+	std::vector<uint8_t> data_;
+	uint64_t cap_, bb_, used_ = 0;
+};
+
+// The reference's OWN core::GraphManager (AddNode, RobustPrune, HandleNodeDeletion ...) running on top of
+// MirroredStorage(GrowStorage) with GpuSearcher as its ISearcher: the index a host keeps while rows come and go.
+struct LiveHost {
+	core::LmDiskannConfig cfg;
+	core::NodeLayoutOffsets lay;
+	uint64_t bb = 0;
+	std::unique_ptr<GrowStorage> inner;
+	std::shared_ptr<b200::DeviceNodeStore> store;
+	std::unique_ptr<b200::MirroredStorage> storage;
+	std::unique_ptr<b200::GpuSearcher> searcher;
+	std::unique_ptr<core::GraphManager> graph;
+	std::vector<common::row_t> inserted; // insertion order
+	common::IndexPointer delete_queue_head;
 };
 
 template <typename F>
@@ -341,6 +406,132 @@ int lmdhost_rewrite_block(void *p, int64_t row_id, const uint8_t *block, uint64_
 		h->storage->MarkBlockDirty(ptr);
 		h->store->RefreshBlock(*h->storage, *h->graph, row_id);
 	});
+}
+
+// ---- live index ---------------------------------------------------------------------
+void *lmdlive_create(int metric, int vec_type, uint64_t dims, uint32_t r, uint32_t l_insert, float alpha,
+                     uint32_t l_search, uint64_t capacity, int device) {
+	LiveHost *out = nullptr;
+	int rc = Guard([&]() {
+		auto h = std::make_unique<LiveHost>();
+		h->cfg.metric_type = static_cast<common::LmDiskannMetricType>(metric);
+		h->cfg.node_vector_type = static_cast<common::LmDiskannVectorType>(vec_type);
+		h->cfg.dimensions = dims;
+		h->cfg.r = r;
+		h->cfg.l_insert = l_insert;
+		h->cfg.alpha = alpha;
+		h->cfg.l_search = l_search;
+		h->lay = core::CalculateLayoutInternal(h->cfg);
+		h->bb = (h->lay.total_node_size + 4095) / 4096 * 4096; // db/LmDiskannIndex.cpp:161-162
+		h->inner = std::make_unique<GrowStorage>(capacity, h->bb);
+		h->store = std::make_shared<b200::DeviceNodeStore>(h->cfg, capacity, device, h->bb);
+		h->storage = std::make_unique<b200::MirroredStorage>(h->inner.get(), h->store);
+		h->searcher = std::make_unique<b200::GpuSearcher>(h->store);
+		h->searcher->AttachLiveMirror(h->storage.get());
+		// GraphManager sees only the two interfaces, exactly as Coordinator wires them (core/Coordinator.hpp:115-118)
+		h->graph = std::make_unique<core::GraphManager>(h->cfg, h->lay, h->bb, h->storage.get(), h->searcher.get());
+		out = h.release();
+	});
+	return rc == 0 ? out : nullptr;
+}
+
+void lmdlive_destroy(void *p) {
+	delete static_cast<LiveHost *>(p);
+}
+
+// core::GraphManager::AddNode per row (core/Coordinator.cpp Insert -> GraphManager.cpp:65-203)
+int lmdlive_insert(void *p, const int64_t *row_ids, const float *vectors, uint64_t n) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	return Guard([&]() {
+		for (uint64_t i = 0; i < n; i++) {
+			common::IndexPointer ptr;
+			if (!h->graph->AddNode(row_ids[i], vectors + i * h->cfg.dimensions, h->cfg.dimensions, ptr)) {
+				throw std::runtime_error("AddNode failed");
+			}
+			// a row id that was deleted and comes back counts once, at its new position
+			h->inserted.erase(std::remove(h->inserted.begin(), h->inserted.end(), row_ids[i]), h->inserted.end());
+			h->inserted.push_back(row_ids[i]);
+		}
+	});
+}
+
+// core/Coordinator.cpp:186-212 Delete, the three steps that concern storage and graph
+int lmdlive_delete(void *p, const int64_t *row_ids, uint64_t n) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	return Guard([&]() {
+		for (uint64_t i = 0; i < n; i++) {
+			h->storage->EnqueueDeletion(row_ids[i], h->delete_queue_head);
+			h->graph->HandleNodeDeletion(row_ids[i]);
+			h->graph->FreeNode(row_ids[i]);
+		}
+	});
+}
+
+int lmdlive_set_entry(void *p, int64_t row_id) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	return Guard([&]() {
+		common::IndexPointer ptr;
+		if (!h->graph->TryGetNodePointer(row_id, ptr)) {
+			throw ::duckdb::InvalidInputException("unknown row id");
+		}
+		h->graph->SetEntryPoint(ptr, row_id);
+	});
+}
+
+// Batched search on the live mirror; the entry point is whatever the reference's graph manager reports now.
+int lmdlive_search(void *p, const float *queries, uint64_t nq, uint64_t k, uint64_t L, int64_t *out_ids,
+                   uint32_t *out_count) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	return Guard([&]() {
+		h->storage->Flush();
+		h->store->SyncEntryPoint(*h->graph);
+		h->searcher->SearchBatch(queries, nq, k, L, out_ids, nullptr, out_count, nullptr);
+	});
+}
+
+// One query through core::ISearcher::Search (flushes pending changes by itself).
+int lmdlive_search_one(void *p, const float *query, uint64_t k, uint64_t L, int64_t *out_ids, uint64_t *out_n) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	return Guard([&]() {
+		std::vector<common::row_t> res;
+		core::ISearcher *s = h->searcher.get();
+		s->Search(query, h->cfg, h->graph.get(), k, res, L);
+		*out_n = res.size();
+		std::copy(res.begin(), res.end(), out_ids);
+	});
+}
+
+// The HOST's view: blocks of every live row id in insertion order + the graph manager's entry point.
+int lmdlive_export(void *p, uint8_t *out_blocks, int64_t *out_row_ids, uint64_t *out_n, int64_t *entry_out,
+                   uint64_t *block_bytes_out) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	return Guard([&]() {
+		uint64_t m = 0;
+		for (common::row_t rid : h->inserted) {
+			common::IndexPointer ptr;
+			if (!h->graph->TryGetNodePointer(rid, ptr)) {
+				continue; // deleted
+			}
+			if (out_blocks) {
+				std::memcpy(out_blocks + m * h->bb, h->inner->GetNodeBlockData(ptr), h->bb);
+				out_row_ids[m] = rid;
+			}
+			m++;
+		}
+		*out_n = m;
+		*entry_out = h->graph->GetEntryPointPointer() == common::IndexPointer()
+		                 ? common::NumericLimits<common::row_t>::Maximum()
+		                 : h->graph->GetEntryPointRowId();
+		*block_bytes_out = h->bb;
+	});
+}
+
+void lmdlive_counters(void *p, uint64_t *flushes, uint64_t *blocks_sent, uint64_t *marks, uint64_t *device_nodes) {
+	LiveHost *h = static_cast<LiveHost *>(p);
+	*flushes = h->storage->FlushCount();
+	*blocks_sent = h->storage->BlocksSent();
+	*marks = h->inner->marks_;
+	*device_nodes = h->store->NodeCount();
 }
 
 } // extern "C"

@@ -347,3 +347,79 @@ def test_recall_matches_oracle_10k(lmd, oracle, fixtures_mod):
     assert rg == ro, (rg, ro)
     assert rg >= 0.9, rg
     del torch
+
+
+# ---- live mirror: lmd_store_apply / lmd_store_remove ---------------------------------
+@pytest.mark.parametrize("sparse_ids", [False, True])
+def test_apply_and_remove_track_the_host_blocks(lmd, oracle, make_index, fixtures_mod, sparse_ids):
+    """The host's storage changes between searches (new rows, re-pruned neighbour lists, deletions); after
+    apply()/remove() the mirror must search exactly like the CPU reference semantics on the host's CURRENT blocks."""
+    n, dims, r, k, L = 2400, 64, 16, 10, 48
+    rng = np.random.default_rng(5)
+    rid = None
+    if sparse_ids:
+        rid = np.sort(rng.choice(np.arange(5, 20 * n, dtype=np.int64), size=n, replace=False))
+        rid[0], rid[7] = rid[7], rid[0]  # not monotone either
+    ix = make_index(n, dims, r, metric="L2", kind="clustered", nq=64, row_ids=rid)
+    rid = np.arange(n, dtype=np.int64) if rid is None else rid
+    blocks, bb, q, lay = ix["blocks_np"], ix["block_bytes"], ix["queries"], ix["layout"]
+    n0 = 1500  # the index as first mirrored: later rows are unknown ids inside the early blocks -> skipped
+
+    def check(s, live, blk, entry, what):
+        ids, dist, cnt, _ = s.search(q, k, L)
+        o = oracle.search(blk[live], bb, dims, r, q, k, L, row_ids=rid[live], entry_row_id=int(entry))
+        check_parity(ids, dist, cnt, o[0], o[1], o[2], what=what)
+        return ids
+
+    with lmd.Store(dims, r, capacity=n + 8, l_search=100) as s:
+        s.upload(blocks[:n0], row_ids=rid[:n0])
+        s.set_entry(rid[0])
+        live = np.arange(n0)
+        check(s, live, blocks, rid[0], "initial")
+        # 1. inserts: 900 new rows arrive in three batches (each batch = new blocks only; old blocks unchanged)
+        for lo, hi in ((n0, 1800), (1800, 1801), (1801, n)):
+            assert s.apply(rid[lo:hi], blocks[lo:hi]) == hi - lo
+            live = np.arange(hi)
+            check(s, live, blocks, rid[0], "after insert up to %d" % hi)
+        assert s.node_count == n
+        # 2. dirty blocks: re-wire 300 existing nodes (shuffled neighbour lists cut to a random count), one of them
+        #    given twice in the batch with the LAST version the valid one; none are new
+        cur = blocks.copy()
+        touched = rng.choice(n, size=300, replace=False)
+        for t in touched:
+            ids_view = cur[t, lay["ids_off"]:lay["ids_off"] + 8 * r].view(np.int64)
+            cnt_t = int(cur[t, 0:2].view(np.uint16)[0])
+            perm = rng.permutation(cnt_t)
+            ids_view[:cnt_t] = ids_view[:cnt_t][perm]
+            cur[t, 0:2] = np.array([rng.integers(1, cnt_t + 1)], dtype=np.uint16).view(np.uint8)
+        stale = blocks[touched[:1]].copy()
+        stale[0, 0:2] = 0
+        batch_ids = np.concatenate([rid[touched[:1]], rid[touched]])
+        batch_blk = np.concatenate([stale, cur[touched]])
+        assert s.apply(batch_ids, batch_blk) == 0
+        check(s, live, cur, rid[0], "after dirty blocks")
+        assert np.array_equal(s.download_block(rid[touched[0]]), cur[touched[0]])
+        # 3. deletions (GraphManager.cpp:476-499): 200 rows leave; rows that still name them skip them
+        gone = rng.choice(np.arange(1, n), size=200, replace=False)
+        assert s.remove(np.concatenate([rid[gone], [-12345]])) == 200
+        assert s.remove(rid[gone[:5]]) == 0  # already gone
+        live = np.setdiff1d(np.arange(n), gone)
+        got = check(s, live, cur, rid[0], "after deletions")
+        assert not np.isin(got, rid[gone]).any()
+        # 4. the entry point is deleted: no entry -> empty results (Searcher.cpp:74-77) until the host picks another
+        assert s.remove(rid[:1]) == 1
+        ids, dist, cnt, _ = s.search(q, k, L)
+        assert (cnt == 0).all() and (ids == -1).all()
+        live = live[live != 0]
+        s.set_entry(rid[live[3]])
+        check(s, live, cur, rid[live[3]], "new entry point")
+        # 5. a deleted row id comes back as a NEW node with a different block
+        back = gone[:3]
+        newblk = cur[back].copy()
+        assert s.apply(rid[back], newblk) == 3
+        live = np.concatenate([live, back])  # appended at the end of the mirror, and of the oracle's block array
+        check(s, live, cur, rid[live[3]], "re-inserted rows")
+        # capacity is enforced before anything is written
+        with pytest.raises(lmd.LmdError):
+            s.apply(np.arange(10**9, 10**9 + 50, dtype=np.int64), np.zeros((50, bb), dtype=np.uint8))
+        check(s, live, cur, rid[live[3]], "after the refused batch")

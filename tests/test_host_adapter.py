@@ -41,6 +41,17 @@ def _lib():
     l.lmdhost_initial_candidates.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
     l.lmdhost_rewrite_block.argtypes = [P, C.c_int64, P, C.c_uint64]
     l.lmdhost_build_and_write_back.argtypes = [P, C.c_uint32, C.c_float, C.c_uint64, P, C.c_uint64, C.c_uint64, P, P]
+    l.lmdlive_create.restype = P
+    l.lmdlive_create.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.c_float, C.c_uint32,
+                                 C.c_uint64, C.c_int]
+    l.lmdlive_destroy.argtypes = [P]
+    l.lmdlive_insert.argtypes = [P, P, P, C.c_uint64]
+    l.lmdlive_delete.argtypes = [P, P, C.c_uint64]
+    l.lmdlive_set_entry.argtypes = [P, C.c_int64]
+    l.lmdlive_search.argtypes = [P, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P]
+    l.lmdlive_search_one.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
+    l.lmdlive_export.argtypes = [P, P, P, P, P, P]
+    l.lmdlive_counters.argtypes = [P, P, P, P, P]
     return l
 
 
@@ -108,7 +119,8 @@ def test_host_libraries_load():
     syms = subprocess.run(["nm", "-DC", os.path.join(HOST_DIR, "liblmd_host.so")], capture_output=True, text=True).stdout
     for s in ("diskann::b200::GpuSearcher::Search(", "diskann::b200::GpuSearcher::SearchBatch(",
               "diskann::b200::DeviceNodeStore::MirrorFrom(", "diskann::b200::GpuIndexScan::Scan(",
-              "diskann::b200::GpuCoordinatorSearch("):
+              "diskann::b200::GpuCoordinatorSearch(", "diskann::b200::MirroredStorage::Flush(",
+              "diskann::b200::MirroredStorage::MarkBlockDirty(", "diskann::b200::DeviceNodeStore::Apply("):
         assert s in syms, s
     assert "typeinfo for diskann::core::ISearcher" in syms  # GpuSearcher derives from the reference's interface
 
@@ -286,3 +298,119 @@ def test_build_graph_and_write_back_through_the_interfaces(oracle, fixtures_mod)
         # ... and the adapter's own searches (now on the built store) return the same rows
         err, ids, cnt_q, _ = h.multi_scan(q, 10)
         assert err is None and (ids == o[0]).all(axis=1).mean() >= 0.97
+
+
+class Live:
+    """tests/host_harness.cpp LiveHost: the reference's own core::GraphManager on MirroredStorage + GpuSearcher."""
+
+    def __init__(self, lib, dims, r, metric=1, l_insert=32, alpha=1.2, l_search=40, capacity=4096):
+        self.lib, self.dims = lib, dims
+        self.h = lib.lmdlive_create(metric, 1, dims, r, l_insert, alpha, l_search, capacity, 0)
+        if not self.h:
+            raise RuntimeError("lmdlive_create: " + lib.lmdhost_last_error().decode())
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.lib.lmdlive_destroy(self.h)
+        self.h = None
+
+    def _ok(self, rc):
+        assert rc == 0, self.lib.lmdhost_last_error().decode()
+
+    def insert(self, row_ids, x):
+        rid = np.ascontiguousarray(row_ids, dtype=np.int64)
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        self._ok(self.lib.lmdlive_insert(self.h, rid.ctypes.data, x.ctypes.data, rid.size))
+
+    def delete(self, row_ids):
+        rid = np.ascontiguousarray(row_ids, dtype=np.int64)
+        self._ok(self.lib.lmdlive_delete(self.h, rid.ctypes.data, rid.size))
+
+    def set_entry(self, row_id):
+        self._ok(self.lib.lmdlive_set_entry(self.h, int(row_id)))
+
+    def search(self, q, k, L):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        ids = np.full((q.shape[0], k), -1, dtype=np.int64)
+        cnt = np.zeros(q.shape[0], dtype=np.uint32)
+        self._ok(self.lib.lmdlive_search(self.h, q.ctypes.data, q.shape[0], k, L, ids.ctypes.data, cnt.ctypes.data))
+        return ids, cnt
+
+    def search_one(self, q, k, L):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        out = np.full(k, -1, dtype=np.int64)
+        n = C.c_uint64(0)
+        self._ok(self.lib.lmdlive_search_one(self.h, q.ctypes.data, k, L, out.ctypes.data, C.addressof(n)))
+        return out[:n.value]
+
+    def export(self):
+        n, entry, bb = C.c_uint64(0), C.c_int64(0), C.c_uint64(0)
+        self._ok(self.lib.lmdlive_export(self.h, None, None, C.addressof(n), C.addressof(entry), C.addressof(bb)))
+        blocks = np.zeros((n.value, bb.value), dtype=np.uint8)
+        rid = np.zeros(n.value, dtype=np.int64)
+        self._ok(self.lib.lmdlive_export(self.h, blocks.ctypes.data, rid.ctypes.data, C.addressof(n),
+                                         C.addressof(entry), C.addressof(bb)))
+        return blocks, rid, entry.value, bb.value
+
+    def counters(self):
+        v = [C.c_uint64(0) for _ in range(4)]
+        self.lib.lmdlive_counters(self.h, *[C.addressof(x) for x in v])
+        return dict(zip(("flushes", "blocks_sent", "marks", "device_nodes"), (x.value for x in v)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric", ["L2", "COSINE"])
+def test_live_mirror_under_the_reference_graph_manager(oracle, fixtures_mod, metric):
+    """Row f2. The reference's OWN insert loop (core::GraphManager::AddNode -> ISearcher::SearchForInitialCandidates ->
+    RobustPrune -> MarkBlockDirty) runs with GpuSearcher as its searcher and MirroredStorage as its storage manager:
+    every candidate search happens on the device against a mirror that the decorator keeps current. The host's blocks
+    must come out as the CPU reference builds them, and searches on the mirror must equal the CPU search on the host's
+    blocks at every point of the index's life (inserts, deletions, entry-point change, re-insertion)."""
+    n, dims, r, l_insert, k, L = 700, 32, 12, 32, 10, 40
+    m = METRIC[metric]
+    x = fixtures_mod.make_dataset(n, dims, kind="clustered", seed=21, normalize=(metric == "COSINE"))
+    q = fixtures_mod.make_dataset(40, dims, kind="clustered", seed=22, normalize=(metric == "COSINE"))
+    rid = np.random.default_rng(3).choice(np.arange(100, 50 * n, dtype=np.int64), size=n, replace=False)
+
+    def check(lv, what):
+        blocks, live_rid, entry, bb = lv.export()
+        ids, cnt = lv.search(q, k, L)
+        o = oracle.search(blocks, bb, dims, r, q, k, L, metric=m, row_ids=live_rid, entry_row_id=entry)
+        assert np.array_equal(cnt, o[2]), what
+        same = (ids == o[0]).all(axis=1).mean()
+        assert same >= 0.97, "%s: only %.3f of the queries ID-identical" % (what, same)
+        return blocks, live_rid, entry
+
+    with Live(_lib(), dims, r, metric=m, l_insert=l_insert, l_search=L, capacity=n + 16) as lv:
+        n1 = 500
+        lv.insert(rid[:n1], x[:n1])
+        blocks, live_rid, entry = check(lv, "after 500 inserts")
+        assert entry == rid[0] and np.array_equal(live_rid, rid[:n1])
+        # the host's blocks equal a serial CPU build of the same rows (reference AddNode + patched Searcher, H1-H5)
+        want, want_entry = oracle.build_serial(x[:n1], r, l_insert=l_insert, alpha=1.2, metric=m, row_ids=rid[:n1])
+        assert want_entry == entry
+        same_blocks = (blocks == want).all(axis=1).mean()
+        assert same_blocks >= 0.95, "only %.3f of the host blocks equal the CPU build" % same_blocks
+        c = lv.counters()
+        # one flush per candidate search (every AddNode after the first), and far fewer blocks than a re-mirror each time
+        assert c["device_nodes"] == n1 and n1 - 1 <= c["flushes"] <= n1 + 2
+        assert c["blocks_sent"] <= c["marks"] + n1 and c["blocks_sent"] < n1 * (r + 2)
+        # single-query path (ISearcher::Search) flushes by itself
+        one = lv.search_one(q[0], k, L)
+        o = oracle.search(blocks, blocks.shape[1], dims, r, q[:1], k, L, metric=m, row_ids=live_rid, entry_row_id=entry)
+        assert np.array_equal(one, o[0][0][:len(one)]) and len(one) == o[2][0]
+        # deletions through Coordinator::Delete's steps, including the entry point
+        gone = np.concatenate([rid[:1], rid[50:90]])
+        lv.delete(gone)
+        ids, cnt = lv.search(q, k, L)
+        assert (cnt == 0).all()  # no entry point: empty results (core/Searcher.cpp:74-77)
+        lv.set_entry(rid[1])
+        check(lv, "after deleting 41 rows and moving the entry point")
+        # more inserts on top (their candidate searches see the deletions), one of them a row id that was deleted
+        lv.insert(rid[n1:], x[n1:])
+        lv.insert(rid[60:61], x[60:61])
+        blocks, live_rid, entry = check(lv, "after 200 more inserts")
+        assert live_rid.size == n - 41 + 1 and live_rid[-1] == rid[60] and entry == rid[1]
+        assert not np.isin(lv.search(q, k, L)[0], np.setdiff1d(gone, rid[60:61])).any()
