@@ -88,6 +88,11 @@ SYMBOLS = [
     ("lmd_store_device_bytes", C.c_uint64, [_P]),
     ("lmd_search_batch", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P,
                                     _P, C.POINTER(Stats)]),
+    ("lmd_filter_create", C.c_int32, [_P, _P, C.c_uint64, C.POINTER(_P)]),
+    ("lmd_filter_destroy", C.c_int32, [_P]),
+    ("lmd_filter_count", C.c_uint64, [_P]),
+    ("lmd_search_batch_filtered", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                             _P, _P, _P, _P, C.POINTER(Stats)]),
     ("lmd_merge_topk", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P]),
     ("lmd_store_upload_vectors", C.c_int32, [_P, _P, _P, C.c_uint64]),
     ("lmd_build_graph", C.c_int32, [_P, C.POINTER(BuildParams), C.POINTER(BuildStats)]),
@@ -264,20 +269,30 @@ class Store:
     def device_bytes(self):
         return int(lib().lmd_store_device_bytes(self._h))
 
+    def make_filter(self, allowed_row_ids):
+        """allowed_ids set of a filtered search (row f4) -> Filter (close() it, or use `with`)."""
+        return Filter(self, allowed_row_ids)
+
     def search_raw(self, queries, nq, k, L=0, route=ROUTE_EXACT, flags=0, out_ids=None, out_dist=None, out_count=None,
-                   out_qstats=None, stats=True):
+                   out_qstats=None, stats=True, filter=None):
         """Thin call: any mix of numpy arrays / torch tensors / raw addresses. stats=False passes a NULL lmd_stats
         (the call still synchronises unless SEARCH_ASYNC is set) and returns None."""
+        if filter is not None:
+            def call(*a):
+                return lib().lmd_search_batch_filtered(self._h, filter._h, *a)
+        else:
+            def call(*a):
+                return lib().lmd_search_batch(self._h, *a)
         if (flags & SEARCH_ASYNC) or not stats:
-            _check(lib().lmd_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids),
-                                          _ptr(out_dist), _ptr(out_count), _ptr(out_qstats), None))
+            _check(call(_ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist), _ptr(out_count),
+                        _ptr(out_qstats), None))
             return None
         st = Stats()
-        _check(lib().lmd_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist),
-                                      _ptr(out_count), _ptr(out_qstats), C.byref(st)))
+        _check(call(_ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist), _ptr(out_count),
+                    _ptr(out_qstats), C.byref(st)))
         return st
 
-    def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0, qstats=False):
+    def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0, qstats=False, filter=None):
         """Host-buffer search: queries [nq, dims] float32 numpy -> (ids [nq,k] int64, dist [nq,k] f32,
         count [nq] u32, Stats[, qstats [nq,2] u32])."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
@@ -292,8 +307,39 @@ class Store:
         qs = np.zeros((nq, 2), dtype=np.uint32) if qstats else None
         if qstats:
             flags |= SEARCH_PER_QUERY_STATS
-        st = self.search_raw(q, nq, k, L, route, flags, ids, dist, count, qs)
+        st = self.search_raw(q, nq, k, L, route, flags, ids, dist, count, qs, filter=filter)
         return (ids, dist, count, st, qs) if qstats else (ids, dist, count, st)
+
+
+class Filter:
+    """lmd_filter: an allowed-ids set resolved to the store's slots."""
+
+    def __init__(self, store, allowed_row_ids):
+        rid = allowed_row_ids if hasattr(allowed_row_ids, "data_ptr") else \
+            np.ascontiguousarray(allowed_row_ids, dtype=np.int64)
+        self._h = _P()
+        self._keep = store
+        _check(lib().lmd_filter_create(store._h, _ptr(rid), int(rid.shape[0]), C.byref(self._h)))
+
+    @property
+    def count(self):
+        return int(lib().lmd_filter_count(self._h))
+
+    def close(self):
+        try:
+            if self._h:
+                lib().lmd_filter_destroy(self._h)
+                self._h = _P()
+        except TypeError:
+            pass
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
 
 
 def merge_topk(ids, dist, shards, nq, k, out_ids, out_dist, device=0):

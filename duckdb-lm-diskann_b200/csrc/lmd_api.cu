@@ -67,11 +67,9 @@ lmd_status grow(T *&ptr, uint64_t &have, uint64_t need_elems, lmd_store *s) {
 
 } // namespace
 
-extern "C" {
-
-lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
-                            uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
-                            uint32_t *out_qstats, lmd_stats *stats) {
+static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const float *queries, uint64_t nq, uint32_t k,
+                       uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids, float *out_dist,
+                       uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats) {
 	if (stats) {
 		memset(stats, 0, sizeof(*stats));
 	}
@@ -120,6 +118,11 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 		}
 	}
 	std::lock_guard<std::mutex> g(s->mu);
+	if (filter && (filter->store != s || filter->epoch != s->epoch)) {
+		set_error("lmd_search_batch_filtered: the filter was built for another store or before rows were added / "
+		          "removed; create it again");
+		return LMD_ERR_STATE;
+	}
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	cudaStream_t st = s->stream;
 	const uint32_t q32 = (uint32_t)nq;
@@ -203,6 +206,7 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 	ta.d_out_count = separate ? nullptr : d_count;
 	ta.d_qstats = d_qstats;
 	ta.d_cand = d_cand;
+	ta.d_allowed = filter ? filter->d_bits : nullptr;
 	if (!async) {
 		LMD_CUDA_OK(cudaEventRecord(s->ev[1], st));
 	}
@@ -292,6 +296,24 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
 		stats->algorithmic_bytes = bytes;
 	}
 	return LMD_OK;
+}
+
+extern "C" {
+
+lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
+                            uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                            uint32_t *out_qstats, lmd_stats *stats) {
+	return search_impl(s, nullptr, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
+}
+
+lmd_status lmd_search_batch_filtered(lmd_store *s, const lmd_filter *filter, const float *queries, uint64_t nq,
+                                     uint32_t k, uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids,
+                                     float *out_dist, uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats) {
+	if (!filter) {
+		set_error("lmd_search_batch_filtered: null filter");
+		return LMD_ERR_INVALID_ARG;
+	}
+	return search_impl(s, filter, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
 }
 
 lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq, uint32_t k,

@@ -127,6 +127,7 @@ struct lmd_store {
 	int64_t *d_apply_rids = nullptr;
 	uint32_t *d_apply_slots = nullptr;
 	uint64_t apply_cap = 0; // blocks
+	uint64_t epoch = 0;     // bumped whenever the row id -> slot mapping may have changed (filters are tied to it)
 	uint64_t removed = 0;   // row ids taken out by lmd_store_remove (their slots stay allocated)
 
 	// graph-build scratch (lmd_build.cu), allocated on first use and kept
@@ -139,6 +140,15 @@ struct lmd_store {
 	lmd::Tuning tune;
 	mutable std::unordered_map<uint64_t, std::pair<int, int>> launch_cache; // (kernel, smem) -> (warps per CTA, CTAs per SM)
 	std::mutex mu;
+};
+
+// An allowed-ids set resolved to the store's slots (filtered search).
+struct lmd_filter {
+	lmd_store *store = nullptr;
+	uint32_t *d_bits = nullptr; // [(capacity + 31) / 32]
+	uint64_t words = 0;
+	uint64_t count = 0; // distinct allowed row ids that are in the store
+	uint64_t epoch = 0;
 };
 
 namespace lmd {
@@ -159,6 +169,7 @@ struct TraverseArgs {
 	uint32_t *d_out_count;
 	uint32_t *d_qstats;   // [nq][2] or null
 	uint64_t *d_cand;     // [nq][L] or null
+	const uint32_t *d_allowed = nullptr; // filtered search: bitmap over slots, null = unfiltered
 };
 lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st);
 

@@ -2,6 +2,7 @@
 //   -DLMD_INST_KIND=0 -DLMD_INST_METRIC=<1|2|3> -DLMD_INST_ROUTE=<0|1>   traversal kernels of one metric and route
 //   -DLMD_INST_KIND=1 -DLMD_INST_METRIC=<1|2|3>                          rerank kernels of one metric
 //   -DLMD_INST_KIND=2 -DLMD_INST_METRIC=<1|2|3>                          RobustPrune kernels of one metric
+//   -DLMD_INST_KIND=3 -DLMD_INST_METRIC=<1|2|3> -DLMD_INST_ROUTE=<0|1>   FILTERED traversal kernels (row f4)
 // so that the shape x list-size variants of each family build in parallel with the others.
 #include "lmd_build_kernels.cuh"
 
@@ -15,6 +16,13 @@ lmd_status LMD_CAT(LMD_CAT(dispatch_traverse_m, LMD_INST_METRIC), LMD_CAT(_r, LM
     KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st) {
 	LMD_DISPATCH_SHAPE(traverse_kernel, LMD_INST_METRIC, LMD_INST_ROUTE)
 	set_error("no traversal kernel for this configuration (L=%u)", p.L);
+	return LMD_ERR_UNSUPPORTED;
+}
+#elif LMD_INST_KIND == 3
+lmd_status LMD_CAT(LMD_CAT(dispatch_traverse_filt_m, LMD_INST_METRIC), LMD_CAT(_r, LMD_INST_ROUTE))(
+    KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st) {
+	LMD_DISPATCH_SHAPE_COARSE(traverse_kernel, LMD_INST_METRIC, LMD_INST_ROUTE, 1)
+	set_error("no filtered traversal kernel for this configuration (L=%u)", p.L);
 	return LMD_ERR_UNSUPPORTED;
 }
 #elif LMD_INST_KIND == 2

@@ -51,6 +51,9 @@ struct KParams {
 	uint32_t filter_bytes;              // bytes of the table (either mode)
 	uint32_t prefetch_planes;           // ternary routing: also prefetch the runner-up's plane region
 	uint32_t warp_smem_bytes;
+	// filtered search: bit `slot` set = the row passes the host's filter
+	const uint32_t *__restrict__ allowed;
+	uint32_t res_off; // byte offset of the results list RH inside the warp's shared memory
 };
 
 #define FULL 0xFFFFFFFFu
@@ -612,7 +615,16 @@ __device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_
 	return d + 0.0f;
 }
 
-template <int TEAM, int CH, int G, int LPL, int METRIC, int ROUTE>
+__device__ __forceinline__ bool slot_allowed(const KParams &p, uint32_t slot) {
+	return (__ldg(p.allowed + (slot >> 5)) >> (slot & 31)) & 1u;
+}
+
+// FILT = 1: filtered search, the dual-heap design of the reference's plan ("Consolidated Diskann Proposal v1", section
+// "Filtered Searches"). The exploration heap EH is s_list, untouched: the traversal tunnels through rows that fail the
+// filter exactly as an unfiltered search would. The results heap RH is a second sorted list (s_res, L entries) that is
+// offered every node whose routing distance gets evaluated and admits only allowed rows; results and the rerank
+// candidates come from RH alone.
+template <int TEAM, int CH, int G, int LPL, int METRIC, int ROUTE, int FILT = 0>
 __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 	extern __shared__ __align__(16) uint8_t smem[];
 	const int lane = threadIdx.x & 31;
@@ -627,6 +639,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 	float *s_q = reinterpret_cast<float *>(extra); // generic shape only
 	uint32_t *s_qp = reinterpret_cast<uint32_t *>(extra + (CH == 0 ? p.row_floats * 4 : 0));
 	uint32_t *s_qn = s_qp + p.words * 2;
+	uint64_t *s_res = FILT ? reinterpret_cast<uint64_t *>(wbase + p.res_off) : s_list;
 	const int L = (int)p.L;
 	const int cap = (int)p.list_cap;
 	const uint32_t nbr_lines = (p.r * 4 + 127) / 128;
@@ -643,6 +656,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		}
 		uint32_t n_exp = 0, n_eval = 0, n_evict = 0, n_tie_ovf = 0, n_fallback = 0;
 		int n = 0;
+		int nres = 0;
 		{
 			const uint32_t fill = p.filter_mode ? 0u : FILTER_EMPTY;
 			uint4 e4 = make_uint4(fill, fill, fill, fill);
@@ -672,6 +686,12 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 			}
 			n = 1;
 			n_eval = 1;
+			if (FILT && slot_allowed(p, p.entry_slot)) {
+				if (lane == 0) {
+					s_res[0] = make_key(d0, p.entry_slot);
+				}
+				nres = 1;
+			}
 			__syncwarp();
 		}
 
@@ -749,6 +769,26 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 						d = ternary_distance<(CH > 0 && ROUTE == LMD_ROUTE_TERNARY ? (CH * TEAM * 4 + 63) / 64 : 0)>(p, blk, j, s_qp, s_qn);
 					}
 				}
+				if (FILT) {
+					// RH: allowed rows only, bounded at L, same (distance, slot) order and strict threshold as EH
+					float rworst = nres >= L ? key_dist(s_res[L - 1]) : 0.0f;
+					const bool ok = have && slot_allowed(p, myid) && (nres < L || d < rworst);
+					uint32_t rmask = __ballot_sync(FULL, ok);
+					uint32_t dummy = 0;
+					while (rmask) {
+						const int src = __ffs(rmask) - 1;
+						rmask &= rmask - 1;
+						const float dj = __shfl_sync(FULL, d, src);
+						const uint32_t idj = __shfl_sync(FULL, myid, src);
+						if (nres >= L && !(dj < rworst)) {
+							continue;
+						}
+						nres = list_insert<LPL>(s_res, nres, L, L, make_key(dj, idj), lane, dummy);
+						if (nres >= L) {
+							rworst = key_dist(s_res[L - 1]);
+						}
+					}
+				}
 				// core/Searcher.cpp:175-185, candidates taken in neighbour order with a moving threshold
 				float worst = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
 				const bool pass = have && (n < L || d < worst);
@@ -784,10 +824,13 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		if (n > L) {
 			n = L;
 		}
+		if (FILT) { // only RH is returned
+			n = nres;
+		}
 		if (p.cand) {
 			uint64_t *dst = p.cand + (uint64_t)qi * p.L;
 			for (int i = lane; i < L; i += 32) {
-				dst[i] = i < n ? s_list[i] : LMD_KEY_NONE;
+				dst[i] = i < n ? s_res[i] : LMD_KEY_NONE;
 			}
 		}
 		if (p.out_ids) { // traversal distances are exact: the k best of the list are the answer (Searcher.cpp:189-245)
@@ -795,7 +838,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				int64_t rid = -1;
 				float dd = 0.0f;
 				if ((int)i < n) {
-					uint64_t key = s_list[i];
+					uint64_t key = s_res[i];
 					rid = p.row_ids[key_slot(key)];
 					dd = key_dist(key);
 				}
@@ -990,6 +1033,32 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		return launch_persistent(KERNEL<TEAM, CH, G, 16, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);               \
 	default:                                                                                                           \
 		break;                                                                                                         \
+	}
+
+// filtered traversal: half the list-size variants (lists of 64 / 128 / 256 / 512 entries)
+#define LMD_DISPATCH_LPL_COARSE(KERNEL, TEAM, CH, G, METRIC, ...)                                                      \
+	switch (lpl) {                                                                                                     \
+	case 2:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 2, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 4:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 4, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 8:                                                                                                            \
+		return launch_persistent(KERNEL<TEAM, CH, G, 8, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);                \
+	case 16:                                                                                                           \
+		return launch_persistent(KERNEL<TEAM, CH, G, 16, METRIC, ##__VA_ARGS__>, p, s, nq, st, #KERNEL);               \
+	default:                                                                                                           \
+		break;                                                                                                         \
+	}
+
+#define LMD_DISPATCH_SHAPE_COARSE(KERNEL, METRIC, ...)                                                                 \
+	if (p.row_floats == 128) {                                                                                         \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 4, 2, METRIC, ##__VA_ARGS__)                                                \
+	} else if (p.row_floats == 96) {                                                                                   \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                \
+	} else if (p.row_floats == 768) {                                                                                  \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 6, 2, METRIC, ##__VA_ARGS__)                                               \
+	} else {                                                                                                           \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                               \
 	}
 
 #define LMD_DISPATCH_SHAPE(KERNEL, METRIC, ...)                                                                        \

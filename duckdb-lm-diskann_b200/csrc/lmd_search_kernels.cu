@@ -59,6 +59,13 @@ LMD_DECL_TRAVERSE(2, 0)
 LMD_DECL_TRAVERSE(3, 0)
 LMD_DECL_TRAVERSE(2, 1)
 LMD_DECL_TRAVERSE(3, 1)
+#define LMD_DECL_TRAVERSE_FILT(M, R)                                                                                   \
+	lmd_status dispatch_traverse_filt_m##M##_r##R(KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st);
+LMD_DECL_TRAVERSE_FILT(1, 0)
+LMD_DECL_TRAVERSE_FILT(2, 0)
+LMD_DECL_TRAVERSE_FILT(3, 0)
+LMD_DECL_TRAVERSE_FILT(2, 1)
+LMD_DECL_TRAVERSE_FILT(3, 1)
 LMD_DECL_RERANK(1)
 LMD_DECL_RERANK(2)
 LMD_DECL_RERANK(3)
@@ -134,6 +141,27 @@ static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes
 
 static lmd_status dispatch_traverse(KParams &p, const lmd_store *s, uint32_t nq, int lpl, uint32_t route,
                                     cudaStream_t st) {
+	if (p.allowed) { // filtered search (row f4)
+		if (route == LMD_ROUTE_EXACT) {
+			switch (p.metric) {
+			case LMD_METRIC_L2:
+				return dispatch_traverse_filt_m1_r0(p, s, nq, lpl, st);
+			case LMD_METRIC_COSINE:
+				return dispatch_traverse_filt_m2_r0(p, s, nq, lpl, st);
+			case LMD_METRIC_IP:
+				return dispatch_traverse_filt_m3_r0(p, s, nq, lpl, st);
+			}
+		} else {
+			switch (p.metric) {
+			case LMD_METRIC_COSINE:
+				return dispatch_traverse_filt_m2_r1(p, s, nq, lpl, st);
+			case LMD_METRIC_IP:
+				return dispatch_traverse_filt_m3_r1(p, s, nq, lpl, st);
+			}
+		}
+		set_error("no filtered traversal kernel for this configuration (L=%u)", p.L);
+		return LMD_ERR_UNSUPPORTED;
+	}
 	if (route == LMD_ROUTE_EXACT) {
 		switch (p.metric) {
 		case LMD_METRIC_L2:
@@ -190,12 +218,18 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 		set_error("search list size L = %u exceeds this build's limit of 512", a.L);
 		return LMD_ERR_UNSUPPORTED;
 	}
+	if (a.d_allowed) {
+		lpl = lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16; // the filtered kernels exist for these list sizes only
+		p.allowed = a.d_allowed;
+	}
 	p.list_cap = (uint32_t)lpl * 32;
 	p.merge_min = (uint32_t)(s->tune.merge_min > 0 ? s->tune.merge_min : 5);
 	p.prefetch_planes = s->tune.prefetch_planes ? 1u : 0u;
 	const bool generic = !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	size_t fixed = (size_t)lpl * 32 * 8 + 384 + (generic ? (size_t)p.row_floats * 4 : 0) +
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0);
+	const size_t res_bytes = a.d_allowed ? (size_t)lpl * 32 * 8 : 0; // the results list RH of a filtered search
+	fixed += res_bytes;
 	const FilterPlan fp = pick_filter(s, a.L, fixed);
 	p.filter_mode = fp.mode;
 	p.filter_bytes = fp.bytes;
@@ -203,7 +237,8 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.filter_shift = 32 - fp.lg;
 	p.filter_bmask = (1u << (fp.lg - 3)) - 1;
 	p.filter_hmask = (uint32_t)((1ull << (fp.lg - 3 + 15)) - 1);
-	p.warp_smem_bytes = (uint32_t)((fixed + fp.bytes + 15) / 16 * 16);
+	p.res_off = (uint32_t)((fixed - res_bytes + fp.bytes + 15) / 16 * 16);
+	p.warp_smem_bytes = (uint32_t)(p.res_off + (res_bytes + 15) / 16 * 16);
 	return dispatch_traverse(p, s, a.nq, lpl, a.route, st);
 }
 

@@ -140,6 +140,30 @@ __global__ void scatter_blocks_kernel(const uint8_t *__restrict__ stage, const u
 	}
 }
 
+// Filtered search: allowed row ids -> bitmap over slots. Unknown row ids are ignored; `count` = bits newly set.
+__global__ void filter_bits_kernel(const long long *map_keys, const uint32_t *map_vals, uint64_t map_mask, int identity,
+                                   uint64_t n_nodes, const int64_t *rids, uint64_t n, uint32_t *bits,
+                                   unsigned long long *count) {
+	uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (i >= n) {
+		return;
+	}
+	const int64_t rid = rids[i];
+	uint32_t slot;
+	if (identity) {
+		slot = (rid >= 0 && (uint64_t)rid < n_nodes) ? (uint32_t)rid : LMD_INVALID_SLOT;
+	} else {
+		slot = map_lookup(map_keys, map_vals, map_mask, rid);
+	}
+	if (slot == LMD_INVALID_SLOT) {
+		return;
+	}
+	const uint32_t bit = 1u << (slot & 31);
+	if (!(atomicOr(&bits[slot >> 5], bit) & bit)) {
+		atomicAdd(count, 1ull);
+	}
+}
+
 __global__ void lookup_one_kernel(const long long *map_keys, const uint32_t *map_vals, uint64_t map_mask, int64_t rid,
                                   uint32_t *out) {
 	*out = map_lookup(map_keys, map_vals, map_mask, rid);
@@ -586,6 +610,7 @@ lmd_status store_ingest(lmd_store *s, const int64_t *row_ids, uint64_t base, uin
 	LMD_CUDA_OK(cudaGetLastError());
 	LMD_CUDA_OK(cudaStreamSynchronize(s->stream)); // caller may free / reuse its buffers on return
 	s->n += n;
+	s->epoch++;
 	s->dirty = true;
 	if (s->entry_row != INT64_MAX && !s->has_entry) {
 		// an entry row id set before its block arrived resolves now
@@ -826,6 +851,7 @@ lmd_status lmd_store_remove(lmd_store *s, const int64_t *row_ids, uint64_t n, ui
 	LMD_CUDA_OK(e);
 	if (removed) {
 		s->removed += removed;
+		s->epoch++;
 		s->identity = false; // slot numbers no longer stand for row ids: resolve through the map
 		s->dirty = true;     // neighbour rows that point at the removed slots are rebuilt before the next search
 	}
@@ -840,6 +866,86 @@ lmd_status lmd_store_remove(lmd_store *s, const int64_t *row_ids, uint64_t n, ui
 		*out_removed = removed;
 	}
 	return LMD_OK;
+}
+
+// Filtered search: the host's `allowed_ids` set, resolved once to a bitmap over the
+// store's slots and reused by any number of searches.
+lmd_status lmd_filter_create(lmd_store *s, const int64_t *allowed_row_ids, uint64_t n, lmd_filter **out) {
+	if (!s || !out || (!allowed_row_ids && n)) {
+		set_error("lmd_filter_create: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	*out = nullptr;
+	std::lock_guard<std::mutex> g(s->mu);
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	lmd_filter *f = new (std::nothrow) lmd_filter();
+	if (!f) {
+		set_error("host allocation failed");
+		return LMD_ERR_OOM;
+	}
+	f->store = s;
+	f->epoch = s->epoch;
+	f->words = (s->capacity + 31) / 32;
+	int64_t *d_rids = nullptr;
+	const int64_t *src = allowed_row_ids;
+	cudaError_t e = cudaMalloc((void **)&f->d_bits, f->words * sizeof(uint32_t));
+	if (e == cudaSuccess) {
+		e = cudaMemsetAsync(f->d_bits, 0, f->words * sizeof(uint32_t), s->stream);
+	}
+	unsigned long long *d_count = s->d_counters + 8;
+	unsigned long long h_count = 0;
+	if (e == cudaSuccess && n) {
+		if (!is_device_ptr(allowed_row_ids)) {
+			e = cudaMalloc((void **)&d_rids, n * sizeof(int64_t));
+			if (e == cudaSuccess) {
+				e = cudaMemcpyAsync(d_rids, allowed_row_ids, n * sizeof(int64_t), cudaMemcpyHostToDevice, s->stream);
+			}
+			src = d_rids;
+		}
+		if (e == cudaSuccess) {
+			e = cudaMemsetAsync(d_count, 0, sizeof(unsigned long long), s->stream);
+		}
+		if (e == cudaSuccess) {
+			filter_bits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(
+			    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->identity ? 1 : 0, s->n, src, n,
+			    f->d_bits, d_count);
+			e = cudaGetLastError();
+		}
+		if (e == cudaSuccess) {
+			e = cudaMemcpyAsync(&h_count, d_count, sizeof(h_count), cudaMemcpyDeviceToHost, s->stream);
+		}
+	}
+	if (e == cudaSuccess) {
+		e = cudaStreamSynchronize(s->stream);
+	}
+	cudaFree(d_rids);
+	if (e != cudaSuccess) {
+		cudaGetLastError();
+		set_error("lmd_filter_create failed: %s", cudaGetErrorString(e));
+		cudaFree(f->d_bits);
+		delete f;
+		return e == cudaErrorMemoryAllocation ? LMD_ERR_OOM : LMD_ERR_CUDA;
+	}
+	f->count = h_count;
+	*out = f;
+	return LMD_OK;
+}
+
+lmd_status lmd_filter_destroy(lmd_filter *f) {
+	if (!f) {
+		return LMD_OK;
+	}
+	if (f->store) {
+		cudaSetDevice(f->store->device);
+		cudaStreamSynchronize(f->store->stream);
+	}
+	cudaFree(f->d_bits);
+	delete f;
+	return LMD_OK;
+}
+
+uint64_t lmd_filter_count(const lmd_filter *f) {
+	return f ? f->count : 0;
 }
 
 lmd_status lmd_store_set_entry(lmd_store *s, int64_t row_id) {

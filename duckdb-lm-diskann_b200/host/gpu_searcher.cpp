@@ -396,6 +396,89 @@ void GpuSearcher::SearchBatch(const float *queries, common::idx_t nq, common::id
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+AllowedIds::AllowedIds(DeviceNodeStore &store, const common::row_t *row_ids, common::idx_t count) {
+	Check(lmd_filter_create(store.Handle(), row_ids, count, &filter_), "AllowedIds");
+}
+
+AllowedIds::~AllowedIds() {
+	if (filter_) {
+		lmd_filter_destroy(filter_);
+	}
+}
+
+common::idx_t AllowedIds::Count() const {
+	return lmd_filter_count(filter_);
+}
+
+common::idx_t GpuSearcher::SearchBatchFiltered(const AllowedIds &allowed, const float *queries, common::idx_t nq,
+                                               common::idx_t k_neighbors, common::idx_t search_list_size,
+                                               common::row_t *out_ids, float *out_dist, uint32_t *out_count,
+                                               bool widen) {
+	if (mirror_ && mirror_->HasPending()) {
+		mirror_->Flush(); // note: new or deleted rows make `allowed` stale; the call below then reports it
+	}
+	const common::idx_t dims = store_->Config().dimensions;
+	std::vector<uint32_t> count_storage;
+	if (!out_count) {
+		count_storage.resize(nq);
+		out_count = count_storage.data();
+	}
+	uint32_t L = static_cast<uint32_t>(search_list_size ? search_list_size : store_->Config().l_search);
+	if (L == 0) {
+		L = k_neighbors > 20 ? static_cast<uint32_t>(k_neighbors) + 20 : 40; // core/Searcher.cpp:261-265
+	}
+	L = std::max<uint32_t>(L, static_cast<uint32_t>(k_neighbors));
+	Check(lmd_search_batch_filtered(store_->Handle(), allowed.Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
+	                                L, static_cast<uint32_t>(route_), 0, out_ids, out_dist, out_count, nullptr, nullptr),
+	      "GpuSearcher::SearchBatchFiltered");
+	const common::idx_t reachable = std::min<common::idx_t>(allowed.Count(), k_neighbors);
+	std::vector<common::idx_t> shortq;
+	for (common::idx_t q = 0; q < nq; q++) {
+		if (out_count[q] < reachable) {
+			shortq.push_back(q);
+		}
+	}
+	// widen: only the queries that came back short, with twice the list each round
+	std::vector<float> sub_q;
+	std::vector<common::row_t> sub_ids;
+	std::vector<float> sub_dist;
+	std::vector<uint32_t> sub_cnt;
+	while (widen && !shortq.empty() && L < 512) {
+		L = std::min<uint32_t>(512, L * 2);
+		const common::idx_t m = shortq.size();
+		sub_q.resize(m * dims);
+		sub_ids.resize(m * k_neighbors);
+		sub_dist.resize(m * k_neighbors);
+		sub_cnt.resize(m);
+		for (common::idx_t i = 0; i < m; i++) {
+			std::memcpy(sub_q.data() + i * dims, queries + shortq[i] * dims, dims * sizeof(float));
+		}
+		Check(lmd_search_batch_filtered(store_->Handle(), allowed.Handle(), sub_q.data(), m,
+		                                static_cast<uint32_t>(k_neighbors), L, static_cast<uint32_t>(route_), 0,
+		                                sub_ids.data(), sub_dist.data(), sub_cnt.data(), nullptr, nullptr),
+		      "GpuSearcher::SearchBatchFiltered");
+		std::vector<common::idx_t> still;
+		for (common::idx_t i = 0; i < m; i++) {
+			const common::idx_t q = shortq[i];
+			std::memcpy(out_ids + q * k_neighbors, sub_ids.data() + i * k_neighbors, k_neighbors * sizeof(common::row_t));
+			if (out_dist) {
+				std::memcpy(out_dist + q * k_neighbors, sub_dist.data() + i * k_neighbors, k_neighbors * sizeof(float));
+			}
+			out_count[q] = sub_cnt[i];
+			if (sub_cnt[i] < reachable) {
+				still.push_back(q);
+			}
+		}
+		shortq.swap(still);
+	}
+	common::idx_t under = 0;
+	for (common::idx_t q = 0; q < nq; q++) {
+		under += out_count[q] < k_neighbors ? 1 : 0;
+	}
+	return under;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 void GpuCoordinatorSearch(core::ISearcher *searcher, core::IGraphManager *graph_manager,
                           const core::LmDiskannConfig &config, bool index_loaded, const float *query_vector,
                           common::idx_t k_neighbors, std::vector<common::row_t> &result_row_ids,
@@ -466,6 +549,38 @@ common::idx_t GpuIndexScan::Scan(GpuScanState &state, common::row_t *result, com
 		throw ::duckdb::IOException(::duckdb::StringUtil::Format("Error during LM_DISKANN scan: %s", e.what()));
 	}
 	return output_count;
+}
+
+common::idx_t GpuIndexScan::MultiScanFiltered(const AllowedIds &allowed, const float *queries, common::idx_t nq,
+                                              common::idx_t query_dims, common::idx_t k, common::row_t *out_ids,
+                                              uint32_t *out_count) {
+	if (query_dims != config_.dimensions) {
+		throw ::duckdb::BinderException(::duckdb::StringUtil::Format(
+		    "Query vector dimension (%d) does not match index dimension (%d).", (int)query_dims, (int)config_.dimensions));
+	}
+	if (k == 0) {
+		throw ::duckdb::BinderException("Cannot perform index scan with k=0");
+	}
+	auto *gpu = dynamic_cast<GpuSearcher *>(searcher_);
+	if (!gpu) {
+		// the reference's ISearcher has no filtered entry (the plan's dual-heap search was never written)
+		throw ::duckdb::NotImplementedException("filtered LM_DISKANN scan needs the GpuSearcher");
+	}
+	try {
+		if (graph_) {
+			gpu->Store().SyncEntryPoint(*graph_);
+		}
+		const common::idx_t L = std::max<common::idx_t>(config_.l_search, k);
+		const common::idx_t under = gpu->SearchBatchFiltered(allowed, queries, nq, k, L, out_ids, nullptr, out_count);
+		if (under) {
+			// the plan: "issue a warning ... suggesting to increase L_search"
+			std::cerr << "LM_DISKANN: " << under << " filtered scan(s) found fewer than k=" << k
+			          << " rows that satisfy the filter; consider increasing L_SEARCH" << std::endl;
+		}
+		return under;
+	} catch (const std::exception &e) {
+		throw ::duckdb::IOException(::duckdb::StringUtil::Format("Error during LM_DISKANN scan: %s", e.what()));
+	}
 }
 
 void GpuIndexScan::MultiScan(const float *queries, common::idx_t nq, common::idx_t query_dims, common::idx_t k,

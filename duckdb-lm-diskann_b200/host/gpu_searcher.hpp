@@ -165,6 +165,27 @@ private:
 };
 
 // ---------------------------------------------------------------------------------------------------------------
+// AllowedIds: the `allowed_ids` set of a filtered scan (the reference's plan passes it as
+// `struct ScanOptions { SelectionVector *allowed_ids; idx_t count; }`), resolved once to the device store's slots.
+// Valid until rows are added to / removed from the store.
+// ---------------------------------------------------------------------------------------------------------------
+class AllowedIds {
+public:
+	AllowedIds(DeviceNodeStore &store, const common::row_t *row_ids, common::idx_t count);
+	~AllowedIds();
+	AllowedIds(const AllowedIds &) = delete;
+	AllowedIds &operator=(const AllowedIds &) = delete;
+	// distinct allowed row ids that exist in the index
+	common::idx_t Count() const;
+	const lmd_filter *Handle() const {
+		return filter_;
+	}
+
+private:
+	lmd_filter *filter_ = nullptr;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
 // GpuSearcher: drop-in for core::Searcher behind core::ISearcher.
 // ---------------------------------------------------------------------------------------------------------------
 class GpuSearcher : public core::ISearcher {
@@ -194,6 +215,14 @@ public:
 	// out_dist [nq][k] (may be null), out_count [nq] (may be null). Host or device pointers (all on one side).
 	void SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors, common::idx_t search_list_size,
 	                 common::row_t *out_ids, float *out_dist, uint32_t *out_count, lmd_stats *stats = nullptr);
+
+	// Filtered form (dual heap: exploration over all rows, results over `allowed` only). When `widen` is set, queries
+	// that met fewer than k allowed rows are searched again with L doubled, up to the build's limit of 512 - the
+	// plan's "L_search ... automatically increased for filtered queries". Returns the number of queries that still
+	// have fewer than k results (the host warns the user, as the plan says).
+	common::idx_t SearchBatchFiltered(const AllowedIds &allowed, const float *queries, common::idx_t nq,
+	                                  common::idx_t k_neighbors, common::idx_t search_list_size, common::row_t *out_ids,
+	                                  float *out_dist, uint32_t *out_count, bool widen = true);
 
 	DeviceNodeStore &Store() {
 		return *store_;
@@ -248,6 +277,11 @@ public:
 	// device launch; out [nq][k], -1 padded.
 	void MultiScan(const float *queries, common::idx_t nq, common::idx_t query_dims, common::idx_t k,
 	               common::row_t *out_ids, uint32_t *out_count);
+	// MultiScan restricted to `allowed` (a WHERE clause on the same table, resolved by the host to row ids). Returns
+	// the number of scans that produced fewer than k rows after widening.
+	common::idx_t MultiScanFiltered(const AllowedIds &allowed, const float *queries, common::idx_t nq,
+	                                common::idx_t query_dims, common::idx_t k, common::row_t *out_ids,
+	                                uint32_t *out_count);
 
 private:
 	core::ISearcher *searcher_;

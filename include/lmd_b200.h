@@ -147,6 +147,23 @@ lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uin
                             uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
                             uint32_t *out_qstats, lmd_stats *stats);
 
+/* --- filtered search ---
+ * The reference's plan ("Consolidated Diskann Proposal v1", section "Filtered Searches"; stubs in
+ * libsql/lm_diskann.hpp) hands the index an `allowed_ids` set and searches with two heaps: exploration over ALL rows,
+ * results over allowed rows only. No reference code implements it (parity is against oracle/lmd_oracle.c's
+ * restatement of that design only). lmd_filter_create resolves the host's allowed row ids (host or device memory;
+ * unknown ids ignored, duplicates harmless) to a bitmap over the store's slots; the filter stays valid until rows are
+ * added to or removed from the store (LMD_ERR_STATE afterwards). lmd_search_batch_filtered is lmd_search_batch with
+ * that filter: same traversal, results (and rerank candidates) restricted to allowed rows, out_count[q] < k when
+ * fewer than k allowed rows were met - the host then warns or widens L, as the plan says. */
+typedef struct lmd_filter lmd_filter;
+lmd_status lmd_filter_create(lmd_store *s, const int64_t *allowed_row_ids, uint64_t n, lmd_filter **out);
+lmd_status lmd_filter_destroy(lmd_filter *f);
+uint64_t lmd_filter_count(const lmd_filter *f); /* distinct allowed row ids present in the store */
+lmd_status lmd_search_batch_filtered(lmd_store *s, const lmd_filter *filter, const float *queries, uint64_t nq,
+                                     uint32_t k, uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids,
+                                     float *out_dist, uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats);
+
 /* --- dataset sharding: k-way merge of G gathered per-shard results.
  * ids [G][nq][k], dist [G][nq][k] (device or host, as produced by lmd_search_batch on each shard and
  * all-gathered by the caller) -> out [nq][k] smallest by (distance, id); -1 ids are padding. */

@@ -338,6 +338,7 @@ typedef struct {
 	uint64_t dims;
 	uint32_t r, cfg_l_search;
 	lmdo_layout lay;
+	const uint8_t *allowed; /* filtered search (row f4): one byte per block position, NULL = unfiltered */
 } index_t;
 
 /* GraphManager.cpp:523-531 (TryGetNodePointer) over the harness' row_id -> slot mapping */
@@ -353,7 +354,7 @@ static int try_get_slot(const index_t *ix, int64_t row, uint64_t *slot) {
 }
 
 typedef struct {
-	heap_t top, beam, fin;
+	heap_t top, beam, fin, res;
 	i64map_t visited;
 	float *tmp;
 	uint64_t *qplanes;
@@ -382,7 +383,8 @@ static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uin
 	if (L < k) {
 		L = k;
 	}
-	s->top.n = s->beam.n = s->fin.n = 0;
+	s->top.n = s->beam.n = s->fin.n = s->res.n = 0;
+	s->res.is_max = 1;  /* filtered search: the results heap RH, bounded like `top` */
 	s->top.is_max = 1;  /* H1 */
 	s->beam.is_max = 0; /* :67 */
 	s->fin.is_max = 1;  /* H3 */
@@ -399,6 +401,13 @@ static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uin
 	map_put(&s->visited, ix->entry_row, 0);
 	heap_push(&s->top, e);
 	float worst = d_entry; /* :106 lowest_dist_in_results */
+	/* Filtered search ("Consolidated Diskann Proposal v1", section "Filtered Searches": dual heap). The exploration
+	 * heap EH is the unfiltered search's own state (`top` + `beam`): the traversal tunnels through nodes that fail the
+	 * filter exactly as if there were none. The results heap RH (`res`) is offered every node whose distance gets
+	 * evaluated and keeps the L best ALLOWED ones; only RH is returned. */
+	if (ix->allowed && ix->allowed[ix->entry_slot]) {
+		heap_push(&s->res, e);
+	}
 
 	uint64_t words = lmdo_words_per_plane(ix->dims);
 	if (ix->route == LMDO_ROUTE_TERNARY) {
@@ -447,6 +456,13 @@ static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uin
 				d = approx_from_score(lmdo_ternary_dot(s->qplanes, s->qplanes + words, vp, vn, words),
 				                      ix->metric, NULL);
 			}
+			if (ix->allowed && ix->allowed[nb_slot] && (s->res.n < L || d < s->res.a[0].d)) {
+				cand_t c = {d, nb};
+				heap_push(&s->res, c);
+				if (s->res.n > L) {
+					heap_pop(&s->res);
+				}
+			}
 			if (s->top.n < L || d < worst) { /* :175 */
 				cand_t c = {d, nb};
 				heap_push(&s->beam, c);
@@ -461,6 +477,11 @@ static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uin
 		}
 	}
 
+	if (ix->allowed) { /* only RH is returned: it takes the place of `top` below */
+		heap_t t = s->top;
+		s->top = s->res;
+		s->res = t;
+	}
 	if (!final_pass) {
 		/* Searcher.cpp:189 + H5: SearchForInitialCandidates gets the top list itself, worst first (heap pop order) */
 		uint64_t cnt = 0;
@@ -551,15 +572,18 @@ static void *worker(void *arg) {
 	free(s.top.a);
 	free(s.beam.a);
 	free(s.fin.a);
+	free(s.res.a);
 	return NULL;
 }
 
-int lmdo_search(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const int64_t *row_ids, int64_t entry_row_id,
-                int metric, int vec_type, uint64_t dims, uint32_t r, uint32_t cfg_l_search, const float *queries,
-                uint64_t nq, uint64_t k, uint64_t l_param, int route, int64_t *out_ids, float *out_dist,
-                uint32_t *out_count, uint64_t *out_stats, int nthreads) {
+static int search_impl(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const int64_t *row_ids,
+                       int64_t entry_row_id, int metric, int vec_type, uint64_t dims, uint32_t r, uint32_t cfg_l_search,
+                       const float *queries, uint64_t nq, uint64_t k, uint64_t l_param, int route,
+                       const uint8_t *allowed, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                       uint64_t *out_stats, int nthreads) {
 	index_t ix;
 	memset(&ix, 0, sizeof(ix));
+	ix.allowed = allowed;
 	if (lmdo_layout_calc(dims, vec_type, r, &ix.lay)) {
 		return 2;
 	}
@@ -627,6 +651,25 @@ int lmdo_search(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const i
 		map_free(&rowmap);
 	}
 	return 0;
+}
+
+int lmdo_search(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const int64_t *row_ids, int64_t entry_row_id,
+                int metric, int vec_type, uint64_t dims, uint32_t r, uint32_t cfg_l_search, const float *queries,
+                uint64_t nq, uint64_t k, uint64_t l_param, int route, int64_t *out_ids, float *out_dist,
+                uint32_t *out_count, uint64_t *out_stats, int nthreads) {
+	return search_impl(blocks, n, block_bytes, row_ids, entry_row_id, metric, vec_type, dims, r, cfg_l_search, queries,
+	                   nq, k, l_param, route, NULL, out_ids, out_dist, out_count, out_stats, nthreads);
+}
+
+/* Row f4 (designed in the reference's plan, implemented nowhere in it: PARITY UNPINNED). allowed[i] != 0 <=> the row
+ * of block i passes the filter. allowed == NULL is the unfiltered search. */
+int lmdo_search_filtered(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const int64_t *row_ids,
+                         int64_t entry_row_id, int metric, int vec_type, uint64_t dims, uint32_t r,
+                         uint32_t cfg_l_search, const float *queries, uint64_t nq, uint64_t k, uint64_t l_param,
+                         int route, const uint8_t *allowed, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                         uint64_t *out_stats, int nthreads) {
+	return search_impl(blocks, n, block_bytes, row_ids, entry_row_id, metric, vec_type, dims, r, cfg_l_search, queries,
+	                   nq, k, l_param, route, allowed, out_ids, out_dist, out_count, out_stats, nthreads);
 }
 
 /* ================================================================================================

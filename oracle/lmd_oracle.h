@@ -57,6 +57,16 @@ int lmdo_search(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const i
                 uint64_t nq, uint64_t k, uint64_t l_param, int route, int64_t *out_ids, float *out_dist,
                 uint32_t *out_count, uint64_t *out_stats, int nthreads);
 
+/* Filtered search (the dual-heap design of the reference's "Consolidated Diskann Proposal
+ * v1", which no reference code implements: PARITY UNPINNED). allowed [n] bytes, one per block position (non-zero =
+ * the row passes the filter), NULL = lmdo_search. The traversal is the unfiltered one; results come from a second
+ * bounded heap that only admits allowed rows. */
+int lmdo_search_filtered(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, const int64_t *row_ids,
+                         int64_t entry_row_id, int metric, int vec_type, uint64_t dims, uint32_t r,
+                         uint32_t cfg_l_search, const float *queries, uint64_t nq, uint64_t k, uint64_t l_param,
+                         int route, const uint8_t *allowed, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                         uint64_t *out_stats, int nthreads);
+
 /* Graph write side, same contracts as lmdref_build_serial / lmdref_robust_prune in
  * ref_build_harness.cpp. core/GraphManager.cpp:65-203 (AddNode) and :259-457 (RobustPrune). */
 int lmdo_build_serial(const float *vectors, uint64_t n, uint64_t dims, int metric, int vec_type, uint32_t r,

@@ -50,6 +50,9 @@ def port():
         _sig(l.lmdo_search, C.c_int, [_P, C.c_uint64, C.c_uint64, _P, C.c_int64, C.c_int, C.c_int, C.c_uint64,
                                       C.c_uint32, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, _P, _P,
                                       _P, _P, C.c_int])
+        _sig(l.lmdo_search_filtered, C.c_int, [_P, C.c_uint64, C.c_uint64, _P, C.c_int64, C.c_int, C.c_int, C.c_uint64,
+                                               C.c_uint32, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int,
+                                               _P, _P, _P, _P, _P, C.c_int])
         _sig(l.lmdo_build_serial, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                             C.c_float, _P, C.c_uint64, _P, _P])
         _sig(l.lmdo_robust_prune, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_float, _P,
@@ -146,7 +149,7 @@ def approx_distance(q, compressed, dims, metric, impl="port"):
 
 
 def search(blocks, block_bytes, dims, r, queries, k, L=0, metric=1, vec_type=1, row_ids=None, entry_row_id=0,
-           cfg_l_search=100, route=0, nthreads=0, impl="port"):
+           cfg_l_search=100, route=0, nthreads=0, impl="port", allowed=None):
     """-> ids [nq,k] int64 (-1 padded), dist [nq,k] f32, count [nq] u32, stats [nq,2] u64 {expansions, vector
     fetches}. impl: "port" (C restatement; route 0/1), "fixed" / "literal" (reference sources; route 0 only)."""
     b = _np(np.asarray(blocks).reshape(-1), np.uint8)
@@ -159,7 +162,16 @@ def search(blocks, block_bytes, dims, r, queries, k, L=0, metric=1, vec_type=1, 
     cnt = np.zeros(nq, dtype=np.uint32)
     st = np.zeros((nq, 2), dtype=np.uint64)
     ridp = None if rid is None else rid.ctypes.data
-    if impl == "port":
+    if allowed is not None:
+        # filtered search (row f4; C restatement only - the reference has no such code): allowed [n] per block position
+        if impl != "port":
+            raise ValueError("the reference sources implement no filtered search")
+        a = _np(np.asarray(allowed).astype(np.uint8), np.uint8)
+        assert a.size == n
+        rc = port().lmdo_search_filtered(b.ctypes.data, n, block_bytes, ridp, entry_row_id, metric, vec_type, dims, r,
+                                         cfg_l_search, q.ctypes.data, nq, k, L, route, a.ctypes.data, ids.ctypes.data,
+                                         dist.ctypes.data, cnt.ctypes.data, st.ctypes.data, nthreads)
+    elif impl == "port":
         rc = port().lmdo_search(b.ctypes.data, n, block_bytes, ridp, entry_row_id, metric, vec_type, dims, r,
                                 cfg_l_search, q.ctypes.data, nq, k, L, route, ids.ctypes.data, dist.ctypes.data,
                                 cnt.ctypes.data, st.ctypes.data, nthreads)

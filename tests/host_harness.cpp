@@ -354,6 +354,18 @@ int lmdhost_multi_scan(void *p, const float *queries, uint64_t nq, uint64_t quer
 	return Guard([&]() { h->scan->MultiScan(queries, nq, query_dims, k, out_ids, out_count); });
 }
 
+// Filtered index join: the host resolved a WHERE clause to `allowed` row ids; *under = scans still short of k.
+int lmdhost_multi_scan_filtered(void *p, const int64_t *allowed, uint64_t n_allowed, const float *queries, uint64_t nq,
+                                uint64_t query_dims, uint64_t k, int64_t *out_ids, uint32_t *out_count,
+                                uint64_t *allowed_present, uint64_t *under) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		b200::AllowedIds set(*h->store, allowed, n_allowed);
+		*allowed_present = set.Count();
+		*under = h->scan->MultiScanFiltered(set, queries, nq, query_dims, k, out_ids, out_count);
+	});
+}
+
 int lmdhost_initial_candidates(void *p, const float *vec, uint64_t dims, uint64_t want, int64_t *out_ids,
                                uint64_t *out_n) {
 	Host *h = static_cast<Host *>(p);

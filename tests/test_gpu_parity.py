@@ -423,3 +423,78 @@ def test_apply_and_remove_track_the_host_blocks(lmd, oracle, make_index, fixture
         with pytest.raises(lmd.LmdError):
             s.apply(np.arange(10**9, 10**9 + 50, dtype=np.int64), np.zeros((50, bb), dtype=np.uint8))
         check(s, live, cur, rid[live[3]], "after the refused batch")
+
+
+# ---- filtered search: allowed-ids set + dual heap ------------------------------------
+@pytest.mark.parametrize("n,dims,r,metric,kind,route,L,frac", [
+    (3000, 128, 32, "L2", "clustered", 0, 64, 0.25),
+    (3000, 128, 32, "L2", "iid", 0, 48, 0.5),
+    (2000, 96, 32, "L2", "clustered", 0, 100, 0.05),   # selective: most queries return fewer than k rows
+    (1500, 768, 32, "COSINE", "clustered", 0, 64, 0.3),
+    (1500, 100, 24, "IP", "iid", 0, 40, 0.2),          # generic shape
+    (2000, 128, 32, "COSINE", "clustered", 1, 64, 0.3),  # ternary routing: RH feeds the rerank
+    (2000, 128, 32, "IP", "iid", 1, 200, 0.1),
+    (2500, 128, 32, "L2", "clustered", 0, 512, 0.02),
+    (3000, 128, 32, "L2", "iid", 0, 16, 0.004),        # ~12 allowed rows: fewer than k are met, count says so
+])
+def test_filtered_search_parity(lmd, oracle, make_index, fixtures_mod, n, dims, r, metric, kind, route, L, frac):
+    k = 10
+    ix = make_index(n, dims, r, metric=metric, kind=kind, nq=96)
+    rng = np.random.default_rng(n + dims + L)
+    allowed = rng.random(n) < frac
+    allowed_ids = np.nonzero(allowed)[0].astype(np.int64)
+    with _store(lmd, ix, dims, r, metric) as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        # unknown and repeated row ids in the host's set are harmless
+        with s.make_filter(np.concatenate([allowed_ids, allowed_ids[:7], [10**12, -5]])) as f:
+            assert f.count == allowed_ids.size
+            ids, dist, cnt, st, qs = s.search(ix["queries"], k, L, route=route, qstats=True, filter=f)
+            plain = s.search(ix["queries"], k, L, route=route, qstats=True)
+        with s.make_filter(np.arange(n, dtype=np.int64)) as everything:
+            full = s.search(ix["queries"], k, L, route=route, filter=everything)
+    o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, ix["queries"], k, L, metric=METRIC[metric],
+                      entry_row_id=0, cfg_l_search=100, route=route, allowed=allowed)
+    check_parity(ids, dist, cnt, o[0], o[1], o[2], what="filtered %s route %d" % (metric, route))
+    assert allowed[ids[ids >= 0]].all()
+    if frac < 0.01:
+        assert (cnt < k).all()  # the host is told when fewer than k allowed rows were met (it warns or widens L)
+    # the traversal itself is the unfiltered one (tunnelling through rows that fail the filter): same expansions
+    # (distance evaluations may differ: RH shares the shared-memory budget with the visited filter, and a smaller
+    # visited filter re-evaluates more forgotten nodes)
+    assert np.array_equal(qs[:, 0], plain[4][:, 0])
+    # a filter that allows every row changes nothing
+    assert np.array_equal(full[0], plain[0]) and np.array_equal(full[2], plain[2])
+    if frac > 0.05:
+        truth = allowed_ids[fixtures_mod.brute_force_topk(ix["x"][allowed], ix["queries"], k, metric, device="cuda")]
+        assert fixtures_mod.recall_at_k(ids, truth) == fixtures_mod.recall_at_k(o[0], truth)
+
+
+def test_filter_goes_stale_when_rows_change(lmd, make_index):
+    ix = make_index(1500, 64, 16, metric="L2", kind="iid", nq=16)
+    b, q = ix["blocks_np"], ix["queries"]
+    rid = np.arange(1500, dtype=np.int64) * 3 + 1  # sparse ids: the filter resolves them through the row-id map
+    with lmd.Store(64, 16, capacity=1500) as s:
+        s.upload(b[:1400], row_ids=rid[:1400])
+        s.set_entry(rid[0])
+        f = s.make_filter(rid[:700:2])
+        assert f.count == 350
+        ids = s.search(q, 10, 40, filter=f)[0]
+        assert np.isin(ids[ids >= 0], rid[:700:2]).all()
+        s.apply(rid[5:6], b[5:6])          # an overwritten block keeps the row-id -> slot mapping: still valid
+        s.search(q, 10, 40, filter=f)
+        s.apply(rid[1400:], b[1400:])      # new rows: the mapping changed
+        with pytest.raises(lmd.LmdError) as e:
+            s.search(q, 10, 40, filter=f)
+        assert e.value.status == lmd.ERR_STATE
+        f.close()
+        with s.make_filter(rid[1400:]) as f2:
+            assert f2.count == 100
+            s.remove(rid[1400:1410])
+            with pytest.raises(lmd.LmdError):
+                s.search(q, 10, 40, filter=f2)
+        with lmd.Store(64, 16, capacity=10) as other, s.make_filter(rid[:10]) as f3:
+            other.upload(b[:10])
+            other.set_entry(0)
+            with pytest.raises(lmd.LmdError):
+                other.search(q, 10, 40, filter=f3)

@@ -41,6 +41,7 @@ def _lib():
     l.lmdhost_initial_candidates.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
     l.lmdhost_rewrite_block.argtypes = [P, C.c_int64, P, C.c_uint64]
     l.lmdhost_build_and_write_back.argtypes = [P, C.c_uint32, C.c_float, C.c_uint64, P, C.c_uint64, C.c_uint64, P, P]
+    l.lmdhost_multi_scan_filtered.argtypes = [P, P, C.c_uint64, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P, P, P]
     l.lmdlive_create.restype = P
     l.lmdlive_create.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.c_float, C.c_uint32,
                                  C.c_uint64, C.c_int]
@@ -298,6 +299,45 @@ def test_build_graph_and_write_back_through_the_interfaces(oracle, fixtures_mod)
         # ... and the adapter's own searches (now on the built store) return the same rows
         err, ids, cnt_q, _ = h.multi_scan(q, 10)
         assert err is None and (ids == o[0]).all(axis=1).mean() >= 0.97
+
+
+@pytest.mark.gpu
+def test_filtered_multi_scan_widens_short_scans(oracle, make_index, fixtures_mod):
+    """Row f4 through the adapter: a WHERE clause resolved to allowed row ids; scans that meet fewer than k allowed rows
+    are searched again with a doubled list (the plan's automatic L_search increase), the rest equal the oracle."""
+    n, dims, r, k = 4000, 64, 16, 10
+    rid = np.arange(n, dtype=np.int64) * 7 + 3
+    ix = make_index(n, dims, r, metric="L2", kind="clustered", nq=40, row_ids=rid)
+    q = ix["queries"]
+    allowed_mask = np.random.default_rng(8).random(n) < 0.02   # ~80 rows: L = 16 rarely meets 10 of them
+    allowed = rid[allowed_mask]
+    with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, row_ids=rid, entry=int(rid[0]), l_search=16) as h:
+        out = np.full((q.shape[0], k), -1, dtype=np.int64)
+        cnt = np.zeros(q.shape[0], dtype=np.uint32)
+        present, under = C.c_uint64(0), C.c_uint64(0)
+        rc = h.lib.lmdhost_multi_scan_filtered(h.h, allowed.ctypes.data, allowed.size, q.ctypes.data, q.shape[0], dims,
+                                               k, out.ctypes.data, cnt.ctypes.data, C.addressof(present),
+                                               C.addressof(under))
+        assert rc == 0, h.lib.lmdhost_last_error().decode()
+        assert present.value == allowed.size
+        assert np.isin(out[out >= 0], allowed).all()
+        # every scan equals the oracle's filtered search at the list size the adapter ended with for it
+        by_L = {L: oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q, k, L, row_ids=rid,
+                                 entry_row_id=int(rid[0]), allowed=allowed_mask) for L in (16, 32, 64, 128, 256, 512)}
+        widened = 0
+        for qi in range(q.shape[0]):
+            for L in (16, 32, 64, 128, 256, 512):
+                o = by_L[L]
+                if o[2][qi] >= k or L == 512:
+                    assert cnt[qi] == o[2][qi] and np.array_equal(out[qi], o[0][qi]), (qi, L)
+                    widened += L > 16
+                    break
+        assert widened > 0 and under.value == int((cnt < k).sum())
+        # bad arguments keep the reference's exception types
+        rc = h.lib.lmdhost_multi_scan_filtered(h.h, allowed.ctypes.data, allowed.size, q.ctypes.data, q.shape[0],
+                                               dims + 1, k, out.ctypes.data, cnt.ctypes.data, C.addressof(present),
+                                               C.addressof(under))
+        assert ERR[rc] == "BinderException"
 
 
 class Live:

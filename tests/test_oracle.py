@@ -257,3 +257,38 @@ def test_serial_build_is_searchable(oracle, fixtures_mod):
     ids, _, _, _ = oracle.search(blocks, bb, d, r, q, 10, 64, entry_row_id=entry)
     truth = fixtures_mod.brute_force_topk(x, q, 10, "L2", device="cpu")
     assert fixtures_mod.recall_at_k(ids, truth) >= 0.9
+
+
+# ---- filtered search (row f4): no reference code exists, so the restatement is checked through its properties ------
+@pytest.mark.parametrize("route,metric", [(0, 1), (1, 2)])
+def test_filtered_search_properties(oracle, fixtures_mod, route, metric):
+    n, dims, r, k, L = 2500, 64, 16, 10, 48
+    mname = {1: "L2", 2: "COSINE"}[metric]
+    ix = fixtures_mod.build_index(n, dims, r, metric=mname, device="cpu")
+    b, bb = ix["blocks"].numpy(), ix["layout"]["block_bytes"]
+    q = fixtures_mod.make_dataset(48, dims, seed=43, normalize=(metric == 2))
+    plain = oracle.search(b, bb, dims, r, q, k, L, metric=metric, route=route)
+    # 1. a filter that allows every row is the unfiltered search, expansion counters included
+    full = oracle.search(b, bb, dims, r, q, k, L, metric=metric, route=route, allowed=np.ones(n, dtype=bool))
+    assert all(np.array_equal(x, y) for x, y in zip(plain[:3], full[:3])) and np.array_equal(plain[3][:, 0], full[3][:, 0])
+    allowed = np.random.default_rng(1).random(n) < 0.3
+    f = oracle.search(b, bb, dims, r, q, k, L, metric=metric, route=route, allowed=allowed)
+    # 2. only allowed rows come back, ascending by exact distance, and the traversal is the unfiltered one
+    assert allowed[f[0][f[0] >= 0]].all()
+    assert np.array_equal(f[3][:, 0], plain[3][:, 0])
+    for qi in range(q.shape[0]):
+        d = f[1][qi, :f[2][qi]]
+        assert (np.diff(d) >= 0).all()
+    # 3. an allowed row of the unfiltered top-k is always in the filtered result (it was offered to RH with the same
+    #    distance and RH holds the L >= k best allowed rows)
+    if route == 0:
+        for qi in range(q.shape[0]):
+            keep = [i for i in plain[0][qi] if i >= 0 and allowed[i]]
+            assert set(keep) <= set(f[0][qi].tolist())
+    # 4. tunnelling keeps recall: the filtered result finds most of the true allowed neighbours
+    aid = np.nonzero(allowed)[0]
+    truth = aid[fixtures_mod.brute_force_topk(ix["x"][allowed], q, k, mname, device="cpu")]
+    assert fixtures_mod.recall_at_k(f[0], truth) >= (0.85 if route == 0 else 0.5)
+    # 5. nothing allowed -> nothing returned
+    none = oracle.search(b, bb, dims, r, q, k, L, metric=metric, route=route, allowed=np.zeros(n, dtype=bool))
+    assert (none[2] == 0).all() and (none[0] == -1).all()
