@@ -131,7 +131,28 @@ static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes
 		}
 	}
 	if (mode == 1 && !fits_exact(lg)) {
-		mode = 0;
+		// Stores beyond 2^(lg + 12) nodes (8.4 M at lg = 11) need more buckets for the exact (bucket, tag) identification:
+		// grow the table while the shared-memory budget allows it, and only then fall back to the 4-byte table - sized
+		// for ITS load factor, not for the 2-byte one (measured on 10 M x 96, L = 48: the undersized fallback cost 25 %).
+		const size_t budget = (size_t)227 * 1024 / 12;
+		uint32_t lg1 = lg;
+		while (lg1 < 15 && !fits_exact(lg1)) {
+			lg1++;
+		}
+		if (!(s->tune.filter_log2 >= 6) && fits_exact(lg1) && fixed_bytes + ((size_t)2 << lg1) <= budget) {
+			lg = lg1;
+		} else {
+			mode = 0;
+			if (!(s->tune.filter_log2 >= 6)) {
+				lg = 9;
+				while (lg < 15 && (double)(1u << lg) * 0.45 < expect) {
+					lg++;
+				}
+				while (lg > 9 && fixed_bytes + ((size_t)4 << lg) > (size_t)227 * 1024 / 16) {
+					lg--;
+				}
+			}
+		}
 	}
 	f.mode = (uint32_t)mode;
 	f.lg = lg;

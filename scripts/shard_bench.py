@@ -1,0 +1,217 @@
+#!/usr/bin/env python
+"""Multi-GPU measurement driver for BASELINE.json configs C3 / C4 / C5 (not part of the product; bench.py keeps the
+headline contract). One process per GPU under torchrun; data is generated ON the GPU (same clustered-latent recipe as
+fixtures.make_dataset, torch generator) and the graph is built by lmd_build_graph, so that nothing large crosses PCIe.
+
+  --mode replicated   C3 / C4: every rank holds the whole index, rank g searches its own query batch (no collective)
+  --mode sharded      C5: rank s holds rows [lo_s, hi_s) with a shard-local graph; every rank searches the FULL batch,
+                      one all-gather of [Q][k] (distance, row id) + lmd_merge_topk
+
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 \
+        scripts/shard_bench.py --mode sharded --rows 100000000 --dims 96 --nq 10000 --L 64
+
+Timing: barrier + CUDA events on the searching stream, max over ranks; rank 0 prints one JSON line."""
+import argparse
+import importlib
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def gen(n, dims, seed, device, normalize, latent=16, noise=0.05, chunk=1 << 20):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    a = np.random.default_rng(7).standard_normal((dims, latent))
+    q, _ = np.linalg.qr(a)
+    proj = torch.from_numpy(q.T.astype(np.float32)).to(device)
+    out = torch.empty((n, dims), dtype=torch.float32, device=device)
+    for s in range(0, n, chunk):
+        e = min(n, s + chunk)
+        z = torch.randn((e - s, latent), generator=g, device=device)
+        out[s:e] = z @ proj + noise * torch.randn((e - s, dims), generator=g, device=device)
+    if normalize:
+        out /= out.norm(dim=1, keepdim=True).clamp_min(1e-12)
+    return out
+
+
+def topk_scores(x, q, k, metric, base_id, q_tile=2500, b_tile=1 << 19):
+    """(scores [nq,k], ids [nq,k]) of the k best rows of x per query; score is monotone in the metric's distance and
+    comparable across shards (L2: |x|^2 - 2 q.x; IP / COSINE with unit rows: -q.x)."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    nq = q.shape[0]
+    S = torch.empty((nq, k), device=q.device)
+    I = torch.empty((nq, k), dtype=torch.int64, device=q.device)
+    for q0 in range(0, nq, q_tile):
+        a = q[q0:q0 + q_tile]
+        bs = bi = None
+        for b0 in range(0, x.shape[0], b_tile):
+            b = x[b0:b0 + b_tile]
+            s = a @ b.T
+            s = (b * b).sum(1)[None, :] - 2.0 * s if metric == "L2" else -s
+            ts, ti = torch.topk(s, min(k, b.shape[0]), dim=1, largest=False)
+            ti = ti + (b0 + base_id)
+            if bs is None:
+                bs, bi = ts, ti
+            else:
+                cs, ci = torch.cat([bs, ts], 1), torch.cat([bi, ti], 1)
+                bs, sel = torch.topk(cs, k, dim=1, largest=False)
+                bi = torch.gather(ci, 1, sel)
+        S[q0:q0 + q_tile], I[q0:q0 + q_tile] = bs, bi
+    torch.backends.cuda.matmul.allow_tf32 = old
+    return S, I
+
+
+def recall(found, truth):
+    f = found.unsqueeze(2) == truth.unsqueeze(1)
+    return float(f.any(dim=2).float().sum() / truth.numel())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mode", default="sharded", choices=["sharded", "replicated"])
+    ap.add_argument("--rows", dest="n", type=int, default=1_000_000, help="TOTAL rows")
+    ap.add_argument("--dims", type=int, default=96)
+    ap.add_argument("--r", type=int, default=32)
+    ap.add_argument("--nq", type=int, default=10_000, help="sharded: the batch; replicated: queries PER GPU")
+    ap.add_argument("--k", type=int, default=10)
+    ap.add_argument("--L", type=int, nargs="+", default=[64])
+    ap.add_argument("--l-insert", type=int, default=64)
+    ap.add_argument("--metric", default="L2")
+    ap.add_argument("--route", default="exact", choices=["exact", "ternary"])
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--tag", default="")
+    a = ap.parse_args()
+    rank, world, local = (int(os.environ.get(v, d)) for v, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG", "WARN")
+        dist.init_process_group("nccl", device_id=dev)
+    lmd = importlib.import_module("duckdb-lm-diskann_b200")
+    sh = importlib.import_module("duckdb-lm-diskann_b200.sharded")
+    cos = a.metric == "COSINE"
+    route = lmd.ROUTE_TERNARY if a.route == "ternary" else lmd.ROUTE_EXACT
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def log(*m):
+        if rank == 0:
+            print("[shard_bench]", *m, file=sys.stderr, flush=True)
+
+    t0 = time.time()
+    if a.mode == "sharded":
+        lo, hi = sh.shard_rows(a.n, rank, world)
+        x = gen(hi - lo, a.dims, 42 + rank, dev, cos)          # every shard its own stream of the same distribution
+        row_ids = torch.arange(lo, hi, dtype=torch.int64, device=dev)
+        q = gen(a.nq, a.dims, 43, dev, cos)                    # the same batch on every rank
+    else:
+        lo, hi = 0, a.n
+        x = gen(a.n, a.dims, 42, dev, cos)                     # the same index on every rank
+        row_ids = None
+        q = gen(a.nq, a.dims, 43 + 1000 * rank, dev, cos)      # every rank its own batch
+    torch.cuda.synchronize()
+    t_gen = time.time() - t0
+    store = lmd.Store(a.dims, a.r, metric=lmd.METRIC_BY_NAME[a.metric], capacity=hi - lo, device=local)
+    t0 = time.time()
+    store.upload_vectors(x, row_ids=row_ids)
+    bst = store.build_graph(l_insert=a.l_insert, alpha=1.2)
+    t_build = time.time() - t0
+    log("rows/rank %d, gen %.1f s, upload+build %.1f s (build kernels %.0f ms, %d rounds), store %.1f GB" % (
+        hi - lo, t_gen, t_build, bst.total_ms, bst.rounds, store.device_bytes / 1e9))
+
+    # ground truth: exact top-k per shard (or of the whole replica), merged across shards
+    t0 = time.time()
+    S, I = topk_scores(x, q, a.k, a.metric, lo)
+    if a.mode == "sharded" and world > 1:
+        allS = torch.empty((world,) + S.shape, device=dev)
+        allI = torch.empty((world,) + I.shape, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allS, S)
+        dist.all_gather_into_tensor(allI, I)
+        cs = allS.permute(1, 0, 2).reshape(a.nq, -1)
+        ci = allI.permute(1, 0, 2).reshape(a.nq, -1)
+        _, sel = torch.topk(cs, a.k, dim=1, largest=False)
+        truth = torch.gather(ci, 1, sel)
+    else:
+        truth = I
+    del S, I
+    torch.cuda.synchronize()
+    log("truth %.1f s" % (time.time() - t0))
+    del x
+    torch.cuda.empty_cache()
+
+    # a real (non-default) stream: the default stream's handle is 0, which lmd_store_set_stream reads as "own stream"
+    work = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(work)
+    store.set_stream(work.cuda_stream)
+    results = []
+    for L in a.L:
+        if a.mode == "sharded":
+            searcher = sh.DatasetShardedSearcher(store, device=dev)
+
+            def step():
+                return searcher.search(q, a.k, L, route=route)
+        else:
+            ids = torch.empty((a.nq, a.k), dtype=torch.int64, device=dev)
+            dd = torch.empty((a.nq, a.k), dtype=torch.float32, device=dev)
+
+            def step():
+                store.search_raw(q, a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=ids, out_dist=dd)
+                return ids, dd
+        for _ in range(a.warmup):
+            out = step()
+        st = store.search_raw(q, a.nq, a.k, L, route=route, out_ids=torch.empty((a.nq, a.k), dtype=torch.int64, device=dev))
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(a.steps):
+            out = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / a.steps], device=dev)
+        rec = torch.tensor([recall(out[0], truth)], device=dev)
+        kms = torch.tensor([st.traverse_ms + st.rerank_ms], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(kms, op=dist.ReduceOp.MAX)
+            if a.mode == "replicated":
+                dist.all_reduce(rec, op=dist.ReduceOp.SUM)
+                rec /= world
+        total_q = a.nq if a.mode == "sharded" else a.nq * world
+        row = {"L": L, "ms_per_step": round(float(ms), 4), "qps": round(total_q / (float(ms) * 1e-3), 1),
+               "recall_at_%d" % a.k: round(float(rec), 4), "local_kernel_ms_max": round(float(kms), 4),
+               "E_per_q": round(st.expansions / a.nq, 1), "V_per_q": round(st.distance_evals / a.nq, 1),
+               "local_algorithmic_GBps": round(st.algorithmic_bytes / (st.traverse_ms + st.rerank_ms) / 1e6, 1)}
+        if a.mode == "sharded":
+            row["allgather_bytes_per_rank"] = a.nq * a.k * 12
+        results.append(row)
+        log(row)
+    if rank == 0:
+        print(json.dumps({"driver": "scripts/shard_bench.py", "tag": a.tag, "mode": a.mode, "n_total": a.n,
+                          "dims": a.dims, "r": a.r, "metric": a.metric, "route": a.route, "n_gpus": world,
+                          "rows_per_gpu": hi - lo, "queries_per_step_total": a.nq if a.mode == "sharded" else a.nq * world,
+                          "k": a.k, "l_insert": a.l_insert, "steps": a.steps, "warmup": a.warmup,
+                          "gen_s": round(t_gen, 2), "upload_build_s": round(t_build, 2),
+                          "build_kernels_ms": round(bst.total_ms, 1), "store_GB_per_gpu": round(store.device_bytes / 1e9, 2),
+                          "data": "synthetic clustered-latent (torch CUDA generator)", "results": results}))
+    store.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
