@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liblmd_b200.so")
+LIB_PATH = os.environ.get("LMD_B200_LIB") or os.path.join(HERE, "liblmd_b200.so")  # the override is for kernel-tuning experiments
 
 # common/ann.hpp:16-32
 METRIC_L2, METRIC_COSINE, METRIC_IP = 1, 2, 3

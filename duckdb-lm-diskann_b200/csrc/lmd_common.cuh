@@ -79,6 +79,7 @@ struct Tuning {
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
 	int tie_slots = -1;    // -1 = default (64 for ternary routing, 0 for exact)
 	int prefetch_planes = 1; // ternary routing: prefetch the plane region of the likely next expansion into L2
+	int latency_mode = -1; // -1 = latency kernels for batches below ~10 queries per SM, 0 = never, 1 = always
 	int merge_min = 0;     // batch-merge new candidates when at least this many pass the threshold (0 = default 5)
 };
 

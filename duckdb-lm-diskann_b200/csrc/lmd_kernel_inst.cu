@@ -3,6 +3,7 @@
 //   -DLMD_INST_KIND=1 -DLMD_INST_METRIC=<1|2|3>                          rerank kernels of one metric
 //   -DLMD_INST_KIND=2 -DLMD_INST_METRIC=<1|2|3>                          RobustPrune kernels of one metric
 //   -DLMD_INST_KIND=3 -DLMD_INST_METRIC=<1|2|3> -DLMD_INST_ROUTE=<0|1>   FILTERED traversal kernels (row f4)
+//   -DLMD_INST_KIND=4 -DLMD_INST_METRIC=<1|2|3>                          LATENCY traversal kernels (small batches)
 // so that the shape x list-size variants of each family build in parallel with the others.
 #include "lmd_build_kernels.cuh"
 
@@ -23,6 +24,13 @@ lmd_status LMD_CAT(LMD_CAT(dispatch_traverse_filt_m, LMD_INST_METRIC), LMD_CAT(_
     KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st) {
 	LMD_DISPATCH_SHAPE_COARSE(traverse_kernel, LMD_INST_METRIC, LMD_INST_ROUTE, 1)
 	set_error("no filtered traversal kernel for this configuration (L=%u)", p.L);
+	return LMD_ERR_UNSUPPORTED;
+}
+#elif LMD_INST_KIND == 4
+lmd_status LMD_CAT(dispatch_traverse_lat_m, LMD_INST_METRIC)(KParams &p, const lmd_store *s, uint32_t nq, int lpl,
+                                                             cudaStream_t st) {
+	LMD_DISPATCH_SHAPE_LATENCY(traverse_kernel, LMD_INST_METRIC, 0)
+	set_error("no latency traversal kernel for this configuration (L=%u)", p.L);
 	return LMD_ERR_UNSUPPORTED;
 }
 #elif LMD_INST_KIND == 2

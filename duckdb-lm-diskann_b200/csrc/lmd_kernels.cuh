@@ -54,6 +54,7 @@ struct KParams {
 	// filtered search: bit `slot` set = the row passes the host's filter
 	const uint32_t *__restrict__ allowed;
 	uint32_t res_off; // byte offset of the results list RH inside the warp's shared memory
+	uint32_t latency; // host side only: dispatch to the latency variants
 };
 
 #define FULL 0xFFFFFFFFu
@@ -678,7 +679,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				visited_test_and_set(p, s_filter, p.entry_slot, n_evict);
 			}
 			__syncwarp();
-			compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, 1, lane);
+			compute_batch<TEAM, CH, (ROUTE == LMD_ROUTE_TERNARY ? 1 : G), METRIC>(Q, p, s_nb, s_d, s_d2, 1, lane);
 			__syncwarp();
 			const float d0 = finish_batch<METRIC>(s_d, s_d2, Q.na, 1, lane);
 			if (lane == 0) {
@@ -968,7 +969,10 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		return LMD_ERR_UNSUPPORTED;
 	}
 	// the occupancy queries cost several microseconds each: remember the answer per (kernel, shared memory) pair
-	const uint64_t cache_key = (uint64_t)(uintptr_t)kernel * 0x9E3779B97F4A7C15ull + p.warp_smem_bytes;
+	// a batch too small to give every SM a CTA of 4 warps runs one warp per CTA: the warps then spread over the SMs
+	// instead of sharing a few SMs' load / shared-memory pipes (small index-join chunks, single queries)
+	const bool spread = s->tune.warps_per_cta == 0 && nq <= (uint32_t)s->sm_count * 4;
+	const uint64_t cache_key = (uint64_t)(uintptr_t)kernel * 0x9E3779B97F4A7C15ull + p.warp_smem_bytes * 2ull + (spread ? 1 : 0);
 	int best_w = 0, best_ctas = 0;
 	auto hit = s->launch_cache.find(cache_key);
 	if (hit != s->launch_cache.end()) {
@@ -978,7 +982,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		// opt in to the full 227 KB once: the same kernel is launched with different list / filter sizes
 		LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
 		for (int w = 4; w >= 1; w >>= 1) {
-			const int forced = s->tune.warps_per_cta;
+			const int forced = spread ? 1 : s->tune.warps_per_cta;
 			if ((forced == 1 || forced == 2 || forced == 4) && w != forced) {
 				continue;
 			}
@@ -1056,9 +1060,25 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	} else if (p.row_floats == 96) {                                                                                   \
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                \
 	} else if (p.row_floats == 768) {                                                                                  \
-		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 6, 2, METRIC, ##__VA_ARGS__)                                               \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 6, 6, METRIC, ##__VA_ARGS__)                                               \
 	} else {                                                                                                           \
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                               \
+	}
+
+// Rows in flight per warp (G): 128 / 96-d rows are 512 / 384 bytes and the kernel wants many warps (G = 2, 72 registers,
+// 24 warps per SM); a 768-d row is 3 KB and one row per pass leaves the warp waiting on L2 thirteen times per expansion,
+// so G = 6 (18 KB in flight per warp, 242 registers, 8 warps per SM) - measured on 1 M x 768 cosine, L = 48, 10 k
+// queries: G = 2 8.72 ms, 3 7.90, 4 6.92, 5 6.99, 6 6.01 (profiles/r17_mode_sweep_d768_g*.json).
+//
+// Latency variants for small batches (fewer queries than the GPU has warp slots): the same kernel with G large enough
+// that ALL new neighbours of an expansion (<= 32) are gathered in one pass - every load of the expansion is in flight at
+// once, one HBM round trip instead of one per pass. Costs ~3x the registers, which a half-empty GPU does not miss.
+// Results are bit-identical to the throughput variants (G only changes how many rows are in flight).
+#define LMD_DISPATCH_SHAPE_LATENCY(KERNEL, METRIC, ...)                                                                \
+	if (p.row_floats == 128) {                                                                                         \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 4, 8, METRIC, ##__VA_ARGS__)                                                \
+	} else if (p.row_floats == 96) {                                                                                   \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 8, METRIC, ##__VA_ARGS__)                                                \
 	}
 
 #define LMD_DISPATCH_SHAPE(KERNEL, METRIC, ...)                                                                        \
@@ -1067,7 +1087,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	} else if (p.row_floats == 96) {                                                                                   \
 		LMD_DISPATCH_LPL(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                       \
 	} else if (p.row_floats == 768) {                                                                                  \
-		LMD_DISPATCH_LPL(KERNEL, 32, 6, 2, METRIC, ##__VA_ARGS__)                                                      \
+		LMD_DISPATCH_LPL(KERNEL, 32, 6, 6, METRIC, ##__VA_ARGS__)                                                      \
 	} else {                                                                                                           \
 		LMD_DISPATCH_LPL(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                                      \
 	}

@@ -1023,6 +1023,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 	s->launch_cache.clear();
 	if (k == "filter_log2") {
 		s->tune.filter_log2 = (int)value;
+	} else if (k == "latency_mode") {
+		s->tune.latency_mode = (int)value;
 	} else if (k == "prefetch_planes") {
 		s->tune.prefetch_planes = (int)value;
 	} else if (k == "filter_mode") {

@@ -498,3 +498,27 @@ def test_filter_goes_stale_when_rows_change(lmd, make_index):
             other.set_entry(0)
             with pytest.raises(lmd.LmdError):
                 other.search(q, 10, 40, filter=f3)
+
+
+# ---- latency variants (small batches): same results, bit for bit --------------------------------------------------
+@pytest.mark.parametrize("n,dims,r,metric,L", [(3000, 128, 32, "L2", 56), (2000, 96, 32, "L2", 100),
+                                               (1500, 768, 32, "COSINE", 48), (2000, 128, 64, "IP", 200),
+                                               (2500, 128, 32, "L2", 512)])
+def test_latency_kernels_equal_throughput_kernels(lmd, oracle, make_index, n, dims, r, metric, L):
+    ix = make_index(n, dims, r, metric=metric, kind="clustered", nq=96)
+    q = ix["queries"]
+    with _store(lmd, ix, dims, r, metric) as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        s.set_tuning("latency_mode", 0)
+        a = s.search(q, 10, L, qstats=True)
+        s.set_tuning("latency_mode", 1)
+        b = s.search(q, 10, L, qstats=True)
+        one = s.search(q[:1], 10, L)          # a single query: one warp per CTA
+        s.set_tuning("latency_mode", -1)
+        c = s.search(q, 10, L)                # 96 queries: picked automatically
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+    assert np.array_equal(a[4], b[4])         # same expansions and distance evaluations per query
+    assert np.array_equal(a[0], c[0]) and np.array_equal(a[0][:1], one[0])
+    o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q, 10, L, metric=METRIC[metric], entry_row_id=0)
+    check_parity(b[0], b[1], b[2], o[0], o[1], o[2], what="latency kernels %s" % metric)
