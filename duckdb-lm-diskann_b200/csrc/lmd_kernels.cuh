@@ -456,8 +456,8 @@ __device__ __forceinline__ uint64_t warp_sort_keys(uint64_t key, int lane) {
 // keys, LMD_KEY_NONE behind them) into s_list[0..n) in one pass. Every list entry and every batch key finds its
 // merged position by a binary search in the other sequence (s_bk = the batch in shared memory), then all of them are
 // written at once. The result equals cnt calls of list_insert() in neighbour order (core/Searcher.cpp:175-185)
-// whenever no batch key shares its DISTANCE with another batch key or a list entry: with distinct distances the
-// final list is the L smallest of the union, however the threshold moved in between. If such a tie (or a duplicate
+// unless a batch key ties with the distance that ends up L-th (see the rule inside): otherwise the final list is the
+// L smallest of the union by (distance, id), however the threshold moved in between. If such a tie (or a duplicate
 // of a listed node) exists, nothing is written and `fallback` is set: the caller replays the batch one by one.
 template <int LPL>
 __device__ __forceinline__ int list_merge_batch(uint64_t *s_list, uint64_t *s_bk, int n, int L, int cap, uint64_t bkey,
@@ -479,11 +479,35 @@ __device__ __forceinline__ int list_merge_batch(uint64_t *s_list, uint64_t *s_bk
 	if (lo < n && (s_list[lo] >> 1) < b1) {
 		lo++;
 	}
-	const uint32_t prev_hi = (uint32_t)(__shfl_up_sync(FULL, bkey, 1) >> 32);
+	// When does one merge equal the one-by-one admission of core/Searcher.cpp:175-185? Let w be the distance at merged
+	// position L - 1. Everything closer than w ends up listed either way, everything farther ends up outside either way;
+	// only elements AT distance w depend on the order of arrival (a candidate that ties with the current worst is turned
+	// away, one that arrived while the worst was still larger is not). Old list entries at w behave the same in both
+	// (evictions take the largest (distance, id) first), so the merge is exact unless a BATCH key sits at distance w -
+	// or repeats a listed node (a node the visited filter forgot). While the list is not full after the merge there is
+	// no threshold at all. Ties anywhere else - the normal case with integer ternary distances - are harmless.
 	bool tie = false;
 	if (lane < cnt) {
-		tie = (lo < n && (uint32_t)(s_list[lo] >> 32) == bhi) || (lo > 0 && (uint32_t)(s_list[lo - 1] >> 32) == bhi) ||
-		      (lane > 0 && prev_hi == bhi);
+		tie = lo < n && (s_list[lo] >> 1) == b1; // duplicate of a listed node
+	}
+	if (n + cnt > L) {
+		const int cb = __popc(__ballot_sync(FULL, lane < cnt && lane + lo <= L - 1)); // batch keys among the first L
+		uint32_t whi = 0;
+		if (cb > 0) {
+			whi = (uint32_t)(s_bk[cb - 1] >> 32);
+		}
+		if (L - cb > 0) {
+			const uint32_t lhi = (uint32_t)(s_list[L - cb - 1] >> 32);
+			whi = lhi > whi ? lhi : whi;
+		}
+		// ... and a batch key at distance w only matters when something else is at distance w too
+		const uint32_t prev_hi = (uint32_t)(__shfl_up_sync(FULL, bkey, 1) >> 32);
+		const uint32_t next_hi = (uint32_t)(__shfl_down_sync(FULL, bkey, 1) >> 32);
+		if (lane < cnt && bhi == whi) {
+			tie = tie || (lo < n && (uint32_t)(s_list[lo] >> 32) == bhi) ||
+			      (lo > 0 && (uint32_t)(s_list[lo - 1] >> 32) == bhi) || (lane > 0 && prev_hi == bhi) ||
+			      (lane + 1 < cnt && next_hi == bhi);
+		}
 	}
 	if (__any_sync(FULL, tie)) {
 		fallback = true;
@@ -794,7 +818,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				float worst = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
 				const bool pass = have && (n < L || d < worst);
 				uint32_t amask = __ballot_sync(FULL, pass);
-				if (ROUTE == LMD_ROUTE_EXACT && __popc(amask) >= (int)p.merge_min) {
+				if (__popc(amask) >= (int)p.merge_min) {
 					// same result as the one-by-one loop below, in one merge (see list_merge_batch)
 					const uint64_t bkey = warp_sort_keys(pass ? make_key(d, myid) : LMD_KEY_NONE, lane);
 					bool fallback = false;

@@ -113,7 +113,7 @@ static int lpl_for(uint32_t L) {
 struct FilterPlan {
 	uint32_t mode, lg, bytes;
 };
-static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes) {
+static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes, uint32_t route) {
 	FilterPlan f;
 	const double expect = 0.8 * (double)s->cfg.r * 1.05 * (double)L;
 	int mode = s->tune.filter_mode;
@@ -133,6 +133,16 @@ static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes
 		const size_t budget = (size_t)227 * 1024 / 16;
 		while (lg > 9 && fixed_bytes + ((size_t)(mode == 1 ? 2 : 4) << lg) > budget) {
 			lg--;
+		}
+		// Ternary routing over planes of 3+ words (D > 128): lane j reads neighbour j's planes with 8-byte loads that sit
+		// 8 * words bytes apart across the warp, so every 32-byte sector is fetched by four load instructions and the
+		// kernel lives on L1 hits - and L1 is whatever the CTAs' shared memory leaves of the SM's 256 KB. A 2 KB filter
+		// (4 KB per warp, 130 KB per SM) leaves L1 ~120 KB; the re-evaluations it causes cost 192 B each. Measured on
+		// 1 M x 768 cosine, L = 80: 2.59 ms per 10 k queries with the 8 KB filter, 2.78 with 4 KB, 1.78 with 2 KB
+		// (profiles/r23_tune_ternary.log). A warp-wide coalesced read of the plane region (every byte requested once)
+		// was tried and took the L1 dependence away, but at 2.1 ms it lost to this (profiles/r24_tune_ternary.log).
+		if (route == LMD_ROUTE_TERNARY && s->words > 2 && lg > 10) {
+			lg = 10;
 		}
 	}
 	if (mode == 1 && !fits_exact(lg)) {
@@ -274,7 +284,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0);
 	const size_t res_bytes = a.d_allowed ? (size_t)lpl * 32 * 8 : 0; // the results list RH of a filtered search
 	fixed += res_bytes;
-	const FilterPlan fp = pick_filter(s, a.L, fixed);
+	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route);
 	p.filter_mode = fp.mode;
 	p.filter_bytes = fp.bytes;
 	p.filter_mask = (1u << fp.lg) - 1;

@@ -90,6 +90,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--tag", default="")
+    ap.add_argument("--tune", nargs="*", default=[], help="lmd_set_tuning pairs, e.g. merge_min=3 tie_slots=32")
     a = ap.parse_args()
     rank, world, local = (int(os.environ.get(v, d)) for v, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -153,6 +154,9 @@ def main():
     del x
     torch.cuda.empty_cache()
 
+    for kv in a.tune:
+        key, val = kv.split("=")
+        store.set_tuning(key, int(val))
     # a real (non-default) stream: the default stream's handle is 0, which lmd_store_set_stream reads as "own stream"
     work = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(work)
@@ -194,14 +198,17 @@ def main():
         row = {"L": L, "ms_per_step": round(float(ms), 4), "qps": round(total_q / (float(ms) * 1e-3), 1),
                "recall_at_%d" % a.k: round(float(rec), 4), "local_kernel_ms_max": round(float(kms), 4),
                "E_per_q": round(st.expansions / a.nq, 1), "V_per_q": round(st.distance_evals / a.nq, 1),
-               "local_algorithmic_GBps": round(st.algorithmic_bytes / (st.traverse_ms + st.rerank_ms) / 1e6, 1)}
+               "local_algorithmic_GBps": round(st.algorithmic_bytes / (st.traverse_ms + st.rerank_ms) / 1e6, 1),
+               "traverse_ms": round(st.traverse_ms, 4), "rerank_ms": round(st.rerank_ms, 4),
+               "tie_overflows": st.tie_overflows, "merge_fallbacks_per_q": round(st.merge_fallbacks / a.nq, 2),
+               "filter_evictions_per_q": round(st.filter_evictions / a.nq, 2)}
         if a.mode == "sharded":
             row["allgather_bytes_per_rank"] = a.nq * a.k * 12
         results.append(row)
         log(row)
     if rank == 0:
         print(json.dumps({"driver": "scripts/shard_bench.py", "tag": a.tag, "mode": a.mode, "n_total": a.n,
-                          "dims": a.dims, "r": a.r, "metric": a.metric, "route": a.route, "n_gpus": world,
+                          "dims": a.dims, "r": a.r, "metric": a.metric, "route": a.route, "tune": a.tune, "n_gpus": world,
                           "rows_per_gpu": hi - lo, "queries_per_step_total": a.nq if a.mode == "sharded" else a.nq * world,
                           "k": a.k, "l_insert": a.l_insert, "steps": a.steps, "warmup": a.warmup,
                           "gen_s": round(t_gen, 2), "upload_build_s": round(t_build, 2),

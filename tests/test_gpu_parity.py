@@ -49,7 +49,7 @@ def test_exact_routing_parity(lmd, oracle, make_index, n, dims, r, metric, kind,
 
 
 @pytest.mark.parametrize("metric", ["COSINE", "IP"])
-@pytest.mark.parametrize("dims,r", [(128, 32), (768, 32), (96, 64), (100, 24)])
+@pytest.mark.parametrize("dims,r", [(128, 32), (768, 32), (96, 64), (100, 24), (200, 40), (768, 64)])
 def test_ternary_routing_parity(lmd, oracle, make_index, metric, dims, r):
     n, k, L = 1500, 10, 64
     ix = make_index(n, dims, r, metric=metric, kind="iid", nq=64)
