@@ -94,6 +94,7 @@ SYMBOLS = [
     ("lmd_search_batch_filtered", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                              _P, _P, _P, _P, C.POINTER(Stats)]),
     ("lmd_merge_topk", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P]),
+    ("lmd_merge_topk_async", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P, _P]),
     ("lmd_store_upload_vectors", C.c_int32, [_P, _P, _P, C.c_uint64]),
     ("lmd_build_graph", C.c_int32, [_P, C.POINTER(BuildParams), C.POINTER(BuildStats)]),
     ("lmd_robust_prune_batch", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_float, _P, _P]),
@@ -340,6 +341,12 @@ class Filter:
 
     def __exit__(self, *a):
         self.close()
+
+
+def merge_topk_async(ids, dist, shards, nq, k, out_ids, out_dist, device=0, cuda_stream=0):
+    """Device buffers; enqueued on `cuda_stream` (a raw cudaStream_t address, 0 = default stream), no synchronisation."""
+    _check(lib().lmd_merge_topk_async(device, _ptr(ids), _ptr(dist), shards, nq, k, _ptr(out_ids), _ptr(out_dist),
+                                      cuda_stream or None))
 
 
 def merge_topk(ids, dist, shards, nq, k, out_ids, out_dist, device=0):

@@ -316,6 +316,27 @@ lmd_status lmd_search_batch_filtered(lmd_store *s, const lmd_filter *filter, con
 	return search_impl(s, filter, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
 }
 
+lmd_status lmd_merge_topk_async(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq,
+                                uint32_t k, int64_t *out_ids, float *out_dist, void *cuda_stream) {
+	if (!ids || !dist || !out_ids || !out_dist) {
+		set_error("lmd_merge_topk_async: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (k == 0 || shards == 0 || shards > 64) {
+		set_error("lmd_merge_topk_async: k must be > 0 and shards in [1, 64]");
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (nq == 0) {
+		return LMD_OK;
+	}
+	LMD_CUDA_OK(cudaSetDevice(device));
+	if (!on_device(ids) || !on_device(dist) || !on_device(out_ids) || !on_device(out_dist)) {
+		set_error("lmd_merge_topk_async: all four buffers must be device (or pinned) memory");
+		return LMD_ERR_INVALID_ARG;
+	}
+	return launch_merge_topk(ids, dist, shards, nq, k, out_ids, out_dist, (cudaStream_t)cuda_stream);
+}
+
 lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq, uint32_t k,
                           int64_t *out_ids, float *out_dist) {
 	if (!ids || !dist || !out_ids || !out_dist) {

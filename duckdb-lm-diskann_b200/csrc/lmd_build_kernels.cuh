@@ -251,7 +251,7 @@ static lmd_status launch_prune(K kernel, PruneParams &p, const lmd_store *s, cud
 	} else if (p.kp.row_floats == 96) {                                                                                \
 		return launch_prune(prune_kernel<8, 3, 2, METRIC>, p, s, st);                                                  \
 	} else if (p.kp.row_floats == 768) {                                                                               \
-		return launch_prune(prune_kernel<32, 6, 4, METRIC>, p, s, st);                                                 \
+		return launch_prune(prune_kernel<32, 6, 6, METRIC>, p, s, st);                                                 \
 	} else {                                                                                                           \
 		return launch_prune(prune_kernel<32, 0, 1, METRIC>, p, s, st);                                                 \
 	}

@@ -800,6 +800,15 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 					const bool ok = have && slot_allowed(p, myid) && (nres < L || d < rworst);
 					uint32_t rmask = __ballot_sync(FULL, ok);
 					uint32_t dummy = 0;
+					if (__popc(rmask) >= (int)p.merge_min) { // same batch merge as EH below (s_bk is free until then)
+						const uint64_t rkey = warp_sort_keys(ok ? make_key(d, myid) : LMD_KEY_NONE, lane);
+						bool rfall = false;
+						nres = list_merge_batch<LPL>(s_res, s_bk, nres, L, L, rkey, __popc(rmask), lane, dummy, rfall);
+						__syncwarp();
+						if (!rfall) {
+							rmask = 0;
+						}
+					}
 					while (rmask) {
 						const int src = __ffs(rmask) - 1;
 						rmask &= rmask - 1;

@@ -76,19 +76,29 @@ class QueryShardedSearcher:
 
 
 def _cuda_local_search(store, queries_dev, nq, k, L, route):
-    """Device-resident search through the C ABI: returns (ids [nq,k] i64, dist [nq,k] f32) torch tensors on the GPU."""
+    """Device-resident search through the C ABI: returns (ids [nq,k] i64, dist [nq,k] f32) torch tensors on the GPU.
+    On a non-default torch stream the store is bound to that stream and the search is only ENQUEUED (the all-gather and
+    the merge follow on the same stream, no host round trip); on the default stream (handle 0, which the C ABI reads as
+    "the store's own stream") the call synchronises before the collectives are issued."""
+    from . import SEARCH_ASYNC
     dev = queries_dev.device
     ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
     d = torch.empty((nq, k), dtype=torch.float32, device=dev)
-    store.search_raw(queries_dev, nq, k, L, route=route, out_ids=ids, out_dist=d)
+    cur = torch.cuda.current_stream(dev).cuda_stream
+    if getattr(store, "_bound_stream", 0) != cur:
+        store.set_stream(cur or None)
+        store._bound_stream = cur
+    store.search_raw(queries_dev, nq, k, L, route=route, flags=SEARCH_ASYNC if cur else 0, out_ids=ids, out_dist=d,
+                     stats=False)
     return ids, d
 
 
 def _cuda_merge(all_ids, all_d, shards, nq, k, device_index):
-    from . import merge_topk  # the C ABI (lmd_merge_topk)
+    from . import merge_topk_async  # the C ABI (lmd_merge_topk_async): same stream as the all-gather before it
     out_ids = torch.empty((nq, k), dtype=torch.int64, device=all_ids.device)
     out_d = torch.empty((nq, k), dtype=torch.float32, device=all_ids.device)
-    merge_topk(all_ids, all_d, shards, nq, k, out_ids, out_d, device=device_index)
+    merge_topk_async(all_ids, all_d, shards, nq, k, out_ids, out_d, device=device_index,
+                     cuda_stream=torch.cuda.current_stream(all_ids.device).cuda_stream)
     return out_ids, out_d
 
 

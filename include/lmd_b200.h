@@ -170,6 +170,13 @@ lmd_status lmd_search_batch_filtered(lmd_store *s, const lmd_filter *filter, con
 lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq, uint32_t k,
                           int64_t *out_ids, float *out_dist);
 
+/* The same merge enqueued on the caller's stream (a cudaStream_t passed as void*, NULL = the default stream) without
+ * synchronising: device buffers only. This is the form the sharded searcher uses - search (LMD_SEARCH_ASYNC on a store
+ * bound to that stream with lmd_store_set_stream), all-gather and merge then run back to back on ONE stream with no host
+ * round trip in between. */
+lmd_status lmd_merge_topk_async(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq,
+                                uint32_t k, int64_t *out_ids, float *out_dist, void *cuda_stream);
+
 /* --- graph write side: replaces core/GraphManager.cpp:65-203 (AddNode, one row at a
  *     time) and :259-457 (RobustPrune) by a batch-parallel build on the device. Writes the same node blocks, including
  *     the ternary planes of every neighbour, which nothing in the reference writes (GraphManager.cpp:402-444). --- */
