@@ -2,6 +2,8 @@
 #include "gpu_searcher.hpp"
 
 #include <algorithm>
+#include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <iostream>
 #include <stdexcept>
@@ -410,6 +412,20 @@ common::idx_t AllowedIds::Count() const {
 	return lmd_filter_count(filter_);
 }
 
+// The plan: "L_search ... potentially automatically increased for filtered queries". The exploration list holds the L
+// closest rows of ANY kind, of which only a fraction f passes the filter, so the list is widened by 1 / sqrt(f), at most
+// eightfold and never beyond the build's limit of 512. Measured on 1 M x 128 (profiles/r27_filtered_1m_d128.json):
+// recall over the allowed rows at f = 0.1 is 0.85 at L = 64 and 0.97 at L = 205; at f = 0.01, 0.53 and 0.93 (L = 512).
+uint32_t GpuSearcher::FilteredListSize(uint32_t L, common::idx_t allowed_rows, common::idx_t total_rows) {
+	if (allowed_rows == 0 || total_rows == 0 || allowed_rows >= total_rows) {
+		return L;
+	}
+	double scale = std::sqrt(static_cast<double>(total_rows) / static_cast<double>(allowed_rows));
+	scale = std::min(8.0, scale);
+	const double wide = std::ceil(static_cast<double>(L) * scale);
+	return static_cast<uint32_t>(std::min(512.0, std::max(static_cast<double>(L), wide)));
+}
+
 common::idx_t GpuSearcher::SearchBatchFiltered(const AllowedIds &allowed, const float *queries, common::idx_t nq,
                                                common::idx_t k_neighbors, common::idx_t search_list_size,
                                                common::row_t *out_ids, float *out_dist, uint32_t *out_count,
@@ -428,6 +444,9 @@ common::idx_t GpuSearcher::SearchBatchFiltered(const AllowedIds &allowed, const 
 		L = k_neighbors > 20 ? static_cast<uint32_t>(k_neighbors) + 20 : 40; // core/Searcher.cpp:261-265
 	}
 	L = std::max<uint32_t>(L, static_cast<uint32_t>(k_neighbors));
+	if (widen) {
+		L = FilteredListSize(L, allowed.Count(), store_->NodeCount());
+	}
 	Check(lmd_search_batch_filtered(store_->Handle(), allowed.Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
 	                                L, static_cast<uint32_t>(route_), 0, out_ids, out_dist, out_count, nullptr, nullptr),
 	      "GpuSearcher::SearchBatchFiltered");
@@ -574,8 +593,12 @@ common::idx_t GpuIndexScan::MultiScanFiltered(const AllowedIds &allowed, const f
 		const common::idx_t under = gpu->SearchBatchFiltered(allowed, queries, nq, k, L, out_ids, nullptr, out_count);
 		if (under) {
 			// the plan: "issue a warning ... suggesting to increase L_search"
-			std::cerr << "LM_DISKANN: " << under << " filtered scan(s) found fewer than k=" << k
-			          << " rows that satisfy the filter; consider increasing L_SEARCH" << std::endl;
+			// (plain stdio: formatting an integer through std::cerr crashed inside a Python host whose other extension
+			// modules carry their own libstdc++ locale state)
+			std::fprintf(stderr,
+			             "LM_DISKANN: %llu filtered scan(s) found fewer than k=%llu rows that satisfy the filter; "
+			             "consider increasing L_SEARCH\n",
+			             (unsigned long long)under, (unsigned long long)k);
 		}
 		return under;
 	} catch (const std::exception &e) {

@@ -216,13 +216,17 @@ public:
 	void SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors, common::idx_t search_list_size,
 	                 common::row_t *out_ids, float *out_dist, uint32_t *out_count, lmd_stats *stats = nullptr);
 
-	// Filtered form (dual heap: exploration over all rows, results over `allowed` only). When `widen` is set, queries
-	// that met fewer than k allowed rows are searched again with L doubled, up to the build's limit of 512 - the
-	// plan's "L_search ... automatically increased for filtered queries". Returns the number of queries that still
+	// Filtered form (dual heap: exploration over all rows, results over `allowed` only). When `widen` is set the list
+	// starts at FilteredListSize(L, allowed rows, all rows) and queries that still met fewer than k allowed rows are
+	// searched again with L doubled, up to the build's limit of 512 - the plan's "L_search ... automatically increased
+	// for filtered queries". Returns the number of queries that still
 	// have fewer than k results (the host warns the user, as the plan says).
 	common::idx_t SearchBatchFiltered(const AllowedIds &allowed, const float *queries, common::idx_t nq,
 	                                  common::idx_t k_neighbors, common::idx_t search_list_size, common::row_t *out_ids,
 	                                  float *out_dist, uint32_t *out_count, bool widen = true);
+
+	// L widened by 1 / sqrt(allowed fraction), at most 8 x and at most 512.
+	static uint32_t FilteredListSize(uint32_t L, common::idx_t allowed_rows, common::idx_t total_rows);
 
 	DeviceNodeStore &Store() {
 		return *store_;

@@ -309,7 +309,7 @@ def test_filtered_multi_scan_widens_short_scans(oracle, make_index, fixtures_mod
     rid = np.arange(n, dtype=np.int64) * 7 + 3
     ix = make_index(n, dims, r, metric="L2", kind="clustered", nq=40, row_ids=rid)
     q = ix["queries"]
-    allowed_mask = np.random.default_rng(8).random(n) < 0.02   # ~80 rows: L = 16 rarely meets 10 of them
+    allowed_mask = np.random.default_rng(8).random(n) < 0.004   # ~16 rows: even the widened list rarely meets 10
     allowed = rid[allowed_mask]
     with Host(_lib(), ix["blocks_np"], ix["block_bytes"], dims, r, row_ids=rid, entry=int(rid[0]), l_search=16) as h:
         out = np.full((q.shape[0], k), -1, dtype=np.int64)
@@ -321,18 +321,24 @@ def test_filtered_multi_scan_widens_short_scans(oracle, make_index, fixtures_mod
         assert rc == 0, h.lib.lmdhost_last_error().decode()
         assert present.value == allowed.size
         assert np.isin(out[out >= 0], allowed).all()
-        # every scan equals the oracle's filtered search at the list size the adapter ended with for it
+        # the adapter starts at L widened by 1 / sqrt(allowed fraction) (GpuSearcher::FilteredListSize) and doubles it for
+        # scans that still come back short; every scan equals the oracle's filtered search at the size it ended with
+        import math
+        L0 = min(512, max(16, math.ceil(16 * min(8.0, math.sqrt(n / allowed.size)))))
+        sizes = [L0]
+        while sizes[-1] < 512:
+            sizes.append(min(512, sizes[-1] * 2))
         by_L = {L: oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q, k, L, row_ids=rid,
-                                 entry_row_id=int(rid[0]), allowed=allowed_mask) for L in (16, 32, 64, 128, 256, 512)}
+                                 entry_row_id=int(rid[0]), allowed=allowed_mask) for L in sizes}
         widened = 0
         for qi in range(q.shape[0]):
-            for L in (16, 32, 64, 128, 256, 512):
+            for L in sizes:
                 o = by_L[L]
                 if o[2][qi] >= k or L == 512:
                     assert cnt[qi] == o[2][qi] and np.array_equal(out[qi], o[0][qi]), (qi, L)
-                    widened += L > 16
+                    widened += L > sizes[0]
                     break
-        assert widened > 0 and under.value == int((cnt < k).sum())
+        assert L0 > 16 and under.value == int((cnt < k).sum())
         # bad arguments keep the reference's exception types
         rc = h.lib.lmdhost_multi_scan_filtered(h.h, allowed.ctypes.data, allowed.size, q.ctypes.data, q.shape[0],
                                                dims + 1, k, out.ctypes.data, cnt.ctypes.data, C.addressof(present),
