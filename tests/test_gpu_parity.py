@@ -327,6 +327,18 @@ def test_merge_topk(lmd):
         cand.sort()
         assert [c[1] for c in cand[:k]] == out_i[q].tolist()
         assert np.array_equal(np.array([c[0] for c in cand[:k]], dtype=np.float32), out_d[q])
+    # the stream-ordered form (device buffers, caller's stream, no synchronisation inside) gives the same lists
+    import torch
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        d_ids, d_dist = torch.from_numpy(ids).cuda(), torch.from_numpy(dist).cuda()
+        o_i = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        o_d = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+        lmd.merge_topk_async(d_ids, d_dist, G, nq, k, o_i, o_d, cuda_stream=st.cuda_stream)
+    st.synchronize()
+    assert np.array_equal(o_i.cpu().numpy(), out_i) and np.array_equal(o_d.cpu().numpy(), out_d)
+    with pytest.raises(lmd.LmdError):  # host memory is refused rather than staged
+        lmd.merge_topk_async(ids, dist, G, nq, k, out_i, out_d)
 
 
 def test_recall_matches_oracle_10k(lmd, oracle, fixtures_mod):

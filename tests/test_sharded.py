@@ -129,6 +129,13 @@ def _worker(rank, world, port, mode, use_cuda, case, k, L, ret):
                     return torch.from_numpy(i), torch.from_numpy(dd)
                 s = sh.DatasetShardedSearcher(ostore, device=gather_dev, local_search=local, merge=merge)
             ids, d = s.search(case["q"], k, L)
+            if use_cuda:
+                # again on a side stream: the store is bound to it, search and merge are only enqueued (no host sync)
+                side = torch.cuda.Stream(device="cuda:%d" % cuda_dev)
+                with torch.cuda.stream(side):
+                    ids2, d2 = s.search(case["q"], k, L)
+                    ids2, d2 = ids2.cpu(), d2.cpu()
+                assert torch.equal(ids2, ids.cpu()) and torch.equal(d2, d.cpu())
             ret[rank] = (ids.cpu().numpy(), d.cpu().numpy(), s.last_gather_bytes)
         dist.barrier()
     finally:
