@@ -714,7 +714,15 @@ lmd_status lmd_store_apply(lmd_store *s, const int64_t *row_ids, const void *blo
 	const uint64_t bb = s->cfg.block_bytes;
 	const uint64_t chunk = 16384; // blocks staged per pass (64 MiB at 4 KiB blocks)
 	if (s->apply_cap < (n < chunk ? n : chunk)) {
-		uint64_t cap = n < chunk ? (n < 64 ? 64 : n) : chunk;
+		// grow in powers of two from 1024 blocks: a host that flushes a few dirty blocks per insert must not pay a
+		// cudaFree + cudaMalloc round (tens of milliseconds) whenever a batch is a little larger than the last one
+		uint64_t cap = 1024;
+		while (cap < n && cap < chunk) {
+			cap <<= 1;
+		}
+		if (cap > s->capacity && s->capacity >= 64) {
+			cap = s->capacity;
+		}
 		cudaFree(s->d_apply);
 		cudaFree(s->d_apply_rids);
 		cudaFree(s->d_apply_slots);
