@@ -1,0 +1,122 @@
+"""-m gpu: the CUDA path at BASELINE.json's full sizes (1 M rows, 10 k queries, k = 10: the headline 128-d L2 shape, the
+768-d cosine shape with exact and with ternary routing, the 96-d shape), checked through properties that do not need a
+CPU run of the whole batch - sortedness, exactness of the returned distances, idempotence
+across kernel variants and filter sizes, recall against brute force - plus ID parity against the CPU oracle on a sample
+of the queries (the oracle reads the index as the device built it, downloaded through the C ABI)."""
+import numpy as np
+import pytest
+
+from parity import check_parity
+
+pytestmark = pytest.mark.gpu
+
+N, R, NQ, K = 1_000_000, 32, 10_000, 10
+METRIC = {"L2": 1, "COSINE": 2}
+SHAPES = [
+    # dims, metric, route, L, minimum recall@10
+    (128, "L2", 0, 64, 0.93),       # BASELINE.json configs[1], the headline
+    (768, "COSINE", 0, 48, 0.96),   # configs[2], exact routing
+    (768, "COSINE", 1, 80, 0.94),   # configs[2], ternary (compressed-neighbour) routing + exact rerank
+    (96, "L2", 0, 64, 0.90),        # the row shape of configs[3] / [4] at 1 M rows
+]
+
+
+def _gen(torch, n, seed, dev, DIMS, normalize):
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    a = np.random.default_rng(7).standard_normal((DIMS, 16))
+    q, _ = np.linalg.qr(a)
+    proj = torch.from_numpy(q.T.astype(np.float32)).to(dev)
+    out = torch.empty((n, DIMS), dtype=torch.float32, device=dev)
+    for s in range(0, n, 1 << 18):
+        e = min(n, s + (1 << 18))
+        z = torch.randn((e - s, 16), generator=g, device=dev)
+        out[s:e] = z @ proj + 0.05 * torch.randn((e - s, DIMS), generator=g, device=dev)
+    if normalize:
+        out /= out.norm(dim=1, keepdim=True).clamp_min(1e-12)
+    return out
+
+
+@pytest.mark.parametrize("DIMS,metric,route,L,min_recall", SHAPES)
+def test_full_size_properties_and_sample_parity(lmd, oracle, DIMS, metric, route, L, min_recall):
+    import torch
+    dev = torch.device("cuda", 0)
+    free, _ = torch.cuda.mem_get_info(dev)
+    if free < 40 << 30:
+        pytest.skip("needs ~40 GB of free device memory")
+    cos = metric == "COSINE"
+    x = _gen(torch, N, 42, dev, DIMS, cos)
+    q = _gen(torch, NQ, 43, dev, DIMS, cos)
+    with lmd.Store(DIMS, R, metric=METRIC[metric], capacity=N, l_search=100) as s:
+        s.upload_vectors(x)
+        bst = s.build_graph(l_insert=64)
+        assert bst.nodes == N
+
+        def run(**tune):
+            for key, val in tune.items():
+                s.set_tuning(key, val)
+            ids = torch.empty((NQ, K), dtype=torch.int64, device=dev)
+            dist = torch.empty((NQ, K), dtype=torch.float32, device=dev)
+            cnt = torch.empty((NQ,), dtype=torch.int32, device=dev)
+            st = s.search_raw(q, NQ, K, L, route=route, out_ids=ids, out_dist=dist, out_count=cnt)
+            return ids, dist, cnt, st
+
+        ids, dist, cnt, st = run()
+        # 1. every query is answered in full, ascending by distance, ids in range and distinct per query
+        assert bool((cnt == K).all())
+        assert bool((dist[:, 1:] >= dist[:, :-1]).all())
+        assert bool(((ids >= 0) & (ids < N)).all())
+        assert bool((torch.sort(ids, dim=1).values.diff(dim=1) != 0).all())
+        # 2. the returned distances ARE the exact distances of the returned rows (fp64 recomputation, 1e-5 relative)
+        xr, qr = x[ids.reshape(-1)].double(), q.repeat_interleave(K, dim=0).double()
+        if cos:  # core/distance.hpp:75-99
+            ref = 1.0 - ((xr * qr).sum(1) / (xr.pow(2).sum(1).sqrt() * qr.pow(2).sum(1).sqrt())).clamp(-1.0, 1.0)
+        else:
+            ref = (xr - qr).pow(2).sum(1).sqrt()
+        ref = ref.reshape(NQ, K)
+        # cosine distances of near neighbours are differences of numbers close to 1: fp32 leaves ~1e-7 absolute
+        assert bool(((dist.double() - ref).abs() <= 1e-5 * ref.abs() + (2e-6 if cos else 1e-12)).all())
+        del xr, qr
+        # 3. idempotence: the same call again, the small-batch kernels forced on, and a visited filter 16 x smaller
+        #    (which forgets and re-evaluates) all return the same ids and the same distance bits
+        for tune in ({}, {"latency_mode": 1}, {"latency_mode": -1, "filter_log2": 8}):
+            i2, d2, _, st2 = run(**tune)
+            assert torch.equal(i2, ids) and torch.equal(d2.view(torch.int32), dist.view(torch.int32)), tune
+        assert st2.filter_evictions > st.filter_evictions
+        s.set_tuning("filter_log2", 0)
+        # 4. recall@10 against brute force over all 1 M rows
+        old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        truth = torch.empty((NQ, K), dtype=torch.int64, device=dev)
+        for q0 in range(0, NQ, 2500):
+            a = q[q0:q0 + 2500]
+            best_s = best_i = None
+            for b0 in range(0, N, 1 << 18):
+                b = x[b0:b0 + (1 << 18)]
+                sc = -(a @ b.T) if cos else (b * b).sum(1)[None, :] - 2.0 * (a @ b.T)
+                ts, ti = torch.topk(sc, K, dim=1, largest=False)
+                ti = ti + b0
+                if best_s is None:
+                    best_s, best_i = ts, ti
+                else:
+                    cs, ci = torch.cat([best_s, ts], 1), torch.cat([best_i, ti], 1)
+                    best_s, sel = torch.topk(cs, K, dim=1, largest=False)
+                    best_i = torch.gather(ci, 1, sel)
+            truth[q0:q0 + 2500] = best_i
+        torch.backends.cuda.matmul.allow_tf32 = old
+        recall = float((ids.unsqueeze(2) == truth.unsqueeze(1)).any(dim=2).float().mean())
+        assert recall >= min_recall, recall
+        # 5. ID / distance parity with the CPU oracle on a sample of the batch, on the index as the device built it
+        sample = np.arange(0, NQ, NQ // 200)[:200]
+        blocks = s.download_blocks(0, N)
+        qs = q[torch.from_numpy(sample).to(dev)].cpu().numpy()
+        o = oracle.search(blocks, s.block_bytes, DIMS, R, qs, K, L, metric=METRIC[metric], route=route, entry_row_id=0)
+        ties, total = check_parity(ids.cpu().numpy()[sample], dist.cpu().numpy()[sample],
+                                   cnt.cpu().numpy()[sample].astype(np.uint32), o[0], o[1], o[2], what="1M sample")
+        assert ties <= total // 200
+        o_recall = float((torch.from_numpy(o[0]).to(dev).unsqueeze(2) ==
+                          truth[torch.from_numpy(sample).to(dev)].unsqueeze(1)).any(dim=2).float().mean())
+        g_recall = float((ids[torch.from_numpy(sample).to(dev)].unsqueeze(2) ==
+                          truth[torch.from_numpy(sample).to(dev)].unsqueeze(1)).any(dim=2).float().mean())
+        # recall equal to the reference's on the same queries (ids inside a 1e-5 distance tie may swap in or out)
+        assert abs(o_recall - g_recall) <= ties / float(total) + 1e-9
