@@ -120,3 +120,63 @@ def test_full_size_properties_and_sample_parity(lmd, oracle, DIMS, metric, route
                           truth[torch.from_numpy(sample).to(dev)].unsqueeze(1)).any(dim=2).float().mean())
         # recall equal to the reference's on the same queries (ids inside a 1e-5 distance tie may swap in or out)
         assert abs(o_recall - g_recall) <= ties / float(total) + 1e-9
+
+
+def test_ten_million_rows_properties(lmd):
+    """configs[3] shape: 10 M x 96 L2 (46 GB of node blocks, a visited filter sized for a store above 2^23 rows).
+    Properties only - the index is too large to hand to the CPU oracle inside a test."""
+    import torch
+    dev = torch.device("cuda", 0)
+    free, _ = torch.cuda.mem_get_info(dev)
+    if free < 80 << 30:
+        pytest.skip("needs ~80 GB of free device memory")
+    n, dims, nq, L = 10_000_000, 96, 10_000, 96
+    x = _gen(torch, n, 42, dev, dims, False)
+    q = _gen(torch, nq, 43, dev, dims, False)
+    with lmd.Store(dims, R, capacity=n) as s:
+        s.upload_vectors(x)
+        assert s.build_graph(l_insert=64).nodes == n
+        ids = torch.empty((nq, K), dtype=torch.int64, device=dev)
+        dist = torch.empty((nq, K), dtype=torch.float32, device=dev)
+        cnt = torch.empty((nq,), dtype=torch.int32, device=dev)
+        st = s.search_raw(q, nq, K, L, out_ids=ids, out_dist=dist, out_count=cnt)
+        assert bool((cnt == K).all()) and bool((dist[:, 1:] >= dist[:, :-1]).all())
+        assert bool(((ids >= 0) & (ids < n)).all())
+        ref = (x[ids.reshape(-1)].double() - q.repeat_interleave(K, dim=0).double()).pow(2).sum(1).sqrt().reshape(nq, K)
+        assert bool(((dist.double() - ref).abs() <= 1e-5 * ref.abs() + 1e-12).all())
+        s.set_tuning("filter_mode", 0)  # the 4-byte table instead of the two-choice buckets: same answer
+        i2 = torch.empty_like(ids)
+        d2 = torch.empty_like(dist)
+        s.search_raw(q, nq, K, L, out_ids=i2, out_dist=d2)
+        assert torch.equal(i2, ids) and torch.equal(d2.view(torch.int32), dist.view(torch.int32))
+        old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        hits = 0
+        for q0 in range(0, nq, 2500):
+            a = q[q0:q0 + 2500]
+            best_s = best_i = None
+            for b0 in range(0, n, 1 << 19):
+                b = x[b0:b0 + (1 << 19)]
+                sc = (b * b).sum(1)[None, :] - 2.0 * (a @ b.T)
+                ts, ti = torch.topk(sc, K, dim=1, largest=False)
+                ti = ti + b0
+                if best_s is None:
+                    best_s, best_i = ts, ti
+                else:
+                    cs, ci = torch.cat([best_s, ts], 1), torch.cat([best_i, ti], 1)
+                    best_s, sel = torch.topk(cs, K, dim=1, largest=False)
+                    best_i = torch.gather(ci, 1, sel)
+            hits += int((ids[q0:q0 + 2500].unsqueeze(2) == best_i.unsqueeze(1)).any(dim=2).sum())
+        torch.backends.cuda.matmul.allow_tf32 = old
+        assert hits / float(nq * K) >= 0.93
+        assert st.expansions > 0 and st.tie_overflows == 0
+
+
+def test_store_larger_than_the_device_is_refused(lmd):
+    """100 M x 96 in ONE store is 410 GB of node blocks: creation must fail with an out-of-memory status (the host then
+    shards the dataset), not crash and not fall back to anything."""
+    with pytest.raises(lmd.LmdError) as e:
+        lmd.Store(96, 32, capacity=100_000_000)
+    assert e.value.status == lmd.ERR_OOM
+    with lmd.Store(96, 32, capacity=1000) as s:  # the device is still usable afterwards
+        assert s.node_count == 0
