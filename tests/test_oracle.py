@@ -107,6 +107,15 @@ def test_search_golden(oracle, fixtures_mod, path):
         assert np.array_equal(cnt, z["fixed_count"])
         assert np.array_equal(_bits(dist), _bits(z["fixed_dist"]))
         assert np.array_equal(st, z["fixed_stats"])
+    # the filtered search (row f4) with every row allowed IS this search: its traversal half is thereby pinned to the
+    # reference-generated fixture too (the results-heap half has no reference counterpart)
+    n_blocks = blocks.size // lay["block_bytes"]
+    ids, dist, cnt, st = oracle.search(blocks, lay["block_bytes"], c["dims"], c["r"], z["queries"], c["k"], c["L"],
+                                       metric=c["metric"], vec_type=c["vec_type"], row_ids=c["row_ids"],
+                                       entry_row_id=c["entry"], cfg_l_search=c["cfg_l"],
+                                       allowed=np.ones(n_blocks, dtype=bool))
+    assert np.array_equal(ids, z["fixed_ids"]) and np.array_equal(cnt, z["fixed_count"])
+    assert np.array_equal(_bits(dist), _bits(z["fixed_dist"])) and np.array_equal(st[:, 0], z["fixed_stats"][:, 0])
     # the fixed results are ascending by (distance, id) and the search found something for every query
     d = z["fixed_dist"]
     for q in range(d.shape[0]):
@@ -292,3 +301,49 @@ def test_filtered_search_properties(oracle, fixtures_mod, route, metric):
     # 5. nothing allowed -> nothing returned
     none = oracle.search(b, bb, dims, r, q, k, L, metric=metric, route=route, allowed=np.zeros(n, dtype=bool))
     assert (none[2] == 0).all() and (none[0] == -1).all()
+
+
+def _py_filtered_search(x, nbrs, counts, q, k, L, allowed):
+    """The plan's dual-heap search written out naively (pure Python, small cases only): EH = the patched reference's
+    beam + top-L list over all rows, RH = the L best ALLOWED rows among everything whose distance was evaluated."""
+    def dist(i):
+        acc = np.float32(0.0)
+        for a, b in zip(q, x[i]):  # sequential fp32 accumulation, core/distance.hpp:56-67
+            d = np.float32(a) - np.float32(b)
+            acc = np.float32(acc + np.float32(d * d))
+        return np.float32(np.sqrt(acc))
+    d0 = dist(0)
+    top, beam, res, seen = [(d0, 0)], [(d0, 0)], ([(d0, 0)] if allowed[0] else []), {0}
+    while beam:
+        beam.sort()
+        cur = beam.pop(0)
+        if len(top) >= L and cur[0] > max(top)[0]:
+            break
+        for j in range(counts[cur[1]]):
+            nb = int(nbrs[cur[1], j])
+            if nb in seen:
+                continue
+            seen.add(nb)
+            c = (dist(nb), nb)
+            if allowed[nb] and (len(res) < L or c[0] < max(res)[0]):
+                res.append(c)
+                if len(res) > L:
+                    res.remove(max(res))
+            if len(top) < L or c[0] < max(top)[0]:
+                beam.append(c)
+                top.append(c)
+                if len(top) > L:
+                    top.remove(max(top))
+    return [i for _, i in sorted(res)[:k]]
+
+
+def test_filtered_search_equals_a_naive_restatement(oracle, fixtures_mod):
+    n, dims, r, k, L = 500, 16, 8, 5, 12
+    ix = fixtures_mod.build_index(n, dims, r, device="cpu")
+    q = fixtures_mod.make_dataset(12, dims, seed=43)
+    allowed = np.random.default_rng(4).random(n) < 0.35
+    got = oracle.search(ix["blocks"].numpy(), ix["layout"]["block_bytes"], dims, r, q, k, L, allowed=allowed)
+    nbrs, counts = np.asarray(ix["nbrs"]), np.asarray(ix["counts"])
+    for qi in range(q.shape[0]):
+        want = _py_filtered_search(ix["x"], nbrs, counts, q[qi], k, L, allowed)
+        assert got[0][qi, :got[2][qi]].tolist() == want, qi
