@@ -534,3 +534,38 @@ def test_latency_kernels_equal_throughput_kernels(lmd, oracle, make_index, n, di
     assert np.array_equal(a[0], c[0]) and np.array_equal(a[0][:1], one[0])
     o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q, 10, L, metric=METRIC[metric], entry_row_id=0)
     check_parity(b[0], b[1], b[2], o[0], o[1], o[2], what="latency kernels %s" % metric)
+
+
+def test_concurrent_host_threads_share_one_store(lmd, make_index):
+    """include/lmd_b200.h: concurrent searches on one store are serialised internally. Four host threads, different
+    query slices and list sizes, must each get what a lone caller gets; an error in one thread stays in that thread."""
+    import threading
+    ix = make_index(3000, 128, 32, metric="L2", kind="clustered", nq=96)
+    q = ix["queries"]
+    with _store(lmd, ix, 128, 32, "L2") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        want = {L: s.search(q, 10, L)[:3] for L in (32, 64, 100, 200)}
+        out, errs = {}, []
+
+        def work(t, L):
+            try:
+                for rep in range(6):
+                    lo = (t * 7 + rep * 5) % 40
+                    ids, dist, cnt, _ = s.search(q[lo:lo + 50], 10, L)
+                    assert np.array_equal(ids, want[L][0][lo:lo + 50]) and np.array_equal(cnt, want[L][2][lo:lo + 50])
+                    assert np.array_equal(dist.view(np.uint32), want[L][1][lo:lo + 50].view(np.uint32))
+                if t == 0:
+                    with pytest.raises(lmd.LmdError):
+                        s.search(q, 10, 4096)  # L beyond the build's limit: this thread's error only
+                out[t] = True
+            except BaseException as e:  # noqa: BLE001 - reported below
+                errs.append((t, repr(e)))
+
+        th = [threading.Thread(target=work, args=(t, L)) for t, L in enumerate((32, 64, 100, 200))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        assert not errs, errs
+        assert len(out) == 4
