@@ -19,6 +19,7 @@ INSTANCES = [("trav_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=0", "-DLMD_INST_METRIC=
             [("travf_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=3", "-DLMD_INST_METRIC=%d" % m, "-DLMD_INST_ROUTE=%d" % r])
              for m, r in ((1, 0), (2, 0), (3, 0), (2, 1), (3, 1))] + \
             [("travl_m%d" % m, ["-DLMD_INST_KIND=4", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)] + \
+            [("travm_m%d" % m, ["-DLMD_INST_KIND=5", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)] + \
             [("rerank_m%d" % m, ["-DLMD_INST_KIND=1", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)] + \
             [("prune_m%d" % m, ["-DLMD_INST_KIND=2", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)]
 HEADERS = [os.path.join(CSRC, "lmd_common.cuh"), os.path.join(CSRC, "lmd_kernels.cuh"),

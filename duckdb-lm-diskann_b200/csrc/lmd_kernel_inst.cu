@@ -4,6 +4,7 @@
 //   -DLMD_INST_KIND=2 -DLMD_INST_METRIC=<1|2|3>                          RobustPrune kernels of one metric
 //   -DLMD_INST_KIND=3 -DLMD_INST_METRIC=<1|2|3> -DLMD_INST_ROUTE=<0|1>   FILTERED traversal kernels (row f4)
 //   -DLMD_INST_KIND=4 -DLMD_INST_METRIC=<1|2|3>                          LATENCY traversal kernels (small batches)
+//   -DLMD_INST_KIND=5 -DLMD_INST_METRIC=<1|2|3>                          MID-SIZE-BATCH traversal kernels (G = 4)
 // so that the shape x list-size variants of each family build in parallel with the others.
 #include "lmd_build_kernels.cuh"
 
@@ -31,6 +32,13 @@ lmd_status LMD_CAT(dispatch_traverse_lat_m, LMD_INST_METRIC)(KParams &p, const l
                                                              cudaStream_t st) {
 	LMD_DISPATCH_SHAPE_LATENCY(traverse_kernel, LMD_INST_METRIC, 0)
 	set_error("no latency traversal kernel for this configuration (L=%u)", p.L);
+	return LMD_ERR_UNSUPPORTED;
+}
+#elif LMD_INST_KIND == 5
+lmd_status LMD_CAT(dispatch_traverse_mid_m, LMD_INST_METRIC)(KParams &p, const lmd_store *s, uint32_t nq, int lpl,
+                                                             cudaStream_t st) {
+	LMD_DISPATCH_SHAPE_MID(traverse_kernel, LMD_INST_METRIC, 0)
+	set_error("no mid-size-batch traversal kernel for this configuration (L=%u)", p.L);
 	return LMD_ERR_UNSUPPORTED;
 }
 #elif LMD_INST_KIND == 2

@@ -1098,8 +1098,9 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                               \
 	}
 
-// Rows in flight per warp (G): 128 / 96-d rows are 512 / 384 bytes and the kernel wants many warps (G = 2, 72 registers,
-// 24 warps per SM); a 768-d row is 3 KB and one row per pass leaves the warp waiting on L2 thirteen times per expansion,
+// Rows in flight per warp (G): 128-d rows are 512 bytes and the kernel wants many warps (G = 2, 72 registers, 24 warps
+// per SM; 10 k queries, L = 56: G = 2 1.21 ms, 4 1.35, 8 1.41); 96-d rows are 384 bytes and G = 4 wins (L = 64: G = 2
+// 1.21 ms, 4 1.12, 8 1.35; profiles/r40_mode_sweep_d*.json); a 768-d row is 3 KB and one row per pass leaves the warp waiting on L2 thirteen times per expansion,
 // so G = 6 (18 KB in flight per warp, 242 registers, 8 warps per SM) - measured on 1 M x 768 cosine, L = 48, 10 k
 // queries: G = 2 8.72 ms, 3 7.90, 4 6.92, 5 6.99, 6 6.01 (profiles/r17_mode_sweep_d768_g*.json).
 //
@@ -1114,11 +1115,21 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 8, METRIC, ##__VA_ARGS__)                                                \
 	}
 
+// ... and the step in between (G = 4, ~100 registers, 20 warps per SM) for batches that no longer fit the G = 8
+// kernels' 12 warps per SM in one wave but still leave the throughput kernels' 24 warps per SM half empty - the index
+// join's 2 048-row chunks sit exactly there.
+#define LMD_DISPATCH_SHAPE_MID(KERNEL, METRIC, ...)                                                                    \
+	if (p.row_floats == 128) {                                                                                         \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 4, 4, METRIC, ##__VA_ARGS__)                                                \
+	} else if (p.row_floats == 96) {                                                                                   \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 4, METRIC, ##__VA_ARGS__)                                                \
+	}
+
 #define LMD_DISPATCH_SHAPE(KERNEL, METRIC, ...)                                                                        \
 	if (p.row_floats == 128) {                                                                                         \
 		LMD_DISPATCH_LPL(KERNEL, 8, 4, 2, METRIC, ##__VA_ARGS__)                                                       \
 	} else if (p.row_floats == 96) {                                                                                   \
-		LMD_DISPATCH_LPL(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                       \
+		LMD_DISPATCH_LPL(KERNEL, 8, 3, 4, METRIC, ##__VA_ARGS__)                                                       \
 	} else if (p.row_floats == 768) {                                                                                  \
 		LMD_DISPATCH_LPL(KERNEL, 32, 6, 6, METRIC, ##__VA_ARGS__)                                                      \
 	} else {                                                                                                           \

@@ -71,6 +71,11 @@ LMD_DECL_TRAVERSE_FILT(3, 1)
 LMD_DECL_TRAVERSE_LAT(1)
 LMD_DECL_TRAVERSE_LAT(2)
 LMD_DECL_TRAVERSE_LAT(3)
+#define LMD_DECL_TRAVERSE_MID(M)                                                                                        \
+	lmd_status dispatch_traverse_mid_m##M(KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st);
+LMD_DECL_TRAVERSE_MID(1)
+LMD_DECL_TRAVERSE_MID(2)
+LMD_DECL_TRAVERSE_MID(3)
 LMD_DECL_RERANK(1)
 LMD_DECL_RERANK(2)
 LMD_DECL_RERANK(3)
@@ -198,6 +203,16 @@ static lmd_status dispatch_traverse(KParams &p, const lmd_store *s, uint32_t nq,
 		set_error("no filtered traversal kernel for this configuration (L=%u)", p.L);
 		return LMD_ERR_UNSUPPORTED;
 	}
+	if (route == LMD_ROUTE_EXACT && p.latency == 2) {
+		switch (p.metric) {
+		case LMD_METRIC_L2:
+			return dispatch_traverse_mid_m1(p, s, nq, lpl, st);
+		case LMD_METRIC_COSINE:
+			return dispatch_traverse_mid_m2(p, s, nq, lpl, st);
+		case LMD_METRIC_IP:
+			return dispatch_traverse_mid_m3(p, s, nq, lpl, st);
+		}
+	}
 	if (route == LMD_ROUTE_EXACT && p.latency) {
 		switch (p.metric) {
 		case LMD_METRIC_L2:
@@ -267,10 +282,16 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// small batches: the latency variants (all of an expansion's gathers in flight at once), see lmd_kernels.cuh
 	const bool specialised = p.row_floats == 128 || p.row_floats == 96; // 768-d rows already run with G = 6
 	const int lat = s->tune.latency_mode;
-	if (a.route == LMD_ROUTE_EXACT && !a.d_allowed && specialised &&
-	    (lat == 1 || (lat < 0 && a.nq <= (uint32_t)s->sm_count * 10))) {
-		p.latency = 1;
-		lpl = lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16;
+	if (a.route == LMD_ROUTE_EXACT && !a.d_allowed && specialised) {
+		// latency_mode: -1 = by batch size, 0 = throughput kernels only, 1 = G = 8 kernels, 2 = G = 4 kernels
+		if (lat == 1 || (lat < 0 && a.nq <= (uint32_t)s->sm_count * 12)) { // 168 registers: 12 warps per SM, one wave
+			p.latency = 1;
+		} else if (lat == 2 || (lat < 0 && a.nq <= (uint32_t)s->sm_count * 16)) { // 128 registers: 16 warps per SM
+			p.latency = 2;
+		}
+		if (p.latency) {
+			lpl = lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16;
+		}
 	}
 	if (a.d_allowed) {
 		lpl = lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16; // the filtered kernels exist for these list sizes only

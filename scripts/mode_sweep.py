@@ -20,9 +20,9 @@ store.upload_vectors(x); store.build_graph(l_insert=64); del x
 q = gen(16384, a.dims, 43, dev, a.metric == "COSINE")
 ids = torch.empty((16384, 10), dtype=torch.int64, device=dev)
 rows = []
-for nq in (1024, 1480, 2048, 3000, 4096, 6000, 8192, 10000, 16384):
+for nq in (1024, 1480, 1776, 2048, 2368, 3000, 4096, 6000, 10000):
     row = {"nq": nq}
-    for mode, name in ((0, "throughput"), (1, "latency")):
+    for mode, name in ((0, "throughput"), (1, "latency"), (2, "mid"), (-1, "auto")):
         store.set_tuning("latency_mode", mode)
         best = 1e9
         for i in range(8):
@@ -30,6 +30,6 @@ for nq in (1024, 1480, 2048, 3000, 4096, 6000, 8192, 10000, 16384):
             if i >= 2:
                 best = min(best, st.traverse_ms)
         row[name + "_ms"] = round(best, 4)
-    row["ratio"] = round(row["throughput_ms"] / row["latency_ms"], 3)
+    row["best"] = min(("throughput", "latency", "mid"), key=lambda k: row[k + "_ms"])
     rows.append(row); print(row, file=sys.stderr, flush=True)
 print(json.dumps({"driver": "scripts/mode_sweep.py", "dims": a.dims, "metric": a.metric, "L": a.L, "rows": rows}))
