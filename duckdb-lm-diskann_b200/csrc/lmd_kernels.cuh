@@ -1129,7 +1129,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	if (p.row_floats == 128) {                                                                                         \
 		LMD_DISPATCH_LPL(KERNEL, 8, 4, 2, METRIC, ##__VA_ARGS__)                                                       \
 	} else if (p.row_floats == 96) {                                                                                   \
-		LMD_DISPATCH_LPL(KERNEL, 8, 3, 4, METRIC, ##__VA_ARGS__)                                                       \
+		LMD_DISPATCH_LPL(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                       \
 	} else if (p.row_floats == 768) {                                                                                  \
 		LMD_DISPATCH_LPL(KERNEL, 32, 6, 6, METRIC, ##__VA_ARGS__)                                                      \
 	} else {                                                                                                           \

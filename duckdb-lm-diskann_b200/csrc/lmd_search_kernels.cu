@@ -118,7 +118,7 @@ static int lpl_for(uint32_t L) {
 struct FilterPlan {
 	uint32_t mode, lg, bytes;
 };
-static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes, uint32_t route) {
+static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes, uint32_t route, uint32_t min_warps) {
 	FilterPlan f;
 	const double expect = 0.8 * (double)s->cfg.r * 1.05 * (double)L;
 	int mode = s->tune.filter_mode;
@@ -135,7 +135,8 @@ static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes
 		while (lg < 15 && (double)(1u << lg) * load < expect) {
 			lg++;
 		}
-		const size_t budget = (size_t)227 * 1024 / 16;
+		// 1 KB of every CTA's shared memory belongs to the system: CTAs of 4 warps, min_warps / 4 of them
+		const size_t budget = ((size_t)227 * 1024 - (size_t)min_warps / 4 * 1024) / min_warps;
 		while (lg > 9 && fixed_bytes + ((size_t)(mode == 1 ? 2 : 4) << lg) > budget) {
 			lg--;
 		}
@@ -305,7 +306,19 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0);
 	const size_t res_bytes = a.d_allowed ? (size_t)lpl * 32 * 8 : 0; // the results list RH of a filtered search
 	fixed += res_bytes;
-	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route);
+	// The 128-d / 96-d exact kernels keep 2 rows in flight per team and need 24 warps on an SM to cover HBM latency: a
+	// list of 128+ entries with the 8 KB filter leaves room for 20-22, and the 4 KB filter with its re-evaluations (3 % of
+	// the rows at L = 128, 17 % at L = 256) is the faster trade: 1 M x 128, L = 128 / 160 / 256: 2.94 -> 2.47, 3.82 ->
+	// 3.25, 6.20 -> 5.73 ms per 10 k queries (profiles/r44_long_lists_d*.json). Other kernels hold fewer warps anyway.
+	const uint32_t min_warps = a.route == LMD_ROUTE_EXACT && !a.d_allowed && specialised ? 24u : 16u;
+	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route, min_warps);
+	if (p.row_floats == 96 && a.route == LMD_ROUTE_EXACT && !a.d_allowed && !p.latency && lat < 0 && (lpl == 2 || lpl == 4) &&
+	    fp.bytes >= 8192) {
+		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
+		// (10 M x 96, L = 48 / 128: 1.46 -> 1.37 / 3.53 -> 3.34 ms per 12.5 k queries; 1 M x 96, L = 64: 1.21 -> 1.13;
+		// profiles/r43_g_sweep_*.json; those kernels exist for lists of 64 and 128 entries, not 96). With the 4 KB filter the G = 2 kernel runs 32 warps and stays ahead.
+		p.latency = 2;
+	}
 	p.filter_mode = fp.mode;
 	p.filter_bytes = fp.bytes;
 	p.filter_mask = (1u << fp.lg) - 1;

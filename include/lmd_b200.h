@@ -218,8 +218,9 @@ lmd_status lmd_store_download_blocks(lmd_store *s, uint64_t first_slot, uint64_t
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
 uint32_t lmd_abi_version(void);
 /* Tuning knobs for experiments (not needed for correct use): "filter_log2", "filter_mode", "warps_per_cta",
- * "ctas_per_sm", "tie_slots", "merge_min", "prefetch_planes", "latency_mode" (-1 auto / 0 / 1: the small-batch
- * kernels that gather all neighbours of an expansion in one pass). */
+ * "ctas_per_sm", "tie_slots", "merge_min", "prefetch_planes", "latency_mode" (-1 auto by batch size / 0 the throughput
+ * kernels / 1 the small-batch kernels that gather all neighbours of an expansion in one pass / 2 the mid-size-batch
+ * kernels with 4 rows in flight per team; 128-d and 96-d rows, exact routing). */
 lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value);
 
 #ifdef __cplusplus

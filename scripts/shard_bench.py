@@ -13,6 +13,7 @@ fixtures.make_dataset, torch generator) and the graph is built by lmd_build_grap
 Timing: barrier + CUDA events on the searching stream, max over ranks; rank 0 prints one JSON line."""
 import argparse
 import importlib
+import itertools
 import json
 import os
 import sys
@@ -90,6 +91,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--tag", default="")
+    ap.add_argument("--sweep", nargs="*", default=[],
+                    help="repeat every L over the product of these tuning values, e.g. latency_mode=0,2 filter_log2=12,13")
     ap.add_argument("--tune", nargs="*", default=[], help="lmd_set_tuning pairs, e.g. merge_min=3 tie_slots=32")
     a = ap.parse_args()
     rank, world, local = (int(os.environ.get(v, d)) for v, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
@@ -162,7 +165,11 @@ def main():
     torch.cuda.set_stream(work)
     store.set_stream(work.cuda_stream)
     results = []
-    for L in a.L:
+    sweep = [(kv.split("=")[0], [int(v) for v in kv.split("=")[1].split(",")]) for kv in a.sweep]
+    points = [dict(zip([k for k, _ in sweep], vals)) for vals in itertools.product(*[v for _, v in sweep])]
+    for L, point in [(L, pt) for L in a.L for pt in points]:
+        for key, val in point.items():
+            store.set_tuning(key, val)
         if a.mode == "sharded":
             searcher = sh.DatasetShardedSearcher(store, device=dev)
 
@@ -195,7 +202,7 @@ def main():
                 dist.all_reduce(rec, op=dist.ReduceOp.SUM)
                 rec /= world
         total_q = a.nq if a.mode == "sharded" else a.nq * world
-        row = {"L": L, "ms_per_step": round(float(ms), 4), "qps": round(total_q / (float(ms) * 1e-3), 1),
+        row = {"L": L, "tuning": point, "ms_per_step": round(float(ms), 4), "qps": round(total_q / (float(ms) * 1e-3), 1),
                "recall_at_%d" % a.k: round(float(rec), 4), "local_kernel_ms_max": round(float(kms), 4),
                "E_per_q": round(st.expansions / a.nq, 1), "V_per_q": round(st.distance_evals / a.nq, 1),
                "local_algorithmic_GBps": round(st.algorithmic_bytes / (st.traverse_ms + st.rerank_ms) / 1e6, 1),
