@@ -310,7 +310,10 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// list of 128+ entries with the 8 KB filter leaves room for 20-22, and the 4 KB filter with its re-evaluations (3 % of
 	// the rows at L = 128, 17 % at L = 256) is the faster trade: 1 M x 128, L = 128 / 160 / 256: 2.94 -> 2.47, 3.82 ->
 	// 3.25, 6.20 -> 5.73 ms per 10 k queries (profiles/r44_long_lists_d*.json). Other kernels hold fewer warps anyway.
-	const uint32_t min_warps = a.route == LMD_ROUTE_EXACT && !a.d_allowed && specialised ? 24u : 16u;
+	// The filtered kernels (72 registers up to 128 entries) gain the same way up to L = 128 (1 M x 128, all rows allowed,
+	// L = 64 / 128: 1.79 -> 1.52, 3.66 -> 3.15 ms); at L = 256 they hold 96 registers, the small filter adds 14 % of
+	// re-evaluations and loses (8.76 -> 9.97 ms), so longer filtered lists keep the old rule (profiles/r47_filtered.json).
+	const uint32_t min_warps = a.route == LMD_ROUTE_EXACT && specialised && (!a.d_allowed || lpl <= 4) ? 24u : 16u;
 	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route, min_warps);
 	if (p.row_floats == 96 && a.route == LMD_ROUTE_EXACT && !a.d_allowed && !p.latency && lat < 0 && (lpl == 2 || lpl == 4) &&
 	    fp.bytes >= 8192) {

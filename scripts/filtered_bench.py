@@ -11,6 +11,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--rows", dest="n", type=int, default=1_000_000)
 ap.add_argument("--dims", type=int, default=128)
 ap.add_argument("--nq", type=int, default=10_000)
+ap.add_argument("--filter-log2", type=int, nargs="*", default=[0], help="visited-filter sizes to compare (0 = the library's choice)")
+ap.add_argument("--fracs", type=float, nargs="*", default=[1.0, 0.5, 0.1, 0.01])
 a = ap.parse_args()
 lmd = importlib.import_module("duckdb-lm-diskann_b200")
 dev = torch.device("cuda", 0)
@@ -22,7 +24,7 @@ ids = torch.empty((a.nq, 10), dtype=torch.int64, device=dev)
 cnt = torch.empty((a.nq,), dtype=torch.int32, device=dev)
 rows = []
 g = torch.Generator(device=dev); g.manual_seed(5)
-for frac in (1.0, 0.5, 0.1, 0.01):
+for frac in a.fracs:
     mask = torch.rand(a.n, generator=g, device=dev) < frac
     allowed = torch.nonzero(mask).squeeze(1)
     xs = x[allowed]
@@ -30,18 +32,20 @@ for frac in (1.0, 0.5, 0.1, 0.01):
     truth = allowed[ti]
     del xs
     with store.make_filter(allowed) as f:
-        for L in (64, 128, 256):
+        for L, flg in [(L, v) for L in (64, 128, 256) for v in a.filter_log2]:
+            store.set_tuning("filter_log2", flg)
             best = None
             for i in range(5):
                 st = store.search_raw(q, a.nq, 10, L, out_ids=ids, out_count=cnt, filter=f)
                 if i >= 2 and (best is None or st.traverse_ms < best.traverse_ms):
                     best = st
-            rows.append({"allowed_fraction": frac, "allowed_rows": int(allowed.numel()), "L": L,
+            rows.append({"allowed_fraction": frac, "allowed_rows": int(allowed.numel()), "L": L, "filter_log2": flg,
                          "recall_at_10_vs_allowed_truth": round(recall(ids, truth), 4),
                          "queries_with_fewer_than_k": int((cnt < 10).sum()),
                          "traverse_ms": round(best.traverse_ms, 4), "kernel_qps": round(a.nq / (best.traverse_ms * 1e-3)),
                          "E_per_q": round(best.expansions / a.nq, 1), "V_per_q": round(best.distance_evals / a.nq, 1)})
             print(rows[-1], file=sys.stderr, flush=True)
+store.set_tuning("filter_log2", 0)
 for L in (64, 128):
     st = None
     for i in range(4):
