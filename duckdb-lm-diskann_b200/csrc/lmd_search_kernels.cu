@@ -313,7 +313,11 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// The filtered kernels (72 registers up to 128 entries) gain the same way up to L = 128 (1 M x 128, all rows allowed,
 	// L = 64 / 128: 1.79 -> 1.52, 3.66 -> 3.15 ms); at L = 256 they hold 96 registers, the small filter adds 14 % of
 	// re-evaluations and loses (8.76 -> 9.97 ms), so longer filtered lists keep the old rule (profiles/r47_filtered.json).
-	const uint32_t min_warps = a.route == LMD_ROUTE_EXACT && specialised && (!a.d_allowed || lpl <= 4) ? 24u : 16u;
+	// Small batches run 12 (G = 8) or 16 (G = 4) warps per SM at most, which leaves room for the filter that never forgets:
+	// 1 M x 128, L = 128, 16 KB against 4 KB: 1 query 383 -> 348 us, 1 024 queries 564 -> 524 us
+	// (profiles/r50_small_batch_L128.json).
+	const uint32_t min_warps = p.latency == 1 ? 12u : p.latency == 2 ? 16u
+	                           : a.route == LMD_ROUTE_EXACT && specialised && (!a.d_allowed || lpl <= 4) ? 24u : 16u;
 	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route, min_warps);
 	if (p.row_floats == 96 && a.route == LMD_ROUTE_EXACT && !a.d_allowed && !p.latency && lat < 0 && (lpl == 2 || lpl == 4) &&
 	    fp.bytes >= 8192) {

@@ -11,6 +11,8 @@ ap.add_argument("--rows", dest="n", type=int, default=1_000_000)
 ap.add_argument("--dims", type=int, default=128)
 ap.add_argument("--L", type=int, default=56)
 ap.add_argument("--metric", default="L2")
+ap.add_argument("--nqs", type=int, nargs="*", default=[1024, 1480, 1776, 2048, 2368, 3000, 4096, 6000, 10000])
+ap.add_argument("--filter-log2", type=int, nargs="*", default=[0], help="visited-filter sizes (0 = the library's choice)")
 a = ap.parse_args()
 lmd = importlib.import_module("duckdb-lm-diskann_b200")
 dev = torch.device("cuda", 0)
@@ -20,8 +22,9 @@ store.upload_vectors(x); store.build_graph(l_insert=64); del x
 q = gen(16384, a.dims, 43, dev, a.metric == "COSINE")
 ids = torch.empty((16384, 10), dtype=torch.int64, device=dev)
 rows = []
-for nq in (1024, 1480, 1776, 2048, 2368, 3000, 4096, 6000, 10000):
-    row = {"nq": nq}
+for nq, flg in [(n, f) for n in a.nqs for f in a.filter_log2]:
+    row = {"nq": nq, "filter_log2": flg}
+    store.set_tuning("filter_log2", flg)
     for mode, name in ((0, "throughput"), (1, "latency"), (2, "mid"), (-1, "auto")):
         store.set_tuning("latency_mode", mode)
         best = 1e9

@@ -530,7 +530,11 @@ def test_latency_kernels_equal_throughput_kernels(lmd, oracle, make_index, n, di
         s.set_tuning("latency_mode", -1)
         c = s.search(q, 10, L)                # 96 queries: picked automatically
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
-    assert np.array_equal(a[4], b[4])         # same expansions and distance evaluations per query
+    # same expansions per query; the evaluations differ only by what the visited filters forget (the small-batch kernels
+    # run fewer warps per SM and get a larger filter)
+    assert np.array_equal(a[4][:, 0], b[4][:, 0])
+    va, vb = a[4][:, 1].astype(np.int64), b[4][:, 1].astype(np.int64)
+    assert np.all(vb <= va + va // 50 + 2) and np.all(va <= vb + vb // 3)   # L = 512 on 2 500 rows: 20 % re-evaluated
     assert np.array_equal(a[0], c[0]) and np.array_equal(a[0][:1], one[0])
     o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, q, 10, L, metric=METRIC[metric], entry_row_id=0)
     check_parity(b[0], b[1], b[2], o[0], o[1], o[2], what="latency kernels %s" % metric)
