@@ -194,6 +194,22 @@ def test_dataset_sharding_gloo_world2():
     assert np.all(np.diff(merged[1], axis=1) >= 0)
 
 
+def test_both_modes_gloo_world3_ragged():
+    """Three ranks, 1 601 rows and 37 queries: neither divides by 3, so the slices and shards are ragged."""
+    case, k, L = _make_case(n=1601, world=3), 10, 32
+    full, merged = _expected(case, k, L)
+    out = _run("query", False, case, k, L, world=3)
+    for ids, d, c, lo, hi in out:
+        assert np.array_equal(ids, full[0]) and np.array_equal(c, full[2])
+        assert np.array_equal(d.view(np.uint32), full[1].view(np.uint32))
+    assert [o[3:] for o in out] == [(0, 13), (13, 25), (25, 37)]
+    out = _run("dataset", False, case, k, L, world=3)
+    for ids, d, nbytes in out:
+        assert np.array_equal(ids, merged[0]) and np.array_equal(d.view(np.uint32), merged[1].view(np.uint32))
+        assert nbytes == 37 * k * 12 * 3
+    assert [b.shape[0] for b, _ in case["shards"]] == [534, 534, 533]
+
+
 @pytest.mark.gpu
 def test_query_sharding_cuda_world2():
     case, k, L = _make_case(n=3000, dims=128, r=32, nq=101), 10, 48
