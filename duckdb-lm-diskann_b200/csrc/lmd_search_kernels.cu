@@ -319,11 +319,12 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	const uint32_t min_warps = p.latency == 1 ? 12u : p.latency == 2 ? 16u
 	                           : a.route == LMD_ROUTE_EXACT && specialised && (!a.d_allowed || lpl <= 4) ? 24u : 16u;
 	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route, min_warps);
-	if (p.row_floats == 96 && a.route == LMD_ROUTE_EXACT && !a.d_allowed && !p.latency && lat < 0 && (lpl == 2 || lpl == 4) &&
-	    fp.bytes >= 8192) {
+	if (p.row_floats == 96 && a.route == LMD_ROUTE_EXACT && !a.d_allowed && !p.latency && lat < 0 &&
+	    (lpl == 2 || lpl == 4) && fp.bytes >= 8192) {
 		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
 		// (10 M x 96, L = 48 / 128: 1.46 -> 1.37 / 3.53 -> 3.34 ms per 12.5 k queries; 1 M x 96, L = 64: 1.21 -> 1.13;
-		// profiles/r43_g_sweep_*.json; those kernels exist for lists of 64 and 128 entries, not 96). With the 4 KB filter the G = 2 kernel runs 32 warps and stays ahead.
+		// profiles/r43_g_sweep_*.json; those kernels exist for lists of 64 and 128 entries, not 96). With the 4 KB filter
+		// the G = 2 kernel runs 32 warps and stays ahead.
 		p.latency = 2;
 	}
 	p.filter_mode = fp.mode;
