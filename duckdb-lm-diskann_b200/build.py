@@ -23,7 +23,7 @@ INSTANCES = [("trav_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=0", "-DLMD_INST_METRIC=
             [("rerank_m%d" % m, ["-DLMD_INST_KIND=1", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)] + \
             [("prune_m%d" % m, ["-DLMD_INST_KIND=2", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)]
 HEADERS = [os.path.join(CSRC, "lmd_common.cuh"), os.path.join(CSRC, "lmd_kernels.cuh"),
-           os.path.join(CSRC, "lmd_build_kernels.cuh"),
+           os.path.join(CSRC, "lmd_build_kernels.cuh"), os.path.join(CSRC, "lmd_plan.hpp"),
            os.path.join(HERE, "..", "include", "lmd_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [

@@ -1,0 +1,126 @@
+// Launch planning of the search kernels as plain host code (no CUDA types): list-size classes, visited-filter sizing,
+// and which kernel family serves a batch. lmd_search_kernels.cu calls these; tests/test_plan.py compiles this header
+// with g++ and pins the plans the measurements in DESIGN.md section 6 were taken with.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+namespace lmd {
+
+inline int lpl_for(uint32_t L) {
+	return L <= 32 ? 1 : L <= 64 ? 2 : L <= 96 ? 3 : L <= 128 ? 4 : L <= 192 ? 6 : L <= 256 ? 8 : L <= 384 ? 12 : L <= 512 ? 16 : 0;
+}
+
+// The small-batch, mid-size-batch and filtered kernels exist for lists of 64 / 128 / 256 / 512 entries only.
+inline int lpl_coarse(int lpl) {
+	return lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16;
+}
+
+// Visited-filter sizing. `lg` = log2(entries). Mode 1 (two-choice buckets of 8 x 16-bit entries, 2 bytes per entry) is
+// used whenever the store is small enough for its exact (bucket, tag) identification, i.e. nodes < 2^(lg - 3 + 15);
+// mode 0 (u32 open addressing, 4 bytes per entry) otherwise. The table is sized for the nodes a search is expected to
+// discover (about 0.8 R new neighbours per expansion, ~1.05 L expansions) at a load of 0.7 (mode 1) / 0.45 (mode 0), then
+// shrunk until at least `min_warps` warps fit on an SM: the gathers need warps in flight more than a perfect filter.
+struct FilterPlan {
+	uint32_t mode, lg, bytes;
+};
+// `nodes`, `r`, `words`: the store's node count, graph degree and ternary plane words; `ternary`: the route;
+// `tune_mode` / `tune_log2`: the "filter_mode" / "filter_log2" tuning keys (negative / 0 = not set).
+inline FilterPlan plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32_t L, size_t fixed_bytes, bool ternary,
+                              uint32_t min_warps, int tune_mode, int tune_log2) {
+	FilterPlan f;
+	const double expect = 0.8 * (double)r * 1.05 * (double)L;
+	int mode = tune_mode;
+	if (mode != 0 && mode != 1) {
+		mode = 1;
+	}
+	auto fits_exact = [&](uint32_t lg) { return lg >= 4 && nodes < (1ull << (lg - 3 + 15)); };
+	uint32_t lg;
+	if (tune_log2 >= 6 && tune_log2 <= 16) {
+		lg = (uint32_t)tune_log2;
+	} else {
+		const double load = mode == 1 ? 0.7 : 0.45;
+		lg = 9;
+		while (lg < 15 && (double)(1u << lg) * load < expect) {
+			lg++;
+		}
+		// 1 KB of every CTA's shared memory belongs to the system: CTAs of 4 warps, min_warps / 4 of them
+		const size_t budget = ((size_t)227 * 1024 - (size_t)min_warps / 4 * 1024) / min_warps;
+		while (lg > 9 && fixed_bytes + ((size_t)(mode == 1 ? 2 : 4) << lg) > budget) {
+			lg--;
+		}
+		// Ternary routing over planes of 3+ words (D > 128): lane j reads neighbour j's planes with 8-byte loads that sit
+		// 8 * words bytes apart across the warp, so every 32-byte sector is fetched by four load instructions and the
+		// kernel lives on L1 hits - and L1 is whatever the CTAs' shared memory leaves of the SM's 256 KB. A 2 KB filter
+		// (4 KB per warp, 130 KB per SM) leaves L1 ~120 KB; the re-evaluations it causes cost 192 B each. Measured on
+		// 1 M x 768 cosine, L = 80: 2.59 ms per 10 k queries with the 8 KB filter, 2.78 with 4 KB, 1.78 with 2 KB
+		// (profiles/r23_tune_ternary.log). A warp-wide coalesced read of the plane region (every byte requested once)
+		// was tried and took the L1 dependence away, but at 2.1 ms it lost to this (profiles/r24_tune_ternary.log).
+		if (ternary && words > 2 && lg > 10) {
+			lg = 10;
+		}
+	}
+	if (mode == 1 && !fits_exact(lg)) {
+		// Stores beyond 2^(lg + 12) nodes (8.4 M at lg = 11) need more buckets for the exact (bucket, tag) identification:
+		// grow the table while the shared-memory budget allows it, and only then fall back to the 4-byte table - sized
+		// for ITS load factor, not for the 2-byte one (measured on 10 M x 96, L = 48: the undersized fallback cost 25 %).
+		const size_t budget = (size_t)227 * 1024 / 12;
+		uint32_t lg1 = lg;
+		while (lg1 < 15 && !fits_exact(lg1)) {
+			lg1++;
+		}
+		if (!(tune_log2 >= 6) && fits_exact(lg1) && fixed_bytes + ((size_t)2 << lg1) <= budget) {
+			lg = lg1;
+		} else {
+			mode = 0;
+			if (!(tune_log2 >= 6)) {
+				lg = 9;
+				while (lg < 15 && (double)(1u << lg) * 0.45 < expect) {
+					lg++;
+				}
+				while (lg > 9 && fixed_bytes + ((size_t)4 << lg) > (size_t)227 * 1024 / 16) {
+					lg--;
+				}
+			}
+		}
+	}
+	f.mode = (uint32_t)mode;
+	f.lg = lg;
+	f.bytes = (uint32_t)((mode == 1 ? 2u : 4u) << lg);
+	return f;
+}
+
+// Which traversal family serves an exact, unfiltered search over 128-d / 96-d rows: 0 = throughput kernels (2 rows in
+// flight per team), 1 = small-batch kernels (G = 8: all gathers of an expansion at once; 168 registers, 12 warps per SM),
+// 2 = mid-size-batch kernels (G = 4; 128 registers, 16 warps per SM). `tune` is the "latency_mode" key (-1 = by batch).
+inline int plan_family(uint32_t nq, uint32_t sm_count, int tune) {
+	if (tune == 1 || (tune < 0 && nq <= sm_count * 12)) {
+		return 1;
+	}
+	if (tune == 2 || (tune < 0 && nq <= sm_count * 16)) {
+		return 2;
+	}
+	return 0;
+}
+
+// Warps the chosen kernels want resident on an SM; the visited filter is shrunk until that many fit (DESIGN.md 6,
+// "Long lists"). `specialised` = 128-d or 96-d rows; `lpl` = list entries / 32 after rounding to the family's sizes.
+inline uint32_t plan_min_warps(int family, bool exact, bool specialised, bool filtered, int lpl) {
+	if (family == 1) {
+		return 12;
+	}
+	if (family == 2) {
+		return 16;
+	}
+	return exact && specialised && (!filtered || lpl <= 4) ? 24u : 16u;
+}
+
+// 96-d rows (384 bytes): the G = 4 kernels also win on full batches when shared memory holds the G = 2 kernel at 24 warps
+// or fewer anyway, i.e. with the 8 KB filter; they exist for lists of 64 and 128 entries.
+inline bool plan_96d_prefers_g4(uint32_t row_floats, bool exact, bool filtered, int family, int tune, int lpl,
+                                uint32_t filter_bytes) {
+	return row_floats == 96 && exact && !filtered && family == 0 && tune < 0 && (lpl == 2 || lpl == 4) &&
+	       filter_bytes >= 8192;
+}
+
+} // namespace lmd

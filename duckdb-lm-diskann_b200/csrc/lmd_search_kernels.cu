@@ -2,6 +2,7 @@
 // translation units (lmd_kernel_inst.cu compiled once per kernel kind, metric and route), and the k-way merge kernel
 // of the dataset-sharded mode.
 #include "lmd_kernels.cuh"
+#include "lmd_plan.hpp"
 
 namespace lmd {
 
@@ -104,81 +105,6 @@ static KParams base_params(const lmd_store *s, const float *d_queries, uint32_t 
 	p.entry_slot = s->entry_slot;
 	p.has_entry = s->has_entry ? 1u : 0u;
 	return p;
-}
-
-static int lpl_for(uint32_t L) {
-	return L <= 32 ? 1 : L <= 64 ? 2 : L <= 96 ? 3 : L <= 128 ? 4 : L <= 192 ? 6 : L <= 256 ? 8 : L <= 384 ? 12 : L <= 512 ? 16 : 0;
-}
-
-// Visited-filter sizing. `lg` = log2(entries). Mode 1 (two-choice buckets of 8 x 16-bit entries, 2 bytes per entry) is
-// used whenever the store is small enough for its exact (bucket, tag) identification, i.e. nodes < 2^(lg - 3 + 15);
-// mode 0 (u32 open addressing, 4 bytes per entry) otherwise. The table is sized for the nodes a search is expected to
-// discover (about 0.8 R new neighbours per expansion, ~1.05 L expansions) at a load of 0.7 (mode 1) / 0.45 (mode 0), then
-// shrunk until at least `min_warps` warps fit on an SM: the gathers need warps in flight more than a perfect filter.
-struct FilterPlan {
-	uint32_t mode, lg, bytes;
-};
-static FilterPlan pick_filter(const lmd_store *s, uint32_t L, size_t fixed_bytes, uint32_t route, uint32_t min_warps) {
-	FilterPlan f;
-	const double expect = 0.8 * (double)s->cfg.r * 1.05 * (double)L;
-	int mode = s->tune.filter_mode;
-	if (mode != 0 && mode != 1) {
-		mode = 1;
-	}
-	auto fits_exact = [&](uint32_t lg) { return lg >= 4 && (uint64_t)s->n < (1ull << (lg - 3 + 15)); };
-	uint32_t lg;
-	if (s->tune.filter_log2 >= 6 && s->tune.filter_log2 <= 16) {
-		lg = (uint32_t)s->tune.filter_log2;
-	} else {
-		const double load = mode == 1 ? 0.7 : 0.45;
-		lg = 9;
-		while (lg < 15 && (double)(1u << lg) * load < expect) {
-			lg++;
-		}
-		// 1 KB of every CTA's shared memory belongs to the system: CTAs of 4 warps, min_warps / 4 of them
-		const size_t budget = ((size_t)227 * 1024 - (size_t)min_warps / 4 * 1024) / min_warps;
-		while (lg > 9 && fixed_bytes + ((size_t)(mode == 1 ? 2 : 4) << lg) > budget) {
-			lg--;
-		}
-		// Ternary routing over planes of 3+ words (D > 128): lane j reads neighbour j's planes with 8-byte loads that sit
-		// 8 * words bytes apart across the warp, so every 32-byte sector is fetched by four load instructions and the
-		// kernel lives on L1 hits - and L1 is whatever the CTAs' shared memory leaves of the SM's 256 KB. A 2 KB filter
-		// (4 KB per warp, 130 KB per SM) leaves L1 ~120 KB; the re-evaluations it causes cost 192 B each. Measured on
-		// 1 M x 768 cosine, L = 80: 2.59 ms per 10 k queries with the 8 KB filter, 2.78 with 4 KB, 1.78 with 2 KB
-		// (profiles/r23_tune_ternary.log). A warp-wide coalesced read of the plane region (every byte requested once)
-		// was tried and took the L1 dependence away, but at 2.1 ms it lost to this (profiles/r24_tune_ternary.log).
-		if (route == LMD_ROUTE_TERNARY && s->words > 2 && lg > 10) {
-			lg = 10;
-		}
-	}
-	if (mode == 1 && !fits_exact(lg)) {
-		// Stores beyond 2^(lg + 12) nodes (8.4 M at lg = 11) need more buckets for the exact (bucket, tag) identification:
-		// grow the table while the shared-memory budget allows it, and only then fall back to the 4-byte table - sized
-		// for ITS load factor, not for the 2-byte one (measured on 10 M x 96, L = 48: the undersized fallback cost 25 %).
-		const size_t budget = (size_t)227 * 1024 / 12;
-		uint32_t lg1 = lg;
-		while (lg1 < 15 && !fits_exact(lg1)) {
-			lg1++;
-		}
-		if (!(s->tune.filter_log2 >= 6) && fits_exact(lg1) && fixed_bytes + ((size_t)2 << lg1) <= budget) {
-			lg = lg1;
-		} else {
-			mode = 0;
-			if (!(s->tune.filter_log2 >= 6)) {
-				lg = 9;
-				while (lg < 15 && (double)(1u << lg) * 0.45 < expect) {
-					lg++;
-				}
-				while (lg > 9 && fixed_bytes + ((size_t)4 << lg) > (size_t)227 * 1024 / 16) {
-					lg--;
-				}
-			}
-		}
-	}
-	f.mode = (uint32_t)mode;
-	f.lg = lg;
-	f.bytes = (uint32_t)((mode == 1 ? 2u : 4u) << lg);
-	return f;
 }
 
 static lmd_status dispatch_traverse(KParams &p, const lmd_store *s, uint32_t nq, int lpl, uint32_t route,
@@ -285,17 +211,13 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	const int lat = s->tune.latency_mode;
 	if (a.route == LMD_ROUTE_EXACT && !a.d_allowed && specialised) {
 		// latency_mode: -1 = by batch size, 0 = throughput kernels only, 1 = G = 8 kernels, 2 = G = 4 kernels
-		if (lat == 1 || (lat < 0 && a.nq <= (uint32_t)s->sm_count * 12)) { // 168 registers: 12 warps per SM, one wave
-			p.latency = 1;
-		} else if (lat == 2 || (lat < 0 && a.nq <= (uint32_t)s->sm_count * 16)) { // 128 registers: 16 warps per SM
-			p.latency = 2;
-		}
+		p.latency = (uint32_t)plan_family(a.nq, (uint32_t)s->sm_count, lat);
 		if (p.latency) {
-			lpl = lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16;
+			lpl = lpl_coarse(lpl);
 		}
 	}
 	if (a.d_allowed) {
-		lpl = lpl <= 2 ? 2 : lpl <= 4 ? 4 : lpl <= 8 ? 8 : 16; // the filtered kernels exist for these list sizes only
+		lpl = lpl_coarse(lpl); // the filtered kernels exist for these list sizes only
 		p.allowed = a.d_allowed;
 	}
 	p.list_cap = (uint32_t)lpl * 32;
@@ -316,11 +238,11 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// Small batches run 12 (G = 8) or 16 (G = 4) warps per SM at most, which leaves room for the filter that never forgets:
 	// 1 M x 128, L = 128, 16 KB against 4 KB: 1 query 383 -> 348 us, 1 024 queries 564 -> 524 us
 	// (profiles/r50_small_batch_L128.json).
-	const uint32_t min_warps = p.latency == 1 ? 12u : p.latency == 2 ? 16u
-	                           : a.route == LMD_ROUTE_EXACT && specialised && (!a.d_allowed || lpl <= 4) ? 24u : 16u;
-	const FilterPlan fp = pick_filter(s, a.L, fixed, a.route, min_warps);
-	if (p.row_floats == 96 && a.route == LMD_ROUTE_EXACT && !a.d_allowed && !p.latency && lat < 0 &&
-	    (lpl == 2 || lpl == 4) && fp.bytes >= 8192) {
+	const bool exact = a.route == LMD_ROUTE_EXACT;
+	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl);
+	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, !exact, min_warps, s->tune.filter_mode,
+	                                  (int)s->tune.filter_log2);
+	if (plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
 		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
 		// (10 M x 96, L = 48 / 128: 1.46 -> 1.37 / 3.53 -> 3.34 ms per 12.5 k queries; 1 M x 96, L = 64: 1.21 -> 1.13;
 		// profiles/r43_g_sweep_*.json; those kernels exist for lists of 64 and 128 entries, not 96). With the 4 KB filter

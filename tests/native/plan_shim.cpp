@@ -1,0 +1,28 @@
+// tests/test_plan.py: C entry points over csrc/lmd_plan.hpp (plain host code), compiled with g++ at test time.
+#include "lmd_plan.hpp"
+
+extern "C" {
+int plan_lpl(uint32_t L) {
+	return lmd::lpl_for(L);
+}
+int plan_lpl_coarse(int lpl) {
+	return lmd::lpl_coarse(lpl);
+}
+int plan_family(uint32_t nq, uint32_t sm_count, int tune) {
+	return lmd::plan_family(nq, sm_count, tune);
+}
+uint32_t plan_min_warps(int family, int exact, int specialised, int filtered, int lpl) {
+	return lmd::plan_min_warps(family, exact != 0, specialised != 0, filtered != 0, lpl);
+}
+int plan_96d_prefers_g4(uint32_t row_floats, int exact, int filtered, int family, int tune, int lpl, uint32_t filter_bytes) {
+	return lmd::plan_96d_prefers_g4(row_floats, exact != 0, filtered != 0, family, tune, lpl, filter_bytes) ? 1 : 0;
+}
+// out[0..2] = mode, log2(entries), bytes
+void plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32_t L, uint64_t fixed_bytes, int ternary,
+                 uint32_t min_warps, int tune_mode, int tune_log2, uint32_t *out) {
+	const lmd::FilterPlan f = lmd::plan_filter(nodes, r, words, L, (size_t)fixed_bytes, ternary != 0, min_warps, tune_mode, tune_log2);
+	out[0] = f.mode;
+	out[1] = f.lg;
+	out[2] = f.bytes;
+}
+}
