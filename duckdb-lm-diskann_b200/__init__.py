@@ -18,10 +18,14 @@ LIB_PATH = os.environ.get("LMD_B200_LIB") or os.path.join(HERE, "liblmd_b200.so"
 # common/ann.hpp:16-32
 METRIC_L2, METRIC_COSINE, METRIC_IP = 1, 2, 3
 VEC_FLOAT32, VEC_INT8 = 1, 2
-ROUTE_EXACT, ROUTE_TERNARY = 0, 1
+ROUTE_EXACT, ROUTE_TERNARY, ROUTE_INT8 = 0, 1, 2
+CODEC_NONE, CODEC_INT8 = 0, 1
 SEARCH_SEPARATE_RERANK = 1
 SEARCH_PER_QUERY_STATS = 2
 SEARCH_ASYNC = 4
+SEARCH_STRICT_FP = 8
+SEARCH_NO_PREFILTER = 16
+SEARCH_TENSOR_RERANK = 32
 EMPTY_ROW_ID = np.iinfo(np.int64).max  # core/GraphManager.cpp:154-156
 OK, ERR_INVALID_ARG, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_UNSUPPORTED = range(6)
 METRIC_BY_NAME = {"L2": METRIC_L2, "COSINE": METRIC_COSINE, "IP": METRIC_IP}
@@ -46,7 +50,7 @@ class Config(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("queries", C.c_uint64), ("expansions", C.c_uint64), ("distance_evals", C.c_uint64),
                 ("reranked", C.c_uint64), ("filter_evictions", C.c_uint64), ("tie_overflows", C.c_uint64),
-                ("merge_fallbacks", C.c_uint64), ("algorithmic_bytes", C.c_uint64),
+                ("merge_fallbacks", C.c_uint64), ("algorithmic_bytes", C.c_uint64), ("exact_fetches", C.c_uint64),
                 ("traverse_ms", C.c_float), ("rerank_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
                 ("total_ms", C.c_float), ("launches", C.c_uint32), ("l_used", C.c_uint32)]
 
@@ -88,6 +92,14 @@ SYMBOLS = [
     ("lmd_store_device_bytes", C.c_uint64, [_P]),
     ("lmd_search_batch", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P,
                                     _P, C.POINTER(Stats)]),
+    ("lmd_store_enable_codec", C.c_int32, [_P, C.c_uint32]),
+    ("lmd_store_get_codec", C.c_int32, [_P, _P, C.POINTER(C.c_float)]),
+    ("lmd_store_release_blocks", C.c_int32, [_P]),
+    ("lmd_ctx_create", C.c_int32, [_P, C.POINTER(_P)]),
+    ("lmd_ctx_destroy", C.c_int32, [_P]),
+    ("lmd_ctx_set_stream", C.c_int32, [_P, _P]),
+    ("lmd_ctx_search_batch", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P,
+                                        _P, _P, C.POINTER(Stats)]),
     ("lmd_filter_create", C.c_int32, [_P, _P, C.c_uint64, C.POINTER(_P)]),
     ("lmd_filter_destroy", C.c_int32, [_P]),
     ("lmd_filter_count", C.c_uint64, [_P]),
@@ -255,6 +267,25 @@ class Store:
         _check(lib().lmd_store_download_blocks(self._h, first_slot, n, _ptr(out)))
         return out
 
+    def enable_codec(self, codec=CODEC_INT8):
+        """Builds the int8 edge-codec sidecar (row f4): ROUTE_INT8 searches, and the exact route's lower-bound pre-filter."""
+        _check(lib().lmd_store_enable_codec(self._h, codec))
+
+    def get_codec(self):
+        """-> (offsets [dims] float32, scale) of the codec grid."""
+        off = np.zeros(self.cfg.dims, dtype=np.float32)
+        sc = C.c_float(0)
+        _check(lib().lmd_store_get_codec(self._h, _ptr(off), C.byref(sc)))
+        return off, float(sc.value)
+
+    def release_blocks(self):
+        """Frees the raw block mirror (search-only store)."""
+        _check(lib().lmd_store_release_blocks(self._h))
+
+    def context(self):
+        """A per-caller search context (own stream / counters / scratch): one per host thread."""
+        return Context(self)
+
     def set_stream(self, cuda_stream):
         """cuda_stream: a raw cudaStream_t address (e.g. torch.cuda.current_stream().cuda_stream) or None."""
         _check(lib().lmd_store_set_stream(self._h, cuda_stream or None))
@@ -275,10 +306,13 @@ class Store:
         return Filter(self, allowed_row_ids)
 
     def search_raw(self, queries, nq, k, L=0, route=ROUTE_EXACT, flags=0, out_ids=None, out_dist=None, out_count=None,
-                   out_qstats=None, stats=True, filter=None):
+                   out_qstats=None, stats=True, filter=None, ctx=None):
         """Thin call: any mix of numpy arrays / torch tensors / raw addresses. stats=False passes a NULL lmd_stats
         (the call still synchronises unless SEARCH_ASYNC is set) and returns None."""
-        if filter is not None:
+        if ctx is not None:
+            def call(*a):
+                return lib().lmd_ctx_search_batch(ctx._h, filter._h if filter is not None else None, *a)
+        elif filter is not None:
             def call(*a):
                 return lib().lmd_search_batch_filtered(self._h, filter._h, *a)
         else:
@@ -293,7 +327,7 @@ class Store:
                     _ptr(out_qstats), C.byref(st)))
         return st
 
-    def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0, qstats=False, filter=None):
+    def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0, qstats=False, filter=None, ctx=None):
         """Host-buffer search: queries [nq, dims] float32 numpy -> (ids [nq,k] int64, dist [nq,k] f32,
         count [nq] u32, Stats[, qstats [nq,2] u32])."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
@@ -308,8 +342,39 @@ class Store:
         qs = np.zeros((nq, 2), dtype=np.uint32) if qstats else None
         if qstats:
             flags |= SEARCH_PER_QUERY_STATS
-        st = self.search_raw(q, nq, k, L, route, flags, ids, dist, count, qs, filter=filter)
+        st = self.search_raw(q, nq, k, L, route, flags, ids, dist, count, qs, filter=filter, ctx=ctx)
         return (ids, dist, count, st, qs) if qstats else (ids, dist, count, st)
+
+
+class Context:
+    """lmd_ctx: searches through different contexts of one store run side by side (one per host thread)."""
+
+    def __init__(self, store):
+        self._h = _P()
+        self.store = store
+        _check(lib().lmd_ctx_create(store._h, C.byref(self._h)))
+
+    def search(self, queries, k, L=0, **kw):
+        return self.store.search(queries, k, L, ctx=self, **kw)
+
+    def set_stream(self, cuda_stream):
+        _check(lib().lmd_ctx_set_stream(self._h, cuda_stream or None))
+
+    def close(self):
+        try:
+            if self._h:
+                lib().lmd_ctx_destroy(self._h)
+                self._h = _P()
+        except TypeError:
+            pass
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
 
 
 class Filter:

@@ -67,9 +67,22 @@ lmd_status grow(T *&ptr, uint64_t &have, uint64_t need_elems, lmd_store *s) {
 
 } // namespace
 
-static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const float *queries, uint64_t nq, uint32_t k,
-                       uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids, float *out_dist,
-                       uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats) {
+// Grows one scratch array of a SearchState; `have` is ITS capacity in elements (each array has its own: d_qstats needs
+// 2 nq entries whatever k is, d_out_count nq, the id / distance arrays nq * k).
+template <typename T>
+static lmd_status grow_to(T *&ptr, uint64_t &have, uint64_t need_elems) {
+	lmd_status rc = grow(ptr, have, need_elems, nullptr);
+	if (rc != LMD_OK) {
+		have = 0;
+	}
+	return rc;
+}
+
+static const size_t PIN_Q_BYTES = 48 * 1024, PIN_OUT_BYTES = 80 * 1024;
+
+static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *filter, const float *queries, uint64_t nq,
+                              uint32_t k, uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids, float *out_dist,
+                              uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats) {
 	if (stats) {
 		memset(stats, 0, sizeof(*stats));
 	}
@@ -92,7 +105,7 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 		set_error("lmd_search_batch: batch too large");
 		return LMD_ERR_INVALID_ARG;
 	}
-	if (route != LMD_ROUTE_EXACT && route != LMD_ROUTE_TERNARY) {
+	if (route != LMD_ROUTE_EXACT && route != LMD_ROUTE_TERNARY && route != LMD_ROUTE_INT8) {
 		set_error("lmd_search_batch: unknown route %u", route);
 		return LMD_ERR_INVALID_ARG;
 	}
@@ -111,20 +124,33 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 		set_error("search list size L = %u exceeds this build's limit of 512", l_used);
 		return LMD_ERR_UNSUPPORTED;
 	}
-	if (s->dirty) {
-		lmd_status st = lmd_store_finalize(s);
+	// Searches only read the store: they hold its lock shared, so calls on different contexts run side by side; whatever
+	// changes the store (upload, apply / remove, finalize, build, tuning) holds it exclusively.
+	std::shared_lock<std::shared_mutex> rd(s->mu);
+	if (route == LMD_ROUTE_INT8 && s->cfg.metric != LMD_METRIC_L2) {
+		set_error("the int8 edge codec is defined for the L2 metric only");
+		return LMD_ERR_UNSUPPORTED;
+	}
+	while (!route_ready(s, route)) {
+		rd.unlock();
+		lmd_status st = store_prepare(s, route);
 		if (st != LMD_OK) {
 			return st;
 		}
+		rd.lock();
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::lock_guard<std::mutex> g(ss.mu);
 	if (filter && (filter->store != s || filter->epoch != s->epoch)) {
 		set_error("lmd_search_batch_filtered: the filter was built for another store or before rows were added / "
 		          "removed; create it again");
 		return LMD_ERR_STATE;
 	}
+	if (filter && route == LMD_ROUTE_INT8) {
+		set_error("lmd_search_batch_filtered: the int8 edge codec has no filtered kernels");
+		return LMD_ERR_UNSUPPORTED;
+	}
 	LMD_CUDA_OK(cudaSetDevice(s->device));
-	cudaStream_t st = s->stream;
+	cudaStream_t st = ss.stream;
 	const uint32_t q32 = (uint32_t)nq;
 	void *a_q, *a_ids, *a_dist, *a_count, *a_qstats;
 	const BufKind kq = classify(queries, &a_q), ki = classify(out_ids, &a_ids), kd = classify(out_dist, &a_dist),
@@ -136,7 +162,7 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 		return LMD_ERR_INVALID_ARG;
 	}
 	const bool dev_io = !stage_q && !stage_out; // nothing to copy: device-resident or zero-copy pinned buffers
-	const bool separate = route == LMD_ROUTE_TERNARY || (flags & LMD_SEARCH_SEPARATE_RERANK);
+	const bool separate = route != LMD_ROUTE_EXACT || (flags & LMD_SEARCH_SEPARATE_RERANK);
 	const bool want_qstats = (flags & LMD_SEARCH_PER_QUERY_STATS) && out_qstats;
 	const bool async = (flags & LMD_SEARCH_ASYNC) != 0;
 	lmd_status rc;
@@ -146,53 +172,76 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 	}
 
 	if (!async) {
-		LMD_CUDA_OK(cudaEventRecord(s->ev[0], st));
+		LMD_CUDA_OK(cudaEventRecord(ss.ev[0], st));
 	}
 	const float *d_q = static_cast<const float *>(a_q);
 	int64_t *d_ids = static_cast<int64_t *>(a_ids);
 	float *d_dist = static_cast<float *>(a_dist);
 	uint32_t *d_count = static_cast<uint32_t *>(a_count);
 	uint32_t *d_qstats = want_qstats ? static_cast<uint32_t *>(a_qstats) : nullptr;
-	if (stage_q) {
-		uint64_t need_q = nq * (uint64_t)s->cfg.dims;
-		uint64_t have_q = s->scratch_q;
-		if ((rc = grow(s->d_q, have_q, need_q, s)) != LMD_OK) {
-			s->scratch_q = 0;
+	// Pageable point queries and small batches (DuckDB hands Scan a pageable float* and a std::vector to fill,
+	// core/ISearcher.hpp:30-34): the query is copied into this state's pinned, device-mapped block with a host memcpy and
+	// the kernels read it and write the result there in place - no cudaMemcpy call on either side of the launch.
+	const uint64_t out_bytes = nq * ((uint64_t)k * 12 + 12);
+	const bool pin_q = stage_q && nq * (uint64_t)s->cfg.dims * 4 <= PIN_Q_BYTES && (!stage_out || out_bytes <= PIN_OUT_BYTES);
+	const bool pin_out = stage_out && out_bytes <= PIN_OUT_BYTES && (!stage_q || pin_q);
+	if ((pin_q || pin_out) && !ss.h_pin) {
+		LMD_CUDA_OK(cudaHostAlloc((void **)&ss.h_pin, PIN_Q_BYTES + PIN_OUT_BYTES, cudaHostAllocMapped | cudaHostAllocPortable));
+	}
+	int64_t *p_ids = nullptr;
+	float *p_dist = nullptr;
+	uint32_t *p_count = nullptr, *p_qstats = nullptr;
+	if (pin_q) {
+		memcpy(ss.h_pin, queries, nq * (uint64_t)s->cfg.dims * 4);
+		void *dp = nullptr;
+		LMD_CUDA_OK(cudaHostGetDevicePointer(&dp, ss.h_pin, 0));
+		d_q = static_cast<const float *>(dp);
+	} else if (stage_q) {
+		const uint64_t need_q = nq * (uint64_t)s->cfg.dims;
+		if ((rc = grow_to(ss.d_q, ss.scratch_q, need_q)) != LMD_OK) {
 			return rc;
 		}
-		s->scratch_q = have_q;
-		LMD_CUDA_OK(cudaMemcpyAsync(s->d_q, queries, need_q * sizeof(float), cudaMemcpyHostToDevice, st));
-		d_q = s->d_q;
+		LMD_CUDA_OK(cudaMemcpyAsync(ss.d_q, queries, need_q * sizeof(float), cudaMemcpyHostToDevice, st));
+		d_q = ss.d_q;
 	}
-	if (stage_out) {
-		uint64_t need_k = nq * (uint64_t)k;
-		if (s->scratch_k < need_k || !s->d_out_ids) {
-			uint64_t a = 0, b = 0, c = 0, d = 0;
-			if ((rc = grow(s->d_out_ids, a, need_k, s)) != LMD_OK || (rc = grow(s->d_out_dist, b, need_k, s)) != LMD_OK ||
-			    (rc = grow(s->d_out_count, c, need_k, s)) != LMD_OK ||
-			    (rc = grow(s->d_qstats, d, std::max<uint64_t>(need_k, 2 * nq), s)) != LMD_OK) {
-				s->scratch_k = 0;
-				return rc;
-			}
-			s->scratch_k = need_k;
+	if (pin_out) {
+		uint8_t *o = ss.h_pin + PIN_Q_BYTES;
+		p_ids = reinterpret_cast<int64_t *>(o);
+		p_dist = reinterpret_cast<float *>(o + nq * k * 8);
+		p_count = reinterpret_cast<uint32_t *>(o + nq * k * 12);
+		p_qstats = reinterpret_cast<uint32_t *>(o + nq * k * 12 + nq * 4);
+		void *dp = nullptr;
+		LMD_CUDA_OK(cudaHostGetDevicePointer(&dp, o, 0));
+		uint8_t *d = static_cast<uint8_t *>(dp);
+		d_ids = reinterpret_cast<int64_t *>(d);
+		d_dist = reinterpret_cast<float *>(d + nq * k * 8);
+		d_count = reinterpret_cast<uint32_t *>(d + nq * k * 12);
+		d_qstats = want_qstats ? reinterpret_cast<uint32_t *>(d + nq * k * 12 + nq * 4) : nullptr;
+	} else if (stage_out) {
+		const uint64_t need_k = nq * (uint64_t)k;
+		if ((rc = grow_to(ss.d_out_ids, ss.scratch_k, need_k)) != LMD_OK) {
+			return rc;
 		}
-		d_ids = s->d_out_ids;
-		d_dist = s->d_out_dist; // always computed on the device; copied back only when asked for
-		d_count = s->d_out_count;
-		d_qstats = want_qstats ? s->d_qstats : nullptr;
+		uint64_t have_d = ss.d_out_dist ? ss.scratch_k : 0; // ids and distances grow together
+		if ((rc = grow_to(ss.d_out_dist, have_d, ss.scratch_k)) != LMD_OK ||
+		    (rc = grow_to(ss.d_out_count, ss.scratch_cnt, nq)) != LMD_OK ||
+		    (want_qstats && (rc = grow_to(ss.d_qstats, ss.scratch_qs, 2 * nq)) != LMD_OK)) {
+			ss.scratch_k = 0;
+			return rc;
+		}
+		d_ids = ss.d_out_ids;
+		d_dist = ss.d_out_dist; // always computed on the device; copied back only when asked for
+		d_count = ss.d_out_count;
+		d_qstats = want_qstats ? ss.d_qstats : nullptr;
 	}
 	uint64_t *d_cand = nullptr;
 	if (separate) {
-		uint64_t need_c = nq * (uint64_t)l_used;
-		uint64_t have_c = s->scratch_cand;
-		if ((rc = grow(s->d_cand, have_c, need_c, s)) != LMD_OK) {
-			s->scratch_cand = 0;
+		if ((rc = grow_to(ss.d_cand, ss.scratch_cand, nq * (uint64_t)l_used)) != LMD_OK) {
 			return rc;
 		}
-		s->scratch_cand = have_c;
-		d_cand = s->d_cand;
+		d_cand = ss.d_cand;
 	}
-	LMD_CUDA_OK(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), st));
+	LMD_CUDA_OK(cudaMemsetAsync(ss.d_counters, 0, 8 * sizeof(unsigned long long), st));
 
 	TraverseArgs ta;
 	ta.s = s;
@@ -207,14 +256,17 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 	ta.d_qstats = d_qstats;
 	ta.d_cand = d_cand;
 	ta.d_allowed = filter ? filter->d_bits : nullptr;
+	ta.strict = (flags & LMD_SEARCH_STRICT_FP) != 0;
+	ta.no_prefilter = (flags & LMD_SEARCH_NO_PREFILTER) != 0;
+	ta.d_counters = ss.d_counters;
 	if (!async) {
-		LMD_CUDA_OK(cudaEventRecord(s->ev[1], st));
+		LMD_CUDA_OK(cudaEventRecord(ss.ev[1], st));
 	}
 	if ((rc = launch_traverse(ta, st)) != LMD_OK) {
 		return rc;
 	}
 	if (!async) {
-		LMD_CUDA_OK(cudaEventRecord(s->ev[2], st));
+		LMD_CUDA_OK(cudaEventRecord(ss.ev[2], st));
 	}
 	uint32_t launches = 1;
 	if (separate) {
@@ -228,6 +280,9 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 		ra.d_out_ids = d_ids;
 		ra.d_out_dist = d_dist;
 		ra.d_out_count = d_count;
+		ra.strict = (flags & LMD_SEARCH_STRICT_FP) != 0;
+		ra.tensor = (flags & LMD_SEARCH_TENSOR_RERANK) != 0;
+		ra.d_counters = ss.d_counters;
 		if ((rc = launch_rerank(ra, st)) != LMD_OK) {
 			return rc;
 		}
@@ -236,8 +291,8 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 	if (async) {
 		return LMD_OK;
 	}
-	LMD_CUDA_OK(cudaEventRecord(s->ev[3], st));
-	if (stage_out) {
+	LMD_CUDA_OK(cudaEventRecord(ss.ev[3], st));
+	if (stage_out && !pin_out) {
 		LMD_CUDA_OK(cudaMemcpyAsync(out_ids, d_ids, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
 		if (out_dist) {
 			LMD_CUDA_OK(cudaMemcpyAsync(out_dist, d_dist, nq * k * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -251,13 +306,25 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 	}
 	unsigned long long h_cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 	if (stats) {
-		LMD_CUDA_OK(cudaMemcpyAsync(h_cnt, s->d_counters, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
+		LMD_CUDA_OK(cudaMemcpyAsync(h_cnt, ss.d_counters, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
 	}
-	LMD_CUDA_OK(cudaEventRecord(s->ev[4], st));
+	LMD_CUDA_OK(cudaEventRecord(ss.ev[4], st));
 	cudaError_t e = cudaStreamSynchronize(st);
 	if (e != cudaSuccess) {
 		set_error("search kernels failed: %s", cudaGetErrorString(e));
 		return LMD_ERR_CUDA;
+	}
+	if (pin_out) {
+		memcpy(out_ids, p_ids, nq * k * sizeof(int64_t));
+		if (out_dist) {
+			memcpy(out_dist, p_dist, nq * k * sizeof(float));
+		}
+		if (out_count) {
+			memcpy(out_count, p_count, nq * sizeof(uint32_t));
+		}
+		if (want_qstats) {
+			memcpy(out_qstats, p_qstats, nq * 2 * sizeof(uint32_t));
+		}
 	}
 	if (stats) {
 		stats->queries = nq;
@@ -267,24 +334,30 @@ static lmd_status search_impl(lmd_store *s, const lmd_filter *filter, const floa
 		stats->reranked = h_cnt[4];
 		stats->tie_overflows = h_cnt[5];
 		stats->merge_fallbacks = h_cnt[6];
+		stats->exact_fetches = h_cnt[7];
 		stats->launches = launches;
 		stats->l_used = l_used;
-		cudaEventElapsedTime(&stats->traverse_ms, s->ev[1], s->ev[2]);
+		cudaEventElapsedTime(&stats->traverse_ms, ss.ev[1], ss.ev[2]);
 		if (separate) {
-			cudaEventElapsedTime(&stats->rerank_ms, s->ev[2], s->ev[3]);
+			cudaEventElapsedTime(&stats->rerank_ms, ss.ev[2], ss.ev[3]);
 		}
-		cudaEventElapsedTime(&stats->total_ms, s->ev[0], s->ev[4]);
+		cudaEventElapsedTime(&stats->total_ms, ss.ev[0], ss.ev[4]);
 		if (stage_q) {
-			cudaEventElapsedTime(&stats->h2d_ms, s->ev[0], s->ev[1]);
+			cudaEventElapsedTime(&stats->h2d_ms, ss.ev[0], ss.ev[1]);
 		}
 		if (stage_out) {
-			cudaEventElapsedTime(&stats->d2h_ms, s->ev[3], s->ev[4]);
+			cudaEventElapsedTime(&stats->d2h_ms, ss.ev[3], ss.ev[4]);
 		}
 		// SURVEY.md section 8d. The sidecar holds uint32 slots, so an expansion reads 4R bytes of ids
 		// (the reference's 8 + 8R becomes 4R); padding is never counted.
 		const uint64_t vec = (uint64_t)s->cfg.dims * 4;
 		uint64_t bytes = nq * ((uint64_t)s->cfg.dims * 4 + (uint64_t)k * 12);
-		if (route == LMD_ROUTE_EXACT) {
+		const bool prefiltered = route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && !ta.no_prefilter && !filter &&
+		                         !ta.strict && !s->tune.strict_fp && s->tune.prefilter != 0;
+		if (route == LMD_ROUTE_INT8 || prefiltered) {
+			// one code block per expansion (neighbour slots + code norms + R int8 codes), then an exact row per fetched node
+			bytes += h_cnt[1] * (uint64_t)s->code_block_bytes + h_cnt[7] * vec + (route == LMD_ROUTE_INT8 ? vec * nq : 0);
+		} else if (route == LMD_ROUTE_EXACT) {
 			bytes += h_cnt[1] * 4ull * s->cfg.r + h_cnt[2] * vec;
 		} else {
 			bytes += h_cnt[1] * (4ull * s->cfg.r) + h_cnt[2] * (uint64_t)s->lay.ternary_edge_bytes + vec * nq;
@@ -303,7 +376,11 @@ extern "C" {
 lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
                             uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
                             uint32_t *out_qstats, lmd_stats *stats) {
-	return search_impl(s, nullptr, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
+	if (!s) {
+		set_error("lmd_search_batch: null store");
+		return LMD_ERR_INVALID_ARG;
+	}
+	return search_impl(s, s->def, nullptr, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
 }
 
 lmd_status lmd_search_batch_filtered(lmd_store *s, const lmd_filter *filter, const float *queries, uint64_t nq,
@@ -313,7 +390,72 @@ lmd_status lmd_search_batch_filtered(lmd_store *s, const lmd_filter *filter, con
 		set_error("lmd_search_batch_filtered: null filter");
 		return LMD_ERR_INVALID_ARG;
 	}
-	return search_impl(s, filter, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
+	if (!s) {
+		set_error("lmd_search_batch_filtered: null store");
+		return LMD_ERR_INVALID_ARG;
+	}
+	return search_impl(s, s->def, filter, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats, stats);
+}
+
+// ---- per-caller search contexts ----------------------------------------------------------------------------------
+lmd_status lmd_ctx_create(lmd_store *s, lmd_ctx **out) {
+	if (!s || !out) {
+		set_error("lmd_ctx_create: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	*out = nullptr;
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	lmd_ctx *c = new (std::nothrow) lmd_ctx();
+	if (!c) {
+		set_error("host allocation failed");
+		return LMD_ERR_OOM;
+	}
+	c->store = s;
+	lmd_status rc = state_init(c->st);
+	if (rc != LMD_OK) {
+		state_free(c->st);
+		delete c;
+		return rc;
+	}
+	cudaStreamSynchronize(c->st.stream);
+	*out = c;
+	return LMD_OK;
+}
+
+lmd_status lmd_ctx_destroy(lmd_ctx *c) {
+	if (!c) {
+		return LMD_OK;
+	}
+	cudaSetDevice(c->store->device);
+	{
+		std::lock_guard<std::mutex> g(c->st.mu); // a search still running on another thread finishes first
+	}
+	state_free(c->st);
+	delete c;
+	return LMD_OK;
+}
+
+lmd_status lmd_ctx_set_stream(lmd_ctx *c, void *cuda_stream) {
+	if (!c) {
+		set_error("lmd_ctx_set_stream: null context");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::lock_guard<std::mutex> g(c->st.mu);
+	LMD_CUDA_OK(cudaSetDevice(c->store->device));
+	LMD_CUDA_OK(cudaStreamSynchronize(c->st.stream));
+	c->st.stream = cuda_stream ? (cudaStream_t)cuda_stream : c->st.own_stream;
+	return LMD_OK;
+}
+
+lmd_status lmd_ctx_search_batch(lmd_ctx *c, const lmd_filter *filter, const float *queries, uint64_t nq, uint32_t k,
+                                uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids, float *out_dist,
+                                uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats) {
+	if (!c) {
+		set_error("lmd_ctx_search_batch: null context");
+		return LMD_ERR_INVALID_ARG;
+	}
+	return search_impl(c->store, c->st, filter, queries, nq, k, L, route, flags, out_ids, out_dist, out_count, out_qstats,
+	                   stats);
 }
 
 lmd_status lmd_merge_topk_async(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq,

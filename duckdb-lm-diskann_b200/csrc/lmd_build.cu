@@ -175,7 +175,7 @@ __global__ void slots_to_rows_kernel(const uint32_t *__restrict__ slots, uint64_
 }
 
 static uint32_t prune_smem_bytes(const lmd_store *s, uint32_t list_cap) {
-	const bool generic = !(s->row_floats == 128 || s->row_floats == 96 || s->row_floats == 768);
+	const bool generic = s->tune.strict_fp || !(s->row_floats == 128 || s->row_floats == 96 || s->row_floats == 768);
 	const uint32_t rpad = (s->cfg.r + 31) & ~31u;
 	return (uint32_t)(((size_t)list_cap * 8 + 384 + (size_t)rpad * 4 + (generic ? (size_t)s->row_floats * 4 : 0) + 15) /
 	                  16 * 16);
@@ -188,6 +188,7 @@ static PruneParams prune_base(const lmd_store *s, float alpha, uint32_t list_cap
 	p.kp.row_floats = s->row_floats;
 	p.kp.dims = s->cfg.dims;
 	p.kp.metric = s->cfg.metric;
+	p.kp.strict = s->tune.strict_fp ? 1u : 0u;
 	p.alpha = alpha;
 	p.r = s->cfg.r;
 	p.nbrs = s->d_nbrs;
@@ -250,7 +251,11 @@ lmd_status lmd_store_upload_vectors(lmd_store *s, const int64_t *row_ids, const 
 	if (n == 0) {
 		return LMD_OK;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_store_upload_vectors: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	if (s->n + n > s->capacity) {
 		set_error("lmd_store_upload_vectors: %llu + %llu nodes exceed the store capacity %llu", (unsigned long long)s->n,
 		          (unsigned long long)n, (unsigned long long)s->capacity);
@@ -285,7 +290,11 @@ lmd_status lmd_store_download_blocks(lmd_store *s, uint64_t first_slot, uint64_t
 		set_error("lmd_store_download_blocks: null argument");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_store_download_blocks: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	if (first_slot + n > s->n) {
 		set_error("lmd_store_download_blocks: slots [%llu, %llu) are beyond the %llu mirrored nodes",
 		          (unsigned long long)first_slot, (unsigned long long)(first_slot + n), (unsigned long long)s->n);
@@ -314,7 +323,7 @@ lmd_status lmd_robust_prune_batch(lmd_store *s, const int64_t *node_row_ids, con
 		set_error("lmd_robust_prune_batch: candidate count must be in [1, 512], R <= 512");
 		return LMD_ERR_UNSUPPORTED;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	cudaStream_t st = s->stream;
 	const uint32_t r = s->cfg.r;
@@ -383,7 +392,11 @@ lmd_status lmd_build_graph(lmd_store *s, const lmd_build_params *params, lmd_bui
 		set_error("lmd_build_graph: this build supports L_INSERT <= 512 and R <= 128 (got %u, %u)", L, r);
 		return LMD_ERR_UNSUPPORTED;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_build_graph: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	const uint64_t n = s->n;
 	if (n == 0) {
 		return LMD_OK;
@@ -562,6 +575,7 @@ lmd_status lmd_build_graph(lmd_store *s, const lmd_build_params *params, lmd_bui
 			cudaEventElapsedTime(&bs.total_ms, ev_all0, ev_all1);
 			bs.launches += 2;
 			s->dirty = false; // d_nbrs IS the sidecar of the blocks just written; d_vecs is unchanged
+			s->views_gen++;
 		}
 	}
 	drop_events();

@@ -117,7 +117,8 @@ __global__ void __launch_bounds__(128) prune_kernel(const PruneParams p) {
 		const bool any_loose = p.cand_slots || p.use_existing || p.inbox;
 		if (any_loose) {
 			QueryRegs<TEAM, CH> Q;
-			load_vec<TEAM, CH>(Q, kp.vecs + (uint64_t)node * kp.row_floats, kp.dims, kp.row_floats, lane, s_q);
+			load_vec<TEAM, CH>(Q, kp.vecs + (uint64_t)node * kp.row_floats, kp.dims, kp.row_floats, lane, s_q,
+			                   CH == 0 && kp.strict);
 			uint32_t n_in = 0;
 			if (p.inbox) {
 				n_in = p.inbox_cnt[node];
@@ -171,7 +172,8 @@ __global__ void __launch_bounds__(128) prune_kernel(const PruneParams p) {
 			bool pruned = false;
 			if (nsel > 0) {
 				QueryRegs<TEAM, CH> Qp;
-				load_vec<TEAM, CH>(Qp, kp.vecs + (uint64_t)cand * kp.row_floats, kp.dims, kp.row_floats, lane, s_q);
+				load_vec<TEAM, CH>(Qp, kp.vecs + (uint64_t)cand * kp.row_floats, kp.dims, kp.row_floats, lane, s_q,
+				                   CH == 0 && kp.strict);
 				for (uint32_t b = 0; b < nsel && !pruned; b += 32) {
 					const int m = (int)(nsel - b < 32u ? nsel - b : 32u);
 					const float dpr = batch_distances<TEAM, CH, G, METRIC>(Qp, kp, s_sel + b, s_d, s_d2, m, lane);
@@ -246,7 +248,9 @@ static lmd_status launch_prune(K kernel, PruneParams &p, const lmd_store *s, cud
 }
 
 #define LMD_DISPATCH_PRUNE_SHAPE(METRIC)                                                                               \
-	if (p.kp.row_floats == 128) {                                                                                      \
+	if (p.kp.strict) {                                                                                                 \
+		return launch_prune(prune_kernel<32, 0, 1, METRIC>, p, s, st);                                                 \
+	} else if (p.kp.row_floats == 128) {                                                                                      \
 		return launch_prune(prune_kernel<8, 4, 2, METRIC>, p, s, st);                                                  \
 	} else if (p.kp.row_floats == 96) {                                                                                \
 		return launch_prune(prune_kernel<8, 3, 2, METRIC>, p, s, st);                                                  \

@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
 #include <unordered_map>
 #include <utility>
@@ -81,6 +82,30 @@ struct Tuning {
 	int prefetch_planes = 1; // ternary routing: prefetch the plane region of the likely next expansion into L2
 	int latency_mode = -1; // -1 = latency kernels for batches below ~10 queries per SM, 0 = never, 1 = always
 	int merge_min = 0;     // batch-merge new candidates when at least this many pass the threshold (0 = default 5)
+	int strict_fp = 0;     // 1 = every kernel of this store accumulates distances in the reference's order (parity tool)
+	int code_sigmas = 0;   // int8 codec grid: scale = code_sigmas / 10 * max sigma / 127 (0 = 4.0 sigmas)
+	int plane_filter_cap = 0; // 1 = the old 2 KB visited-filter cap for ternary routing over wide planes (pre-sidecar rule)
+	int prefilter = 1;     // exact routing on a codec store: 1 = int8 lower-bound pre-filter, 0 = plain traversal
+};
+
+// Everything ONE in-flight search call owns: its stream, events, statistics counters and staging scratch. The store has
+// one of its own (lmd_search_batch, the build and the upload paths run on it); every lmd_ctx is another, so searches
+// issued from different host threads through different contexts share nothing but the read-only node store.
+struct SearchState {
+	cudaStream_t stream = nullptr, own_stream = nullptr; // stream = the active one
+	cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+	unsigned long long *d_counters = nullptr; // [16] work counter + statistics ([8], [9]: store-side scratch)
+	// host<->device staging of one search call (grown on demand)
+	float *d_q = nullptr;
+	int64_t *d_out_ids = nullptr;
+	float *d_out_dist = nullptr;
+	uint32_t *d_out_count = nullptr;
+	uint32_t *d_qstats = nullptr;
+	uint64_t *d_cand = nullptr; // [nq][L] candidate keys for the separate rerank kernel
+	uint64_t scratch_q = 0, scratch_k = 0, scratch_qs = 0, scratch_cnt = 0, scratch_cand = 0;
+	// small pinned (mapped) block for pageable point queries: the kernels read the query and write the result in place
+	uint8_t *h_pin = nullptr;
+	std::mutex mu; // one call at a time per state
 };
 
 } // namespace lmd
@@ -104,17 +129,11 @@ struct lmd_store {
 	uint32_t *d_map_vals = nullptr;
 	uint64_t map_cap = 0;
 	bool identity = true;          // every row id so far equals its slot: the map is bypassed
-	unsigned long long *d_counters = nullptr; // [16] work counter + statistics ([8], [9]: store-side scratch)
 	uint64_t device_bytes = 0;
 
-	// scratch for host<->device staging of one search call (grown on demand)
-	float *d_q = nullptr;
-	int64_t *d_out_ids = nullptr;
-	float *d_out_dist = nullptr;
-	uint32_t *d_out_count = nullptr;
-	uint32_t *d_qstats = nullptr;
-	uint64_t *d_cand = nullptr; // [nq][L] candidate keys for the separate rerank kernel
-	uint64_t scratch_q = 0, scratch_k = 0, scratch_cand = 0;
+	// the store's own search state; the names below keep meaning "the default context's"
+	lmd::SearchState def;
+	unsigned long long *&d_counters = def.d_counters;
 	void *h_stage = nullptr; // pinned staging for pageable uploads
 	size_t h_stage_bytes = 0;
 
@@ -131,16 +150,42 @@ struct lmd_store {
 	uint64_t epoch = 0;     // bumped whenever the row id -> slot mapping may have changed (filters are tied to it)
 	uint64_t removed = 0;   // row ids taken out by lmd_store_remove (their slots stay allocated)
 
+	// Routing sidecars (built lazily, rebuilt when the views changed): per node ONE contiguous block holding the slots of
+	// its R neighbours and their compressed vectors, chunk-major so that lane j's loads of neighbour j coalesce.
+	//   d_side_t  ternary planes (a transposition of the block's own plane region; ROUTE_TERNARY reads nothing else)
+	//   d_codes   int8 edge codec (x ~ code_off[d] + code_scale * c[d]; ROUTE_INT8 and the exact route's pre-filter)
+	uint64_t views_gen = 1;              // bumped by everything that changes blocks / d_vecs / d_nbrs
+	uint8_t *d_side_t = nullptr;
+	uint32_t side_t_bytes = 0, side_t_off = 0;
+	uint64_t side_t_gen = 0;
+	uint32_t codec = 0;                  // LMD_CODEC_* requested by lmd_store_enable_codec
+	uint8_t *d_codes = nullptr;
+	float *d_code_off = nullptr;         // [row_floats + 1]: per-dimension offsets, then the scale
+	float code_scale = 1.0f;
+	uint32_t code_block_bytes = 0, code_data_off = 0;
+	uint64_t codes_gen = 0;
+	bool blocks_released = false;        // lmd_store_release_blocks: d_blocks is gone (search-only store)
+
 	// graph-build scratch (lmd_build.cu), allocated on first use and kept
 	uint32_t *d_inbox = nullptr, *d_inbox_cnt = nullptr, *d_touched = nullptr;
 	uint64_t *d_planes = nullptr; // [capacity][2 * words] ternary planes of every node
 	uint32_t inbox_cap = 0;
 
-	cudaStream_t stream = nullptr, own_stream = nullptr, copy_stream = nullptr; // stream = the active one
-	cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+	cudaStream_t &stream = def.stream, &own_stream = def.own_stream; // stream = the active one
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t (&ev)[8] = def.ev;
 	lmd::Tuning tune;
 	mutable std::unordered_map<uint64_t, std::pair<int, int>> launch_cache; // (kernel, smem) -> (warps per CTA, CTAs per SM)
-	std::mutex mu;
+	mutable std::mutex cache_mu; // launch_cache is filled by concurrent searches
+	// Searches hold `mu` shared (they only read the store) plus their own SearchState::mu; everything that changes the
+	// store - uploads, apply / remove, finalize, build, tuning, stream binding - holds it exclusively.
+	std::shared_mutex mu;
+};
+
+// A per-caller search context (include/lmd_b200.h lmd_ctx_*): its own stream, counters and scratch on the store's device.
+struct lmd_ctx {
+	lmd_store *store = nullptr;
+	lmd::SearchState st;
 };
 
 // An allowed-ids set resolved to the store's slots (filtered search).
@@ -153,6 +198,16 @@ struct lmd_filter {
 };
 
 namespace lmd {
+
+// SearchState life cycle (lmd_store.cu): stream, events, counters; the scratch grows on demand in lmd_api.cu.
+lmd_status state_init(SearchState &st);
+void state_free(SearchState &st);
+
+// Makes the store ready for a search of `route`: rebuilds the neighbour-slot view when dirty and whichever routing
+// sidecar the route needs (takes s->mu exclusively). route_ready() is the shared-lock test for the same condition.
+lmd_status store_prepare(lmd_store *s, uint32_t route);
+lmd_status finalize_locked(lmd_store *s); // the caller holds s->mu exclusively
+bool route_ready(const lmd_store *s, uint32_t route);
 
 // Store internals shared with lmd_build.cu (the caller holds s->mu).
 lmd_status store_copy_to_device(lmd_store *s, void *dst, const void *src, size_t bytes);
@@ -171,6 +226,9 @@ struct TraverseArgs {
 	uint32_t *d_qstats;   // [nq][2] or null
 	uint64_t *d_cand;     // [nq][L] or null
 	const uint32_t *d_allowed = nullptr; // filtered search: bitmap over slots, null = unfiltered
+	bool strict = false;                 // LMD_SEARCH_STRICT_FP
+	bool no_prefilter = false;           // LMD_SEARCH_NO_PREFILTER
+	unsigned long long *d_counters = nullptr; // the calling SearchState's counters (null = the store's own)
 };
 lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st);
 
@@ -182,6 +240,9 @@ struct RerankArgs {
 	int64_t *d_out_ids;
 	float *d_out_dist;
 	uint32_t *d_out_count;
+	bool strict = false;
+	bool tensor = false; // LMD_SEARCH_TENSOR_RERANK
+	unsigned long long *d_counters = nullptr;
 };
 lmd_status launch_rerank(const RerankArgs &a, cudaStream_t st);
 

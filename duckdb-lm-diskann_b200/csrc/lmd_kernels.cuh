@@ -55,9 +55,25 @@ struct KParams {
 	const uint32_t *__restrict__ allowed;
 	uint32_t res_off; // byte offset of the results list RH inside the warp's shared memory
 	uint32_t latency; // host side only: dispatch to the latency variants
+	// LMD_SEARCH_STRICT_FP: distances accumulated exactly as core/distance.hpp:56-99 does - one lane per row, element by
+	// element, separate multiply and add (no FMA) - so that every comparison of the traversal sees the reference's own
+	// bits. Served by the generic-shape kernels only (the query sits in shared memory); a parity tool, never timed.
+	uint32_t strict;
+	// Per-node routing sidecar (ternary planes or int8 codes of the node's R neighbours, laid out so that lane j's loads
+	// of neighbour j coalesce across the warp - see lmd_store.cu build_plane_side_kernel / build_code_side_kernel):
+	//   [u32 slot[R]] [int8 codec only: u32 csq[R], f32 err[R]] pad->16 [data: chunk-major, 16 bytes per (chunk, neighbour)]
+	const uint8_t *__restrict__ side;
+	uint32_t side_bytes;    // bytes per node
+	uint32_t side_data_off; // offset of the chunk-major data inside a node's sidecar block
+	// int8 edge codec: x ~ code_off[d] + code_scale * c[d], c in [-127, 127]
+	const float *__restrict__ code_off; // [row_floats]
+	float code_scale;
+	uint32_t prefilter;     // exact routing: 1 = the int8 lower bound decides which neighbours' rows are fetched at all
 };
 
 #define FULL 0xFFFFFFFFu
+// kernel-side route: the public LMD_ROUTE_* values plus exact routing with the int8 lower-bound pre-filter
+#define LMD_KROUTE_EXACT_PF 3
 #define FILTER_EMPTY 0xFFFFFFFFu
 
 __device__ __forceinline__ float4 ldg4(const float *p) {
@@ -131,7 +147,7 @@ struct QueryRegs {
 // Loads one vector (dims floats at src; row_floats = dims padded to a multiple of 32) into the warp's query view.
 template <int TEAM, int CH>
 __device__ __forceinline__ void load_vec(QueryRegs<TEAM, CH> &Q, const float *src, uint32_t dims, uint32_t row_floats,
-                                         int lane, float *s_q) {
+                                         int lane, float *s_q, bool strict = false) {
 	float na = 0.0f;
 	if (CH > 0) {
 		const int tl = lane % TEAM;
@@ -157,6 +173,13 @@ __device__ __forceinline__ void load_vec(QueryRegs<TEAM, CH> &Q, const float *sr
 		na = team_sum<32>(na);
 		Q.sq = s_q;
 		__syncwarp();
+		if (strict) { // norm_a_sq of distance.hpp:77-83: element by element, multiply then add
+			na = 0.0f;
+			for (uint32_t f = 0; f < dims; f++) {
+				const float v = s_q[f];
+				na = __fadd_rn(na, __fmul_rn(v, v));
+			}
+		}
 	}
 	Q.na = na;
 }
@@ -164,7 +187,7 @@ __device__ __forceinline__ void load_vec(QueryRegs<TEAM, CH> &Q, const float *sr
 template <int TEAM, int CH, int METRIC>
 __device__ __forceinline__ void load_query(QueryRegs<TEAM, CH> &Q, const KParams &p, uint32_t qi, int lane,
                                            float *s_q) {
-	load_vec<TEAM, CH>(Q, p.queries + (uint64_t)qi * p.q_stride, p.dims, p.row_floats, lane, s_q);
+	load_vec<TEAM, CH>(Q, p.queries + (uint64_t)qi * p.q_stride, p.dims, p.row_floats, lane, s_q, CH == 0 && p.strict);
 }
 
 // Raw partial results of the exact distance from the query to the m (1..32) nodes whose slots are in s_nb[0..m):
@@ -209,6 +232,28 @@ __device__ __forceinline__ void compute_batch(const QueryRegs<TEAM, CH> &Q, cons
 						s_b2[j] = b;
 					}
 				}
+			}
+		}
+	} else if (p.strict) {
+		// the reference's own summation (core/distance.hpp:56-61, :69-73, :76-83): lane j walks row j front to back
+		if (lane < m) {
+			const float *row = p.vecs + (uint64_t)s_nb[lane] * p.row_floats;
+			float a = 0.0f, b = 0.0f;
+			for (uint32_t i = 0; i < p.dims; i++) {
+				const float x = __ldg(row + i), q = Q.sq[i];
+				if (METRIC == LMD_METRIC_L2) {
+					const float d = __fsub_rn(q, x);
+					a = __fadd_rn(a, __fmul_rn(d, d));
+				} else {
+					a = __fadd_rn(a, __fmul_rn(q, x));
+					if (METRIC == LMD_METRIC_COSINE) {
+						b = __fadd_rn(b, __fmul_rn(x, x));
+					}
+				}
+			}
+			s_a[lane] = a;
+			if (METRIC == LMD_METRIC_COSINE) {
+				s_b2[lane] = b;
 			}
 		}
 	} else {
@@ -604,40 +649,101 @@ __device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t q
 	__syncwarp();
 }
 
-// core/ternary_quantization.hpp:269-296 (Dot_scalar) + core/distance.hpp:229-235 for neighbour j of block `blk`.
-// WORDS = u64 words per plane when the shape is specialised (every load of the neighbour's two planes is issued before
-// the first popcount), 0 = read it from the parameters.
+// core/ternary_quantization.hpp:269-296 (Dot_scalar) + core/distance.hpp:229-235 for neighbour j of the expanded node.
+// The planes come from the node's routing sidecar: word w of neighbour j is ONE 16-byte entry {pos.lo, pos.hi, neg.lo,
+// neg.hi} at data[(w * R + j) * 16], so the warp's load of word w is 512 contiguous bytes (the block's own SoA planes put
+// lane j's 8-byte words 8 * words bytes apart: 23 sectors per request at D = 768, profiles/r19_ternary768_ncu_details.csv).
+// WORDS = u64 words per plane when the shape is specialised (every load issued before the first popcount), 0 = runtime.
 template <int WORDS>
-__device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_t *blk, uint32_t j,
+__device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_t *side_blk, uint32_t j,
                                                   const uint32_t *s_qp, const uint32_t *s_qn) {
 	const uint32_t words = WORDS > 0 ? (uint32_t)WORDS : p.words;
-	const uint2 *vp = reinterpret_cast<const uint2 *>(blk + p.pos_off) + (uint64_t)j * words;
-	const uint2 *vn = reinterpret_cast<const uint2 *>(blk + p.neg_off) + (uint64_t)j * words;
+	const uint4 *pl = reinterpret_cast<const uint4 *>(side_blk + p.side_data_off) + j;
 	int score = 0;
 	if (WORDS > 0) {
-		uint2 a[WORDS > 0 ? WORDS : 1], b[WORDS > 0 ? WORDS : 1];
+		uint4 v[WORDS > 0 ? WORDS : 1];
 #pragma unroll
 		for (int w = 0; w < WORDS; w++) {
-			a[w] = __ldg(vp + w);
-			b[w] = __ldg(vn + w);
+			v[w] = __ldg(pl + (uint32_t)w * p.r);
 		}
 #pragma unroll
 		for (int w = 0; w < WORDS; w++) {
 			const uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
-			score += __popc(qp0 & a[w].x) + __popc(qp1 & a[w].y) + __popc(qn0 & b[w].x) + __popc(qn1 & b[w].y);
-			score -= __popc(qp0 & b[w].x) + __popc(qp1 & b[w].y) + __popc(qn0 & a[w].x) + __popc(qn1 & a[w].y);
+			score += __popc(qp0 & v[w].x) + __popc(qp1 & v[w].y) + __popc(qn0 & v[w].z) + __popc(qn1 & v[w].w);
+			score -= __popc(qp0 & v[w].z) + __popc(qp1 & v[w].w) + __popc(qn0 & v[w].x) + __popc(qn1 & v[w].y);
 		}
 	} else {
 		for (uint32_t w = 0; w < words; w++) {
-			uint2 a = __ldg(vp + w), b = __ldg(vn + w);
-			uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
-			score += __popc(qp0 & a.x) + __popc(qp1 & a.y) + __popc(qn0 & b.x) + __popc(qn1 & b.y);
-			score -= __popc(qp0 & b.x) + __popc(qp1 & b.y) + __popc(qn0 & a.x) + __popc(qn1 & a.y);
+			const uint4 v = __ldg(pl + w * p.r);
+			const uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
+			score += __popc(qp0 & v.x) + __popc(qp1 & v.y) + __popc(qn0 & v.z) + __popc(qn1 & v.w);
+			score -= __popc(qp0 & v.z) + __popc(qp1 & v.w) + __popc(qn0 & v.x) + __popc(qn1 & v.y);
 		}
 	}
 	float sim = (float)score;
 	float d = p.metric == LMD_METRIC_IP ? -sim : 1.0f - sim;
 	return d + 0.0f;
+}
+
+// ---- int8 edge codec (the L2-capable codec; libsql/lm_diskann.hpp:55-62 INT8) -------------
+// x ~ off[d] + scale * c[d]. The query is brought onto the same grid once per query: qi[d] = clamp(rint((q[d] - off[d]) /
+// scale)), kept as int8 in shared memory; a_sq = sum qi^2 (exact integer); e_q = || (q - off) - scale * qi || (fp32).
+// Then for a neighbour with codes c:  || q^ - x^ ||^2 = scale^2 * (a_sq - 2 * dot(qi, c) + csq)  - all integer, dp4a.
+__device__ __forceinline__ void encode_query_int8(const KParams &p, uint32_t qi, int lane, int8_t *s_qi8, int &a_sq,
+                                                  float &e_q) {
+	const float *src = p.queries + (uint64_t)qi * p.q_stride;
+	const float inv = 1.0f / p.code_scale;
+	int a = 0;
+	float e = 0.0f;
+	for (uint32_t f = lane; f < p.row_floats; f += 32) { // row_floats is a multiple of 32 >= dims: the tail encodes 0
+		int c = 0;
+		if (f < p.dims) {
+			const float v = __ldg(src + f) - __ldg(p.code_off + f);
+			c = __float2int_rn(v * inv);
+			c = c < -127 ? -127 : (c > 127 ? 127 : c);
+			const float r = v - p.code_scale * (float)c;
+			e = fmaf(r, r, e);
+		}
+		s_qi8[f] = (int8_t)c;
+		a += c * c;
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		a += __shfl_xor_sync(FULL, a, o);
+		e += __shfl_xor_sync(FULL, e, o);
+	}
+	a_sq = a;
+	e_q = sqrtf(e) * 1.0001f;
+	__syncwarp();
+}
+
+// dot(qi, c_j) over all dimensions for neighbour j of the expanded node: chunk w (16 dimensions) of neighbour j is the
+// 16-byte entry data[(w * R + j) * 16]; NCH = row_floats / 16 when the shape is specialised, 0 = runtime.
+template <int NCH>
+__device__ __forceinline__ int int8_dot(const KParams &p, const uint8_t *side_blk, uint32_t j, const int8_t *s_qi8) {
+	const uint4 *cp = reinterpret_cast<const uint4 *>(side_blk + p.side_data_off) + j;
+	const uint4 *qp = reinterpret_cast<const uint4 *>(s_qi8);
+	int dot = 0;
+	constexpr int GRP = 8; // 128 bytes of codes in flight per lane
+	const uint32_t nch = NCH > 0 ? (uint32_t)NCH : p.row_floats / 16;
+	for (uint32_t w0 = 0; w0 < nch; w0 += GRP) {
+		uint4 c[GRP];
+#pragma unroll
+		for (int g = 0; g < GRP; g++) {
+			c[g] = (w0 + g < nch) ? __ldg(cp + (w0 + g) * p.r) : make_uint4(0u, 0u, 0u, 0u);
+		}
+#pragma unroll
+		for (int g = 0; g < GRP; g++) {
+			if (w0 + g < nch) {
+				const uint4 q = qp[w0 + g];
+				dot = __dp4a((int)c[g].x, (int)q.x, dot);
+				dot = __dp4a((int)c[g].y, (int)q.y, dot);
+				dot = __dp4a((int)c[g].z, (int)q.z, dot);
+				dot = __dp4a((int)c[g].w, (int)q.w, dot);
+			}
+		}
+	}
+	return dot;
 }
 
 __device__ __forceinline__ bool slot_allowed(const KParams &p, uint32_t slot) {
@@ -664,6 +770,10 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 	float *s_q = reinterpret_cast<float *>(extra); // generic shape only
 	uint32_t *s_qp = reinterpret_cast<uint32_t *>(extra + (CH == 0 ? p.row_floats * 4 : 0));
 	uint32_t *s_qn = s_qp + p.words * 2;
+	int8_t *s_qi8 = reinterpret_cast<int8_t *>(s_qp); // int8 codec: the query on the code grid (row_floats bytes)
+	constexpr bool SIDE = ROUTE != LMD_ROUTE_EXACT;   // the expansion reads the node's routing sidecar block
+	constexpr bool CODES = ROUTE == LMD_ROUTE_INT8 || ROUTE == LMD_KROUTE_EXACT_PF;
+	constexpr bool GATHER = ROUTE == LMD_ROUTE_EXACT || ROUTE == LMD_KROUTE_EXACT_PF; // exact rows of the new neighbours
 	uint64_t *s_res = FILT ? reinterpret_cast<uint64_t *>(wbase + p.res_off) : s_list;
 	const int L = (int)p.L;
 	const int cap = (int)p.list_cap;
@@ -679,9 +789,11 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		if (qi >= p.nq) {
 			break;
 		}
-		uint32_t n_exp = 0, n_eval = 0, n_evict = 0, n_tie_ovf = 0, n_fallback = 0;
+		uint32_t n_exp = 0, n_eval = 0, n_evict = 0, n_tie_ovf = 0, n_fallback = 0, n_fetch = 0;
 		int n = 0;
 		int nres = 0;
+		int q_asq = 0;
+		float q_err = 0.0f;
 		{
 			const uint32_t fill = p.filter_mode ? 0u : FILTER_EMPTY;
 			uint4 e4 = make_uint4(fill, fill, fill, fill);
@@ -695,6 +807,9 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 		if (ROUTE == LMD_ROUTE_TERNARY) {
 			encode_query_planes(p, qi, lane, s_qp, s_qn);
 		}
+		if (CODES) {
+			encode_query_int8(p, qi, lane, s_qi8, q_asq, q_err);
+		}
 		__syncwarp();
 
 		if (p.has_entry) { // core/Searcher.cpp:70-103
@@ -703,7 +818,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				visited_test_and_set(p, s_filter, p.entry_slot, n_evict);
 			}
 			__syncwarp();
-			compute_batch<TEAM, CH, (ROUTE == LMD_ROUTE_TERNARY ? 1 : G), METRIC>(Q, p, s_nb, s_d, s_d2, 1, lane);
+			compute_batch<TEAM, CH, (GATHER ? G : 1), METRIC>(Q, p, s_nb, s_d, s_d2, 1, lane);
 			__syncwarp();
 			const float d0 = finish_batch<METRIC>(s_d, s_d2, Q.na, 1, lane);
 			if (lane == 0) {
@@ -711,6 +826,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 			}
 			n = 1;
 			n_eval = 1;
+			n_fetch = 1;
 			if (FILT && slot_allowed(p, p.entry_slot)) {
 				if (lane == 0) {
 					s_res[0] = make_key(d0, p.entry_slot);
@@ -733,20 +849,21 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 			}
 			__syncwarp();
 			n_exp++;
-			const uint32_t *nrow = p.nbrs + (uint64_t)cur * p.r;
-			const uint8_t *blk = p.blocks + (uint64_t)cur * p.block_bytes;
+			// SIDE: slots, (code norms,) planes / codes of the R neighbours sit in ONE contiguous sidecar block of the node
+			const uint8_t *side_blk = SIDE ? p.side + (uint64_t)cur * p.side_bytes : nullptr;
+			const uint32_t *nrow = SIDE ? reinterpret_cast<const uint32_t *>(side_blk) : p.nbrs + (uint64_t)cur * p.r;
 			uint32_t id_next = lane < p.r ? __ldg(nrow + lane) : LMD_INVALID_SLOT;
 			{
 				// the runner-up of the frontier is the most likely next expansion: pull its neighbour row into L2 now
 				const int idx2 = find_unexpanded<LPL>(s_list, n, lane);
-				if (idx2 >= 0 && (uint32_t)lane < nbr_lines) {
+				if (!SIDE && idx2 >= 0 && (uint32_t)lane < nbr_lines) {
 					const uint32_t *nx = p.nbrs + (uint64_t)key_slot(s_list[idx2]) * p.r + lane * 32;
 					asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
 				}
-				if (ROUTE == LMD_ROUTE_TERNARY && idx2 >= 0 && p.prefetch_planes) {
-					// ... and its block's plane region (positive planes, padding, negative planes: one span)
-					const uint8_t *b2 = p.blocks + (uint64_t)key_slot(s_list[idx2]) * p.block_bytes + (p.pos_off & ~127ull);
-					const uint32_t span = (uint32_t)(p.neg_off - (p.pos_off & ~127ull)) + p.r * p.words * 8;
+				if (SIDE && idx2 >= 0) {
+					// ... or its whole sidecar block (p.prefetch_planes = 0: only the slot row at its head)
+					const uint8_t *b2 = p.side + (uint64_t)key_slot(s_list[idx2]) * p.side_bytes;
+					const uint32_t span = p.prefetch_planes ? p.side_bytes : p.r * 4;
 					for (uint32_t o = lane * 128; o < span; o += 32 * 128) {
 						asm volatile("prefetch.global.L2 [%0];" ::"l"(b2 + o));
 					}
@@ -757,6 +874,16 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				const uint32_t id = id_next;
 				if (base + 32 < p.r) {
 					id_next = j + 32 < p.r ? __ldg(nrow + j + 32) : LMD_INVALID_SLOT;
+				}
+				// int8 codec: the code loads of neighbour j go out BEFORE the filter test (nothing depends on its outcome:
+				// the bytes are contiguous with those of the other lanes), the integer dot product is ready when it ends
+				int c_dot = 0;
+				uint32_t c_sq = 0;
+				float c_err = 0.0f;
+				if (CODES && id != LMD_INVALID_SLOT) {
+					c_sq = __ldg(nrow + p.r + j);
+					c_err = __uint_as_float(__ldg(nrow + 2 * p.r + j));
+					c_dot = int8_dot<(CH > 0 ? CH * TEAM / 4 : 0)>(p, side_blk, j, s_qi8);
 				}
 				bool isnew = false;
 				// The entry point is the one node whose list key does not come from this loop (its distance is always
@@ -774,7 +901,32 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 				float d = 0.0f;
 				uint32_t myid = id;
 				bool have = isnew;
-				if (ROUTE == LMD_ROUTE_EXACT) {
+				uint32_t gmask = mask; // neighbours whose exact row is gathered
+				int gm = m;
+				if (CODES) {
+					// || q^ - x^ || on the code grid: integers all the way to the square root
+					const int i2 = q_asq - 2 * c_dot + (int)c_sq;
+					d = p.code_scale * sqrtf((float)(i2 > 0 ? i2 : 0)) + 0.0f;
+					if (ROUTE == LMD_KROUTE_EXACT_PF) {
+						// d(q, x) >= || q^ - x^ || - || q - q^ || - || x - x^ ||: a neighbour whose lower bound is already
+						// beyond the list's worst would be turned away by core/Searcher.cpp:175 whatever its exact
+						// distance is - its row need not be read. The 5e-4 margin covers every fp32 rounding involved
+						// (the kernel's own distance sum is within D * 2^-24 relative of the true one); the threshold can
+						// only shrink while the batch is admitted, so testing against its value now is conservative.
+						const float worst0 = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
+						const bool skip = n >= L && d > (worst0 + q_err + c_err) * 1.0005f;
+						gmask = __ballot_sync(FULL, isnew && !skip);
+						gm = __popc(gmask);
+						if (gm == 0) {
+							continue;
+						}
+						isnew = isnew && !skip;
+					}
+				}
+				if (GATHER) {
+					const int m = gm; // shadows the discovered count: rows actually fetched
+					const uint32_t mask = gmask;
+					n_fetch += m;
 					const int pos = __popc(mask & ((1u << lane) - 1u));
 					if (isnew) {
 						s_nb[pos] = id;
@@ -789,9 +941,9 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 						myid = s_nb[lane];
 					}
 					__syncwarp();
-				} else {
+				} else if (ROUTE == LMD_ROUTE_TERNARY) {
 					if (isnew) {
-						d = ternary_distance<(CH > 0 && ROUTE == LMD_ROUTE_TERNARY ? (CH * TEAM * 4 + 63) / 64 : 0)>(p, blk, j, s_qp, s_qn);
+						d = ternary_distance<(CH > 0 && ROUTE == LMD_ROUTE_TERNARY ? (CH * TEAM * 4 + 63) / 64 : 0)>(p, side_blk, j, s_qp, s_qn);
 					}
 				}
 				if (FILT) {
@@ -893,6 +1045,7 @@ __global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
 			}
 			atomicAdd(&p.counters[1], (unsigned long long)n_exp);
 			atomicAdd(&p.counters[2], (unsigned long long)n_eval);
+			atomicAdd(&p.counters[7], (unsigned long long)n_fetch);
 			if (n_evict) {
 				atomicAdd(&p.counters[3], (unsigned long long)n_evict);
 			}
@@ -1007,6 +1160,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	const bool spread = s->tune.warps_per_cta == 0 && nq <= (uint32_t)s->sm_count * 4;
 	const uint64_t cache_key = (uint64_t)(uintptr_t)kernel * 0x9E3779B97F4A7C15ull + p.warp_smem_bytes * 2ull + (spread ? 1 : 0);
 	int best_w = 0, best_ctas = 0;
+	std::lock_guard<std::mutex> cache_guard(s->cache_mu);
 	auto hit = s->launch_cache.find(cache_key);
 	if (hit != s->launch_cache.end()) {
 		best_w = hit->second.first;
@@ -1088,7 +1242,9 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	}
 
 #define LMD_DISPATCH_SHAPE_COARSE(KERNEL, METRIC, ...)                                                                 \
-	if (p.row_floats == 128) {                                                                                         \
+	if (p.strict) {                                                                                                    \
+		LMD_DISPATCH_LPL_COARSE(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                               \
+	} else if (p.row_floats == 128) {                                                                                         \
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 4, 2, METRIC, ##__VA_ARGS__)                                                \
 	} else if (p.row_floats == 96) {                                                                                   \
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                \
@@ -1126,7 +1282,9 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	}
 
 #define LMD_DISPATCH_SHAPE(KERNEL, METRIC, ...)                                                                        \
-	if (p.row_floats == 128) {                                                                                         \
+	if (p.strict) {                                                                                                    \
+		LMD_DISPATCH_LPL(KERNEL, 32, 0, 1, METRIC, ##__VA_ARGS__)                                                      \
+	} else if (p.row_floats == 128) {                                                                                         \
 		LMD_DISPATCH_LPL(KERNEL, 8, 4, 2, METRIC, ##__VA_ARGS__)                                                       \
 	} else if (p.row_floats == 96) {                                                                                   \
 		LMD_DISPATCH_LPL(KERNEL, 8, 3, 2, METRIC, ##__VA_ARGS__)                                                       \

@@ -60,6 +60,8 @@ LMD_DECL_TRAVERSE(2, 0)
 LMD_DECL_TRAVERSE(3, 0)
 LMD_DECL_TRAVERSE(2, 1)
 LMD_DECL_TRAVERSE(3, 1)
+LMD_DECL_TRAVERSE(1, 2) // int8 routing (L2)
+LMD_DECL_TRAVERSE(1, 3) // exact routing with the int8 pre-filter (L2)
 #define LMD_DECL_TRAVERSE_FILT(M, R)                                                                                   \
 	lmd_status dispatch_traverse_filt_m##M##_r##R(KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st);
 LMD_DECL_TRAVERSE_FILT(1, 0)
@@ -130,6 +132,12 @@ static lmd_status dispatch_traverse(KParams &p, const lmd_store *s, uint32_t nq,
 		set_error("no filtered traversal kernel for this configuration (L=%u)", p.L);
 		return LMD_ERR_UNSUPPORTED;
 	}
+	if (route == LMD_ROUTE_INT8) {
+		return dispatch_traverse_m1_r2(p, s, nq, lpl, st);
+	}
+	if (route == LMD_KROUTE_EXACT_PF) {
+		return dispatch_traverse_m1_r3(p, s, nq, lpl, st);
+	}
 	if (route == LMD_ROUTE_EXACT && p.latency == 2) {
 		switch (p.metric) {
 		case LMD_METRIC_L2:
@@ -195,9 +203,30 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	if (a.q_stride) {
 		p.q_stride = a.q_stride;
 	}
+	p.strict = (a.strict || s->tune.strict_fp) ? 1u : 0u;
+	if (a.d_counters) {
+		p.counters = a.d_counters;
+	}
 	// room behind the top L for distance ties (see list_insert): integer ternary distances tie all the time, fp32
 	// distances only for duplicate vectors
-	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots : (a.route == LMD_ROUTE_TERNARY ? 64u : 0u);
+	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots : (a.route != LMD_ROUTE_EXACT ? 64u : 0u);
+	// exact routing on a store with the int8 codec: the codes decide which rows are fetched (same results, fewer bytes)
+	uint32_t kroute = a.route;
+	if (a.route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && s->codes_gen == s->views_gen && !a.no_prefilter &&
+	    !a.d_allowed && !p.strict && s->tune.prefilter && s->cfg.metric == LMD_METRIC_L2) {
+		kroute = LMD_KROUTE_EXACT_PF;
+	}
+	if (a.route == LMD_ROUTE_TERNARY) {
+		p.side = s->d_side_t;
+		p.side_bytes = s->side_t_bytes;
+		p.side_data_off = s->side_t_off;
+	} else if (kroute != LMD_ROUTE_EXACT) {
+		p.side = s->d_codes;
+		p.side_bytes = s->code_block_bytes;
+		p.side_data_off = s->code_data_off;
+		p.code_off = s->d_code_off;
+		p.code_scale = s->code_scale;
+	}
 	int lpl = lpl_for(a.L + tie_slots);
 	if (!lpl) {
 		lpl = lpl_for(a.L);
@@ -207,9 +236,9 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 		return LMD_ERR_UNSUPPORTED;
 	}
 	// small batches: the latency variants (all of an expansion's gathers in flight at once), see lmd_kernels.cuh
-	const bool specialised = p.row_floats == 128 || p.row_floats == 96; // 768-d rows already run with G = 6
+	const bool specialised = !p.strict && (p.row_floats == 128 || p.row_floats == 96); // 768-d rows already run with G = 6
 	const int lat = s->tune.latency_mode;
-	if (a.route == LMD_ROUTE_EXACT && !a.d_allowed && specialised) {
+	if (kroute == LMD_ROUTE_EXACT && !a.d_allowed && specialised) {
 		// latency_mode: -1 = by batch size, 0 = throughput kernels only, 1 = G = 8 kernels, 2 = G = 4 kernels
 		p.latency = (uint32_t)plan_family(a.nq, (uint32_t)s->sm_count, lat);
 		if (p.latency) {
@@ -223,9 +252,10 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.list_cap = (uint32_t)lpl * 32;
 	p.merge_min = (uint32_t)(s->tune.merge_min > 0 ? s->tune.merge_min : 5);
 	p.prefetch_planes = s->tune.prefetch_planes ? 1u : 0u;
-	const bool generic = !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
+	const bool generic = p.strict || !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	size_t fixed = (size_t)lpl * 32 * 8 + 384 + (generic ? (size_t)p.row_floats * 4 : 0) +
-	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0);
+	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0) +
+	               (kroute == LMD_ROUTE_INT8 || kroute == LMD_KROUTE_EXACT_PF ? (size_t)p.row_floats : 0);
 	const size_t res_bytes = a.d_allowed ? (size_t)lpl * 32 * 8 : 0; // the results list RH of a filtered search
 	fixed += res_bytes;
 	// The 128-d / 96-d exact kernels keep 2 rows in flight per team and need 24 warps on an SM to cover HBM latency: a
@@ -238,11 +268,11 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// Small batches run 12 (G = 8) or 16 (G = 4) warps per SM at most, which leaves room for the filter that never forgets:
 	// 1 M x 128, L = 128, 16 KB against 4 KB: 1 query 383 -> 348 us, 1 024 queries 564 -> 524 us
 	// (profiles/r50_small_batch_L128.json).
-	const bool exact = a.route == LMD_ROUTE_EXACT;
+	const bool exact = a.route == LMD_ROUTE_EXACT; // (with or without the pre-filter: rows are gathered either way)
 	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl);
-	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, !exact, min_warps, s->tune.filter_mode,
+	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps, s->tune.filter_mode,
 	                                  (int)s->tune.filter_log2);
-	if (plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
+	if (kroute == LMD_ROUTE_EXACT && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
 		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
 		// (10 M x 96, L = 48 / 128: 1.46 -> 1.37 / 3.53 -> 3.34 ms per 12.5 k queries; 1 M x 96, L = 64: 1.21 -> 1.13;
 		// profiles/r43_g_sweep_*.json; those kernels exist for lists of 64 and 128 entries, not 96). With the 4 KB filter
@@ -257,7 +287,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.filter_hmask = (uint32_t)((1ull << (fp.lg - 3 + 15)) - 1);
 	p.res_off = (uint32_t)((fixed - res_bytes + fp.bytes + 15) / 16 * 16);
 	p.warp_smem_bytes = (uint32_t)(p.res_off + (res_bytes + 15) / 16 * 16);
-	return dispatch_traverse(p, s, a.nq, lpl, a.route, st);
+	return dispatch_traverse(p, s, a.nq, lpl, kroute, st);
 }
 
 lmd_status launch_rerank(const RerankArgs &a, cudaStream_t st) {
@@ -267,12 +297,16 @@ lmd_status launch_rerank(const RerankArgs &a, cudaStream_t st) {
 	p.out_dist = a.d_out_dist;
 	p.out_count = a.d_out_count;
 	p.cand = const_cast<uint64_t *>(a.d_cand);
+	p.strict = (a.strict || s->tune.strict_fp) ? 1u : 0u;
+	if (a.d_counters) {
+		p.counters = a.d_counters;
+	}
 	const int lpl = lpl_for(a.L);
 	if (!lpl) {
 		set_error("search list size L = %u exceeds this build's limit of 512", a.L);
 		return LMD_ERR_UNSUPPORTED;
 	}
-	const bool generic = !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
+	const bool generic = p.strict || !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	p.warp_smem_bytes = (uint32_t)(384 + (generic ? (size_t)p.row_floats * 4 : 0));
 	return dispatch_rerank(p, s, a.nq, lpl, st);
 }

@@ -307,6 +307,58 @@ static lmd_status lookup_slot(lmd_store *s, int64_t row_id, uint32_t *slot) {
 
 using namespace lmd;
 
+namespace lmd {
+
+lmd_status state_init(SearchState &st) {
+	LMD_CUDA_OK(cudaMalloc((void **)&st.d_counters, 16 * sizeof(unsigned long long)));
+	LMD_CUDA_OK(cudaStreamCreateWithFlags(&st.own_stream, cudaStreamNonBlocking));
+	st.stream = st.own_stream;
+	for (auto &e : st.ev) {
+		LMD_CUDA_OK(cudaEventCreate(&e));
+	}
+	LMD_CUDA_OK(cudaMemsetAsync(st.d_counters, 0, 128, st.stream));
+	return LMD_OK;
+}
+
+void state_free(SearchState &st) {
+	if (st.stream) {
+		cudaStreamSynchronize(st.stream);
+	}
+	cudaFree(st.d_counters);
+	cudaFree(st.d_q);
+	cudaFree(st.d_out_ids);
+	cudaFree(st.d_out_dist);
+	cudaFree(st.d_out_count);
+	cudaFree(st.d_qstats);
+	cudaFree(st.d_cand);
+	if (st.h_pin) {
+		cudaFreeHost(st.h_pin);
+	}
+	for (auto &e : st.ev) {
+		if (e) {
+			cudaEventDestroy(e);
+		}
+	}
+	if (st.own_stream) {
+		cudaStreamDestroy(st.own_stream);
+	}
+	st.stream = st.own_stream = nullptr;
+	st.d_counters = nullptr;
+	st.d_q = nullptr;
+	st.d_out_ids = nullptr;
+	st.d_out_dist = nullptr;
+	st.d_out_count = nullptr;
+	st.d_qstats = nullptr;
+	st.d_cand = nullptr;
+	st.h_pin = nullptr;
+	for (auto &e : st.ev) {
+		e = nullptr;
+	}
+	st.scratch_q = st.scratch_k = st.scratch_qs = st.scratch_cnt = st.scratch_cand = 0;
+}
+
+} // namespace lmd
+
 extern "C" {
 
 const char *lmd_last_error(void) {
@@ -433,19 +485,13 @@ lmd_status lmd_store_create(const lmd_config *cfg, int device, uint64_t capacity
 	LMD_ALLOC(s->d_row_ids, capacity_nodes * sizeof(int64_t));
 	LMD_ALLOC(s->d_map_keys, s->map_cap * sizeof(int64_t));
 	LMD_ALLOC(s->d_map_vals, s->map_cap * sizeof(uint32_t));
-	LMD_ALLOC(s->d_counters, 16 * sizeof(unsigned long long));
 #undef LMD_ALLOC
-	if (cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
-	    cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+	if ((st = state_init(s->def)) != LMD_OK) {
+		return fail(st);
+	}
+	if (cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
 		set_error("cudaStreamCreate failed");
 		return fail(LMD_ERR_CUDA);
-	}
-	s->stream = s->own_stream;
-	for (auto &e : s->ev) {
-		if (cudaEventCreate(&e) != cudaSuccess) {
-			set_error("cudaEventCreate failed");
-			return fail(LMD_ERR_CUDA);
-		}
 	}
 	cudaGetLastError(); // start from a clean error state
 	fill_i64_kernel<<<(unsigned)((s->map_cap + 255) / 256), 256, 0, s->stream>>>((long long *)s->d_map_keys, s->map_cap,
@@ -474,13 +520,6 @@ lmd_status lmd_store_destroy(lmd_store *s) {
 	cudaFree(s->d_row_ids);
 	cudaFree(s->d_map_keys);
 	cudaFree(s->d_map_vals);
-	cudaFree(s->d_counters);
-	cudaFree(s->d_q);
-	cudaFree(s->d_out_ids);
-	cudaFree(s->d_out_dist);
-	cudaFree(s->d_out_count);
-	cudaFree(s->d_qstats);
-	cudaFree(s->d_cand);
 	cudaFree(s->d_apply);
 	cudaFree(s->d_apply_rids);
 	cudaFree(s->d_apply_slots);
@@ -488,17 +527,13 @@ lmd_status lmd_store_destroy(lmd_store *s) {
 	cudaFree(s->d_inbox_cnt);
 	cudaFree(s->d_touched);
 	cudaFree(s->d_planes);
+	cudaFree(s->d_side_t);
+	cudaFree(s->d_codes);
+	cudaFree(s->d_code_off);
 	if (s->h_stage) {
 		cudaFreeHost(s->h_stage);
 	}
-	for (auto &e : s->ev) {
-		if (e) {
-			cudaEventDestroy(e);
-		}
-	}
-	if (s->own_stream) {
-		cudaStreamDestroy(s->own_stream);
-	}
+	state_free(s->def);
 	if (s->copy_stream) {
 		cudaStreamDestroy(s->copy_stream);
 	}
@@ -511,7 +546,7 @@ lmd_status lmd_store_set_stream(lmd_store *s, void *cuda_stream) {
 		set_error("lmd_store_set_stream: null store");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	LMD_CUDA_OK(cudaStreamSynchronize(s->stream)); // nothing of ours may still be running on the old stream
 	s->stream = cuda_stream ? (cudaStream_t)cuda_stream : s->own_stream;
@@ -612,6 +647,7 @@ lmd_status store_ingest(lmd_store *s, const int64_t *row_ids, uint64_t base, uin
 	s->n += n;
 	s->epoch++;
 	s->dirty = true;
+	s->views_gen++;
 	if (s->entry_row != INT64_MAX && !s->has_entry) {
 		// an entry row id set before its block arrived resolves now
 		uint32_t slot;
@@ -641,7 +677,11 @@ lmd_status lmd_store_upload(lmd_store *s, const int64_t *row_ids, const void *bl
 	if (n == 0) {
 		return LMD_OK;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_store_upload: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	if (s->n + n > s->capacity) {
 		set_error("lmd_store_upload: %llu + %llu nodes exceed the store capacity %llu", (unsigned long long)s->n,
 		          (unsigned long long)n, (unsigned long long)s->capacity);
@@ -662,7 +702,11 @@ lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block) {
 		set_error("lmd_store_update: null argument");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_store_update: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	uint32_t slot;
 	lmd_status st = lookup_slot(s, row_id, &slot);
@@ -687,6 +731,7 @@ lmd_status lmd_store_update(lmd_store *s, int64_t row_id, const void *block) {
 	    (const long long *)s->d_map_keys, s->d_map_vals, s->map_cap - 1, s->d_nbrs + (uint64_t)slot * s->cfg.r);
 	LMD_CUDA_OK(cudaGetLastError());
 	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
+	s->views_gen++;
 	return LMD_OK;
 }
 
@@ -709,7 +754,11 @@ lmd_status lmd_store_apply(lmd_store *s, const int64_t *row_ids, const void *blo
 		set_error("lmd_store_apply: row_ids must be host memory");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_store_apply: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	const uint64_t bb = s->cfg.block_bytes;
 	const uint64_t chunk = 16384; // blocks staged per pass (64 MiB at 4 KiB blocks)
@@ -785,6 +834,7 @@ lmd_status lmd_store_apply(lmd_store *s, const int64_t *row_ids, const void *blo
 	}
 	// 3. stage + scatter the blocks, refresh the views of the overwritten slots
 	const bool rebuild_all = s->dirty || !new_rids.empty(); // a new row id may resolve ids other blocks already hold
+	s->views_gen++;
 	for (uint64_t first = 0; first < n; first += s->apply_cap) {
 		const uint64_t now = n - first < s->apply_cap ? n - first : s->apply_cap;
 		lmd_status st = copy_to_device(s, s->d_apply, (const uint8_t *)blocks + first * bb, now * bb);
@@ -834,7 +884,7 @@ lmd_status lmd_store_remove(lmd_store *s, const int64_t *row_ids, uint64_t n, ui
 		set_error("lmd_store_remove: row_ids must be host memory");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	int64_t *d_rids = nullptr;
 	LMD_CUDA_OK(cudaMalloc((void **)&d_rids, n * sizeof(int64_t)));
@@ -862,6 +912,7 @@ lmd_status lmd_store_remove(lmd_store *s, const int64_t *row_ids, uint64_t n, ui
 		s->epoch++;
 		s->identity = false; // slot numbers no longer stand for row ids: resolve through the map
 		s->dirty = true;     // neighbour rows that point at the removed slots are rebuilt before the next search
+		s->views_gen++;
 	}
 	for (uint64_t i = 0; i < n; i++) {
 		if (row_ids[i] == s->entry_row) { // GraphManager.cpp:477-480
@@ -884,7 +935,7 @@ lmd_status lmd_filter_create(lmd_store *s, const int64_t *allowed_row_ids, uint6
 		return LMD_ERR_INVALID_ARG;
 	}
 	*out = nullptr;
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	lmd_filter *f = new (std::nothrow) lmd_filter();
 	if (!f) {
@@ -961,7 +1012,7 @@ lmd_status lmd_store_set_entry(lmd_store *s, int64_t row_id) {
 		set_error("lmd_store_set_entry: null store");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	s->entry_row = row_id;
 	s->has_entry = false;
@@ -984,7 +1035,13 @@ lmd_status lmd_store_finalize(lmd_store *s) {
 		set_error("lmd_store_finalize: null store");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	return lmd::finalize_locked(s);
+}
+
+} // extern "C"
+
+lmd_status lmd::finalize_locked(lmd_store *s) {
 	if (!s->dirty || s->n == 0) {
 		s->dirty = false;
 		return LMD_OK;
@@ -997,15 +1054,22 @@ lmd_status lmd_store_finalize(lmd_store *s) {
 	LMD_CUDA_OK(cudaGetLastError());
 	LMD_CUDA_OK(cudaStreamSynchronize(s->stream));
 	s->dirty = false;
+	s->views_gen++;
 	return LMD_OK;
 }
+
+extern "C" {
 
 lmd_status lmd_store_download_block(lmd_store *s, int64_t row_id, void *out_block) {
 	if (!s || !out_block) {
 		set_error("lmd_store_download_block: null argument");
 		return LMD_ERR_INVALID_ARG;
 	}
-	std::lock_guard<std::mutex> g(s->mu);
+	std::unique_lock<std::shared_mutex> g(s->mu);
+	if (s->blocks_released) {
+		set_error("lmd_store_download_block: the block mirror of this store was released (lmd_store_release_blocks)");
+		return LMD_ERR_STATE;
+	}
 	LMD_CUDA_OK(cudaSetDevice(s->device));
 	uint32_t slot;
 	lmd_status st = lookup_slot(s, row_id, &slot);
@@ -1028,6 +1092,7 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		return LMD_ERR_INVALID_ARG;
 	}
 	std::string k(key);
+	std::unique_lock<std::shared_mutex> g(s->mu); // searches read the tuning and the launch cache under the same lock
 	s->launch_cache.clear();
 	if (k == "filter_log2") {
 		s->tune.filter_log2 = (int)value;
@@ -1045,6 +1110,15 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		s->tune.tie_slots = (int)value;
 	} else if (k == "merge_min") {
 		s->tune.merge_min = (int)value;
+	} else if (k == "strict_fp") {
+		s->tune.strict_fp = value ? 1 : 0;
+	} else if (k == "code_sigmas") {
+		s->tune.code_sigmas = (int)value;
+		s->codes_gen = 0; // the grid changes: rebuild before the next search that uses it
+	} else if (k == "plane_filter_cap") {
+		s->tune.plane_filter_cap = value ? 1 : 0;
+	} else if (k == "prefilter") {
+		s->tune.prefilter = value ? 1 : 0;
 	} else {
 		set_error("lmd_set_tuning: unknown key %s", key);
 		return LMD_ERR_INVALID_ARG;

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define LMD_ABI_VERSION 1
+#define LMD_ABI_VERSION 2
 
 typedef int32_t lmd_status;
 enum {
@@ -39,15 +39,31 @@ enum { LMD_VEC_FLOAT32 = 1, LMD_VEC_INT8 = 2 };
 /* Routing distance used while traversing.
  * EXACT   = what core/Searcher.cpp:145-173 executes today: exact fp32 distance to each neighbour's own vector.
  * TERNARY = the designed LM-DiskANN mode (Searcher.cpp:168-171 TODO): ternary planes of the neighbours held in
- *           the EXPANDED block (core/distance.hpp:212-243), exact rerank afterwards. COSINE / IP only. */
-enum { LMD_ROUTE_EXACT = 0, LMD_ROUTE_TERNARY = 1 };
+ *           the EXPANDED block (core/distance.hpp:212-243), exact rerank afterwards. COSINE / IP only.
+ * INT8    = the L2-capable edge codec the libSQL original declares (libsql/lm_diskann.hpp:55-62 LmDiskannEdgeType INT8;
+ *           routing loop libsql/lm_diskann.cpp:1596-1625): every neighbour's vector as int8 codes on one global grid
+ *           (per-dimension offset, one scale), held in a device sidecar shaped like the block's plane region; routing
+ *           distance = || q^ - x^ || by integer dot products, exact rerank afterwards. L2 only. No reference code
+ *           executes it: PARITY UNPINNED (checked against oracle/lmd_oracle.c's restatement only). */
+enum { LMD_ROUTE_EXACT = 0, LMD_ROUTE_TERNARY = 1, LMD_ROUTE_INT8 = 2 };
+enum { LMD_CODEC_NONE = 0, LMD_CODEC_INT8 = 1 };
 
 /* lmd_search_batch flags */
 enum {
 	LMD_SEARCH_SEPARATE_RERANK = 1u << 0, /* run the rerank kernel even when traversal distances are already exact */
 	LMD_SEARCH_PER_QUERY_STATS = 1u << 1, /* fill out_qstats */
-	LMD_SEARCH_ASYNC = 1u << 2            /* device-resident or pinned buffers only: enqueue on the store's stream and
+	LMD_SEARCH_ASYNC = 1u << 2,           /* device-resident or pinned buffers only: enqueue on the store's stream and
 	                                         return without synchronising; `stats` must be NULL */
+	LMD_SEARCH_STRICT_FP = 1u << 3,       /* parity tool, never the timed path: every exact distance is accumulated in the
+	                                         reference's own order - one lane per row, element by element, multiply then
+	                                         add, no FMA (core/distance.hpp:56-99) - so that the traversal takes the
+	                                         reference's decisions bit for bit (ids, distances, expansion counts). Also
+	                                         lmd_set_tuning(s, "strict_fp", 1) for lmd_robust_prune_batch / lmd_build_graph */
+	LMD_SEARCH_NO_PREFILTER = 1u << 4,    /* exact routing on a store with the int8 codec enabled: fetch every new
+	                                         neighbour's row (the plain traversal) instead of letting the int8 lower
+	                                         bound skip rows that cannot enter the list. Same results either way. */
+	LMD_SEARCH_TENSOR_RERANK = 1u << 5    /* run the separate rerank as the tcgen05 (3xTF32) contraction staged through
+	                                         bulk async copies instead of the FMA gather kernel (implies SEPARATE_RERANK) */
 };
 
 #define LMD_EMPTY_ROW_ID INT64_MAX /* empty neighbour slot, core/GraphManager.cpp:154-156,451-453 */
@@ -83,6 +99,8 @@ typedef struct {
 	uint64_t tie_overflows;   /* tied frontier entries dropped because the tie region was full (0 = oracle-exact ties) */
 	uint64_t merge_fallbacks; /* candidate batches replayed one by one because of a distance tie (statistics) */
 	uint64_t algorithmic_bytes; /* SURVEY.md section 8d formula for this call */
+	uint64_t exact_fetches;   /* node vectors actually gathered by the traversal (== distance_evals unless the int8
+	                             pre-filter skipped rows; ternary / int8 routing: the entry point only) */
 	float traverse_ms;        /* CUDA-event time of the traversal kernel */
 	float rerank_ms;          /* CUDA-event time of the rerank kernel (0 when fused away) */
 	float h2d_ms, d2h_ms;     /* copies done by the call (0 for device-resident buffers) */
@@ -92,6 +110,8 @@ typedef struct {
 } lmd_stats;
 
 typedef struct lmd_store lmd_store;
+typedef struct lmd_ctx lmd_ctx;     /* a per-caller search context, see lmd_ctx_create */
+typedef struct lmd_group lmd_group; /* several stores on several devices searched as one, see lmd_group_create */
 
 /* --- layout (core/index_config.cpp:104-148 CalculateLayoutInternal; host code, no device needed) --- */
 lmd_status lmd_layout_calc(uint64_t dims, uint32_t vec_type, uint32_t r, lmd_layout *out);
@@ -130,6 +150,18 @@ lmd_status lmd_store_download_block(lmd_store *s, int64_t row_id, void *out_bloc
 /* Runs all later work of this store on the caller's CUDA stream (a cudaStream_t passed as void*; NULL = back to
  * the store's own stream). Lets a host with its own streams / events order and time the searches. */
 lmd_status lmd_store_set_stream(lmd_store *s, void *cuda_stream);
+/* int8 edge codec (row f4). Builds (and from then on keeps up to date, lazily, before the next search that needs it)
+ * the code sidecar: 12 R + R * dims bytes per node. With it, LMD_ROUTE_INT8 searches work, and LMD_ROUTE_EXACT searches
+ * of an L2 store use the codes as a LOWER BOUND that decides which neighbours' vectors are fetched at all - results,
+ * distances and expansion counts stay bit-identical to the plain traversal (see LMD_SEARCH_NO_PREFILTER). */
+lmd_status lmd_store_enable_codec(lmd_store *s, uint32_t codec);
+/* The codec's grid: offsets [dims] (host buffer) and the scale; x ~ offsets[d] + scale * code[d]. LMD_ERR_STATE while no
+ * codec is built. */
+lmd_status lmd_store_get_codec(lmd_store *s, float *out_offsets, float *out_scale);
+/* Frees the raw block mirror of a store that will only be searched (the search kernels read the derived views and
+ * sidecars, never the blocks). Builds every view first. Afterwards upload / update / apply / download / build return
+ * LMD_ERR_STATE; lmd_store_device_bytes reflects the release. */
+lmd_status lmd_store_release_blocks(lmd_store *s);
 uint64_t lmd_store_node_count(const lmd_store *s);
 uint64_t lmd_store_device_bytes(const lmd_store *s); /* core/ISearcher.hpp:43 GetInMemorySize */
 
@@ -142,10 +174,28 @@ uint64_t lmd_store_device_bytes(const lmd_store *s); /* core/ISearcher.hpp:43 Ge
  *          NULL); out_count [nq] (may be NULL). Device, pinned host (written in place) or pageable host memory; the
  *          outputs must all be pageable or all be device / pinned.
  * out_qstats [nq][2] = {expansions, distance evals} when LMD_SEARCH_PER_QUERY_STATS (may be NULL).
- * Thread-safety: concurrent searches on one store are serialised internally; uploads must not overlap searches. */
+ * Thread-safety: lmd_search_batch calls on one store are serialised on the store's own context; use one lmd_ctx per
+ * host thread for searches that run side by side. Searches hold the store shared, uploads / apply / remove / build
+ * exclusively, so either may be called at any time.
+ * Stream ordering: a call reads `queries` on the store's (or context's) stream. Device-resident queries produced on
+ * ANOTHER stream must be complete (or that stream bound with lmd_store_set_stream / lmd_ctx_set_stream) before the call.
+ * Tie order: equal distances are ordered by slot (= arrival order of the row in the store; = row id while row ids are
+ * slot numbers), which is the (distance, id) order of oracle hunk H4 for identity row ids only. */
 lmd_status lmd_search_batch(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
                             uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
                             uint32_t *out_qstats, lmd_stats *stats);
+
+/* --- per-caller search contexts: the reference's Search takes no lock (db/LmDiskannIndex.cpp:677-724 ->
+ *     core/Coordinator.cpp:63-102) and DuckDB runs scans from many threads. A context owns a stream, statistics
+ *     counters, staging scratch and a small pinned block on the store's device; searches on different contexts of one
+ *     store run concurrently on the GPU. `filter` may be NULL. Same arguments and semantics as lmd_search_batch. --- */
+lmd_status lmd_ctx_create(lmd_store *s, lmd_ctx **out);
+lmd_status lmd_ctx_destroy(lmd_ctx *c);
+lmd_status lmd_ctx_set_stream(lmd_ctx *c, void *cuda_stream);
+struct lmd_filter;
+lmd_status lmd_ctx_search_batch(lmd_ctx *c, const struct lmd_filter *filter, const float *queries, uint64_t nq,
+                                uint32_t k, uint32_t L, uint32_t route, uint32_t flags, int64_t *out_ids,
+                                float *out_dist, uint32_t *out_count, uint32_t *out_qstats, lmd_stats *stats);
 
 /* --- filtered search ---
  * The reference's plan ("Consolidated Diskann Proposal v1", section "Filtered Searches"; stubs in

@@ -339,7 +339,24 @@ typedef struct {
 	uint32_t r, cfg_l_search;
 	lmdo_layout lay;
 	const uint8_t *allowed; /* filtered search (row f4): one byte per block position, NULL = unfiltered */
+	const float *code_off;  /* int8 edge codec (row f4, PARITY UNPINNED): x ~ code_off[d] + code_scale * c[d] */
+	float code_scale;
 } index_t;
+
+/* The int8 edge codec's grid (per-dimension offsets + one scale). The CUDA path derives it from the data
+ * (csrc/lmd_sidecar.cu code_params_kernel); the tests download it with lmd_store_get_codec and hand it over here so
+ * that both sides quantise on the same grid. Process-global: set before lmdo_search(route = LMDO_ROUTE_INT8). */
+static const float *g_code_off = NULL;
+static float g_code_scale = 1.0f;
+void lmdo_set_codec(const float *off, float scale) {
+	g_code_off = off;
+	g_code_scale = scale;
+}
+
+static int code_of(float x, float off, float inv) {
+	long c = lrintf((x - off) * inv); /* round to nearest even, as __float2int_rn */
+	return c < -127 ? -127 : (c > 127 ? 127 : (int)c);
+}
 
 /* GraphManager.cpp:523-531 (TryGetNodePointer) over the harness' row_id -> slot mapping */
 static int try_get_slot(const index_t *ix, int64_t row, uint64_t *slot) {
@@ -358,6 +375,8 @@ typedef struct {
 	i64map_t visited;
 	float *tmp;
 	uint64_t *qplanes;
+	int8_t *qcodes; /* int8 codec: the query on the code grid */
+	int q_asq;      /* sum of qcodes^2 */
 	uint64_t expansions, fetches;
 } scratch_t;
 
@@ -414,6 +433,15 @@ static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uin
 		/* the reference re-encodes the query per neighbour (distance.hpp:137-140); same bits, once */
 		lmdo_encode_ternary(q, ix->dims, s->qplanes, s->qplanes + words);
 	}
+	if (ix->route == LMDO_ROUTE_INT8) {
+		const float inv = 1.0f / ix->code_scale;
+		s->q_asq = 0;
+		for (uint64_t i = 0; i < ix->dims; i++) {
+			int c = code_of(q[i], ix->code_off[i], inv);
+			s->qcodes[i] = (int8_t)c;
+			s->q_asq += c * c;
+		}
+	}
 
 	while (s->beam.n) { /* :108 */
 		cand_t cur = heap_pop(&s->beam);
@@ -447,6 +475,19 @@ static uint64_t search_core(const index_t *ix, scratch_t *s, const float *q, uin
 			float d;
 			if (ix->route == LMDO_ROUTE_EXACT) {
 				d = exact_to_slot(ix, s, q, nb_slot); /* :153-173 */
+			} else if (ix->route == LMDO_ROUTE_INT8) {
+				/* libsql/lm_diskann.cpp:1596-1625 with LmDiskannEdgeType INT8: the compressed copy of neighbour i is its
+				 * vector on the codec grid; routing distance = || q^ - x^ ||, integers up to the square root */
+				const float inv = 1.0f / ix->code_scale;
+				lmdo_convert_raw(block_of(ix, nb_slot) + ix->lay.vector_off, s->tmp, ix->dims, ix->vec_type);
+				int dot = 0, csq = 0;
+				for (uint64_t t = 0; t < ix->dims; t++) {
+					int c = code_of(s->tmp[t], ix->code_off[t], inv);
+					dot += c * (int)s->qcodes[t];
+					csq += c * c;
+				}
+				int i2 = s->q_asq - 2 * dot + csq;
+				d = ix->code_scale * sqrtf((float)(i2 > 0 ? i2 : 0)) + 0.0f;
 			} else {
 				/* the TODO at :168-171: compressed copy of neighbour i held in the EXPANDED block,
 				 * SoA planes of index_config.cpp:136-143; distance.hpp:229-242 for the mapping */
@@ -534,6 +575,7 @@ static void *worker(void *arg) {
 	map_init(&s.visited, 4096);
 	s.tmp = (float *)malloc(ix->dims * sizeof(float));
 	s.qplanes = (uint64_t *)malloc(lmdo_words_per_plane(ix->dims) * 16);
+	s.qcodes = (int8_t *)malloc(ix->dims + 16);
 	int64_t *res = (int64_t *)malloc((j->k ? j->k : 1) * sizeof(int64_t));
 	for (;;) {
 		int64_t q0 = __sync_fetch_and_add(j->next, 8);
@@ -567,6 +609,7 @@ static void *worker(void *arg) {
 	}
 	free(res);
 	free(s.qplanes);
+	free(s.qcodes);
 	free(s.tmp);
 	map_free(&s.visited);
 	free(s.top.a);
@@ -593,6 +636,11 @@ static int search_impl(const uint8_t *blocks, uint64_t n, uint64_t block_bytes, 
 	if (route == LMDO_ROUTE_TERNARY && metric == LMDO_METRIC_L2) {
 		return 2; /* distance.hpp:236-239 throws */
 	}
+	if (route == LMDO_ROUTE_INT8 && (metric != LMDO_METRIC_L2 || !g_code_off)) {
+		return 2;
+	}
+	ix.code_off = g_code_off;
+	ix.code_scale = g_code_scale;
 	ix.blocks = blocks;
 	ix.n = n;
 	ix.block_bytes = block_bytes;
@@ -783,6 +831,7 @@ static int builder_init(builder_t *b, uint8_t *blocks, uint64_t block_bytes, int
 	map_init(&b->s.visited, 4096);
 	b->s.tmp = (float *)malloc(dims * sizeof(float));
 	b->s.qplanes = (uint64_t *)malloc(lmdo_words_per_plane(dims) * 16);
+	b->s.qcodes = (int8_t *)malloc(dims + 16);
 	b->cand_cap = (uint64_t)l_insert + r + 8;
 	b->work = (pcand_t *)malloc(b->cand_cap * sizeof(pcand_t));
 	b->cand = (int64_t *)malloc(b->cand_cap * sizeof(int64_t));
@@ -799,6 +848,7 @@ static void builder_free(builder_t *b) {
 	map_free(&b->s.visited);
 	free(b->s.tmp);
 	free(b->s.qplanes);
+	free(b->s.qcodes);
 	free(b->s.top.a);
 	free(b->s.beam.a);
 	free(b->s.fin.a);

@@ -30,7 +30,9 @@ extern "C" {
 /* common/ann.hpp:16-32 */
 enum { LMDO_METRIC_L2 = 1, LMDO_METRIC_COSINE = 2, LMDO_METRIC_IP = 3 };
 enum { LMDO_VEC_FLOAT32 = 1, LMDO_VEC_INT8 = 2 };
-enum { LMDO_ROUTE_EXACT = 0, LMDO_ROUTE_TERNARY = 1 };
+enum { LMDO_ROUTE_EXACT = 0, LMDO_ROUTE_TERNARY = 1, LMDO_ROUTE_INT8 = 2 };
+/* int8 edge codec grid for LMDO_ROUTE_INT8 (row f4, parity unpinned: no reference code executes it) */
+void lmdo_set_codec(const float *off, float scale);
 
 #define LMDO_EMPTY_ID INT64_MAX /* GraphManager.cpp:154-156 */
 

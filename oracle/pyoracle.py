@@ -57,8 +57,19 @@ def port():
                                             C.c_float, _P, C.c_uint64, _P, _P])
         _sig(l.lmdo_robust_prune, C.c_int, [_P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.c_float, _P,
                                             C.c_uint64, _P, _P, C.c_uint64, _P, _P])
+        _sig(l.lmdo_set_codec, None, [_P, C.c_float])
         _libs["port"] = l
     return _libs["port"]
+
+
+_codec_keep = None
+
+
+def set_codec(offsets, scale):
+    """The int8 codec grid the next route=2 searches of the port use (downloaded from the store under test)."""
+    global _codec_keep
+    _codec_keep = np.ascontiguousarray(offsets, dtype=np.float32)
+    port().lmdo_set_codec(_codec_keep.ctypes.data, float(scale))
 
 
 def have_ref(kind="fixed"):

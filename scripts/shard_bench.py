@@ -87,7 +87,8 @@ def main():
     ap.add_argument("--L", type=int, nargs="+", default=[64])
     ap.add_argument("--l-insert", type=int, default=64)
     ap.add_argument("--metric", default="L2")
-    ap.add_argument("--route", default="exact", choices=["exact", "ternary"])
+    ap.add_argument("--route", default="exact", choices=["exact", "ternary", "int8"])
+    ap.add_argument("--codec", action="store_true", help="enable the int8 edge codec (exact route: lower-bound pre-filter)")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--tag", default="")
@@ -105,7 +106,7 @@ def main():
     lmd = importlib.import_module("duckdb-lm-diskann_b200")
     sh = importlib.import_module("duckdb-lm-diskann_b200.sharded")
     cos = a.metric == "COSINE"
-    route = lmd.ROUTE_TERNARY if a.route == "ternary" else lmd.ROUTE_EXACT
+    route = {"exact": lmd.ROUTE_EXACT, "ternary": lmd.ROUTE_TERNARY, "int8": lmd.ROUTE_INT8}[a.route]
 
     def barrier():
         if world > 1:
@@ -157,6 +158,10 @@ def main():
     del x
     torch.cuda.empty_cache()
 
+    if a.codec:
+        t0 = time.time()
+        store.enable_codec()
+        log("int8 codec built in %.2f s, store %.1f GB" % (time.time() - t0, store.device_bytes / 1e9))
     for kv in a.tune:
         key, val = kv.split("=")
         store.set_tuning(key, int(val))
@@ -205,6 +210,7 @@ def main():
         row = {"L": L, "tuning": point, "ms_per_step": round(float(ms), 4), "qps": round(total_q / (float(ms) * 1e-3), 1),
                "recall_at_%d" % a.k: round(float(rec), 4), "local_kernel_ms_max": round(float(kms), 4),
                "E_per_q": round(st.expansions / a.nq, 1), "V_per_q": round(st.distance_evals / a.nq, 1),
+               "fetched_per_q": round(st.exact_fetches / a.nq, 1),
                "local_algorithmic_GBps": round(st.algorithmic_bytes / (st.traverse_ms + st.rerank_ms) / 1e6, 1),
                "traverse_ms": round(st.traverse_ms, 4), "rerank_ms": round(st.rerank_ms, 4),
                "tie_overflows": st.tie_overflows, "merge_fallbacks_per_q": round(st.merge_fallbacks / a.nq, 2),
