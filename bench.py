@@ -13,6 +13,15 @@ A "step" is one pass of the hot path (traversal + exact top-k) over one 10k-quer
   cpu_baseline  the reference's own Searcher.cpp (+ oracle/patches/searcher_fixed.patch) compiled into oracle/_ref,
             timed on this box's host cores on a bounded sample of the same queries
 `--impl reference` times that CPU implementation alone on the same workload (all host threads).
+
+The headline keys keep the contract above; `config` additionally carries (all measured in this run, --extras none skips):
+  parity        tie-aware comparison of the WHOLE batch with the reference CPU run (tests/parity.py rules) and the same for
+                LMD_SEARCH_STRICT_FP (the reference's summation order: bit-equal distances)
+  e2e_pageable  the e2e loop with pageable numpy buffers (what DuckDB's float* / std::vector hand the adapter)
+  sustained     >= 2 s of back-to-back steps with the clock sampler's summary
+  other_configs BASELINE.json configs on the GPUs of this run: c2_strong / c3_strong (ONE 10k batch split over the N
+                ranks), c4 (10M x 96 replicated, 100k queries / N), c5 (dataset-sharded, NCCL all-gather + merge, N >= 2),
+                c2_iid (SURVEY 8d hard case), c2_codec (int8 pre-filter / int8 route on the headline index)
 """
 import argparse
 import importlib
@@ -55,6 +64,8 @@ def parse():
     ap.add_argument("--sweep", action="store_true", help="also print the whole L sweep (stderr)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--extras", default="auto", choices=["auto", "none"],
+                    help="auto = also run the other BASELINE configs / strong scaling / sustained records")
     return ap.parse_args()
 
 
@@ -146,7 +157,7 @@ class ClockSampler:
 
 def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0):
     """Times the reference's CPU search (oracle/_ref fixed build when present, else the C port) on a bounded sample:
-    the rotated query batches, over and over, until about `seconds` of CPU work are done. Returns the ids of batch 0
+    the rotated query batches, over and over, until about `seconds` of CPU work are done. Returns the result of batch 0
     (the parity / recall sample)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle
@@ -160,12 +171,12 @@ def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0
     while dt < seconds:
         q = batches[i % len(batches)]
         t0 = time.perf_counter()
-        ids, _, _, _ = pyoracle.search(blocks_np, block_bytes, a.dims, a.r, q, a.k, L, metric=metric, entry_row_id=0,
-                                       route=1 if a.route == "ternary" else 0, nthreads=nthreads, impl=impl)
+        res = pyoracle.search(blocks_np, block_bytes, a.dims, a.r, q, a.k, L, metric=metric, entry_row_id=0,
+                              route=1 if a.route == "ternary" else 0, nthreads=nthreads, impl=impl)
         dt += time.perf_counter() - t0
         done += q.shape[0]
         if ids0 is None:
-            ids0 = ids
+            ids0 = res  # (ids, distances, counts, per-query [expansions, fetches]) of batch 0
         i += 1
     return {"value": done / dt, "unit": "queries/s", "cores": nthreads, "kind": kind,
             "sample": "%d queries (%d passes over the %d-query batches) at L=%d, %d host threads, %.1f s" % (
@@ -181,6 +192,249 @@ def profiled_traffic(a, L):
         return t.get(key, {}).get("dram_bytes_per_launch")
     except Exception:
         return None
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# other_configs: BASELINE.json configs C2 (strong), C3, C4, C5 on the GPUs of this run. Every record is timed like the
+# headline (barrier + CUDA events on the searching stream, max over ranks); local failures are reported in the record.
+# ------------------------------------------------------------------------------------------------------------------
+class Job:
+    def __init__(self, torch, dist, lmd, sh, wl, rank, world, local, dev, dist_on, steps, warmup):
+        self.torch, self.dist, self.lmd, self.sh, self.wl = torch, dist, lmd, sh, wl
+        self.rank, self.world, self.local, self.dev, self.dist_on = rank, world, local, dev, dist_on
+        self.steps, self.warmup = max(5, min(steps, 20)), max(3, min(warmup, 5))
+        self.stream = torch.cuda.current_stream(dev)
+
+    def barrier(self):
+        if self.dist_on:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, vals, op="max"):
+        t = self.torch.tensor(vals, device=self.dev, dtype=self.torch.float64)
+        if self.dist_on:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return [float(v) for v in t]
+
+    def agree(self, err):
+        """Every rank reports whether its local (allocation-heavy) phase worked BEFORE the next collective, so that one
+        rank's failure turns into an error record on all of them instead of a hang."""
+        if self.reduce([1.0 if err else 0.0])[0] != 0.0:
+            raise RuntimeError(err or "another rank failed in its local phase")
+
+    def time_steps(self, step):
+        """ms per step of `step()` (enqueues on the current stream): warm-up, barrier, events, max over ranks."""
+        torch = self.torch
+        for _ in range(self.warmup):
+            step()
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        for _ in range(self.steps):
+            step()
+        e1.record(self.stream)
+        self.barrier()
+        return self.reduce([e0.elapsed_time(e1) / self.steps])[0]
+
+    def query_sharded(self, store, q_local, truth_local, k, L, route, total_q, flags=0):
+        """This rank searches q_local (its slice / its own batch); no collective on the path. -> record"""
+        torch, lmd = self.torch, self.lmd
+        nq = q_local.shape[0]
+        ids = torch.empty((max(nq, 1), k), dtype=torch.int64, device=self.dev)
+        dd = torch.empty((max(nq, 1), k), dtype=torch.float32, device=self.dev)
+        store.set_stream(self.stream.cuda_stream)
+
+        def step():
+            if nq:
+                store.search_raw(q_local, nq, k, L, route=route, flags=lmd.SEARCH_ASYNC | flags, out_ids=ids, out_dist=dd)
+        ms = self.time_steps(step)
+        st = store.search_raw(q_local, nq, k, L, route=route, flags=flags, out_ids=ids, out_dist=dd) if nq else None
+        hits = self.wl.recall_hits(ids[:nq], truth_local) if nq and truth_local is not None else 0
+        tot = truth_local.numel() if nq and truth_local is not None else 0
+        kms, hits, tot, E, V, F, ab = (st.traverse_ms + st.rerank_ms if st else 0.0), hits, tot, (st.expansions if st else 0), \
+            (st.distance_evals if st else 0), (st.exact_fetches if st else 0), (st.algorithmic_bytes if st else 0)
+        kmax = self.reduce([kms])[0]
+        hits, tot, E, V, F, ab, nqs = self.reduce([hits, tot, E, V, F, ab, nq], op="sum")
+        return {"L": L, "queries_per_step": int(total_q), "queries_per_gpu": int(nq), "ms_per_step": round(ms, 4),
+                "qps": round(total_q / (ms * 1e-3), 1), "recall_at_%d" % k: round(hits / max(tot, 1), 4),
+                "kernel_ms_max_over_gpus": round(kmax, 4), "E_per_q": round(E / max(nqs, 1), 1),
+                "V_per_q": round(V / max(nqs, 1), 1), "rows_fetched_per_q": round(F / max(nqs, 1), 1),
+                "algorithmic_GBps_per_gpu": round(ab / max(self.world, 1) / max(kmax, 1e-9) / 1e6, 1)}
+
+
+def extra_c2_strong(J, store, batch0, truth0, k, L, route):
+    """configs[2] as written: the headline index, ONE 10k-query batch split over the N ranks."""
+    torch = J.torch
+    lo, hi = J.sh.query_slice(batch0.shape[0], J.rank, J.world)
+    q = torch.from_numpy(batch0[lo:hi]).to(J.dev)
+    t = torch.from_numpy(truth0[lo:hi]).to(J.dev)
+    r = J.query_sharded(store, q, t, k, L, route, batch0.shape[0])
+    r["note"] = "one %d-query batch split %d ways (strong scaling); graph replicated" % (batch0.shape[0], J.world)
+    return r
+
+
+def extra_codec(J, store, batch_local, truth_local, k, L):
+    """Row f4: the int8 edge codec on the headline index - exact routing with the lower-bound pre-filter (same results,
+    fewer rows fetched) and int8 routing + exact rerank (parity unpinned). One full batch per GPU like the headline."""
+    torch, lmd = J.torch, J.lmd
+    q = torch.from_numpy(batch_local).to(J.dev)
+    t = torch.from_numpy(truth_local).to(J.dev) if truth_local is not None else None
+    tot = batch_local.shape[0] * J.world
+    out = {"plain": J.query_sharded(store, q, t, k, L, lmd.ROUTE_EXACT, tot)}
+    t0 = time.time()
+    err = None
+    try:
+        store.enable_codec()
+        store.finalize()
+    except Exception as e:  # noqa: BLE001
+        err = repr(e)
+    J.agree(err)
+    out["codec_build_s"] = round(time.time() - t0, 2)
+    out["prefilter"] = J.query_sharded(store, q, t, k, L, lmd.ROUTE_EXACT, tot)
+    rows = []
+    for l in (56, 64, 80, 96):
+        rows.append(J.query_sharded(store, q, t, k, l, lmd.ROUTE_INT8, tot))
+    out["int8_route"] = rows
+    out["note"] = ("exact + pre-filter returns the plain traversal's ids and distance bits (tests/test_gpu_round2.py); "
+                   "int8 route: PARITY UNPINNED (restatement only); recall measured on rank 0's batch when N > 1")
+    return out
+
+
+def extra_built(J, tag, n, dims, metric, kind, nq_total, split, k, runs, r=32, l_insert=64, release=False):
+    """A GPU-generated, GPU-built index replicated on every rank. split=True: ONE batch of nq_total queries split over the
+    ranks (strong); False: nq_total / N queries per rank, every rank its own. runs = [(label, route, L, flags)]."""
+    torch, lmd, wl = J.torch, J.lmd, J.wl
+    cos = metric == "COSINE"
+    t0 = time.time()
+    err = store = None
+    try:
+        x = wl.gen(n, dims, 42 if kind == "clustered" else 44, J.dev, cos, kind=kind)
+        store, bst = wl.build_store(lmd, x, r, metric, J.local, l_insert=l_insert)
+        t_build = time.time() - t0
+        if split:
+            qall = wl.gen(nq_total, dims, 43 if kind == "clustered" else 45, J.dev, cos, kind=kind)
+            lo, hi = J.sh.query_slice(nq_total, J.rank, J.world)
+            q = qall[lo:hi].contiguous()
+        else:
+            q = wl.gen(nq_total // J.world, dims, (43 if kind == "clustered" else 45) + 1000 * J.rank, J.dev, cos,
+                       kind=kind)
+        ns = min(q.shape[0], 5000)  # recall sample per rank
+        _, truth = wl.topk_scores(x, q[:ns], k, metric)
+        del x
+        if release:
+            full_gb = store.device_bytes / 1e9
+            store.finalize()
+            store.release_blocks()
+    except Exception as e:  # noqa: BLE001
+        err = repr(e)
+    torch.cuda.empty_cache()
+    try:
+        J.agree(err)
+    except RuntimeError:
+        if store is not None:
+            store.close()
+        raise
+    rec = {"workload": "synthetic %dx%d float32 %s (%s), R=%d, graph built by lmd_build_graph (l_insert=%d)" % (
+               n, dims, metric, kind, r, l_insert),
+           "gen_build_s": round(t_build, 2), "build_kernels_ms": round(bst.total_ms, 1),
+           "store_GB_per_gpu": round(full_gb if release else store.device_bytes / 1e9, 2),
+           "mode": ("one %d-query batch split %d ways (strong)" if split else "%d queries per step over %d GPUs, replicated") % (
+               nq_total, J.world)}
+    if release:
+        rec["store_GB_per_gpu_blocks_released"] = round(store.device_bytes / 1e9, 2)
+    for label, route, L, flags in runs:
+        # recall on the sample: time the whole slice, count hits on its first ns rows
+        row = J.query_sharded(store, q, None, k, L, route, nq_total if split else (nq_total // J.world) * J.world, flags)
+        ids = torch.empty((ns, k), dtype=torch.int64, device=J.dev)
+        if ns:
+            store.search_raw(q[:ns], ns, k, L, route=route, flags=flags, out_ids=ids, stats=False)
+        hits, tot = J.reduce([wl.recall_hits(ids, truth) if ns else 0, truth.numel() if ns else 0], op="sum")
+        row["recall_at_%d" % k] = round(hits / max(tot, 1), 4)
+        row["recall_sample"] = "%d queries per GPU" % ns
+        rec.setdefault("runs", {})[label] = row
+    store.close()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64):
+    """configs[4]: dataset-sharded - rank s holds rows [lo_s, hi_s) with a shard-local graph; every rank searches the FULL
+    batch, ONE NCCL all-gather of the [Q][k] (distance, row id) lists, k-way merge kernel."""
+    torch, lmd, wl, sh = J.torch, J.lmd, J.wl, J.sh
+    n = rows_per_gpu * J.world
+    nq = 10000
+    lo, hi = sh.shard_rows(n, J.rank, J.world)
+    t0 = time.time()
+    err = store = None
+    try:
+        x = wl.gen(hi - lo, dims, 42 + J.rank, J.dev)
+        row_ids = torch.arange(lo, hi, dtype=torch.int64, device=J.dev)
+        store, bst = wl.build_store(lmd, x, r, "L2", J.local, row_ids=row_ids, l_insert=l_insert)
+        t_build = time.time() - t0
+        q = wl.gen(nq, dims, 43, J.dev)
+        S, I = wl.topk_scores(x, q, k, "L2", base_id=lo)
+        del x, row_ids
+        full_gb = store.device_bytes / 1e9
+        store.finalize()
+        store.release_blocks()
+    except Exception as e:  # noqa: BLE001
+        err = repr(e)
+    try:
+        J.agree(err)
+    except RuntimeError:
+        if store is not None:
+            store.close()
+        raise
+    allS = torch.empty((J.world,) + S.shape, device=J.dev)
+    allI = torch.empty((J.world,) + I.shape, dtype=torch.int64, device=J.dev)
+    J.dist.all_gather_into_tensor(allS, S)
+    J.dist.all_gather_into_tensor(allI, I)
+    _, sel = torch.topk(allS.permute(1, 0, 2).reshape(nq, -1), k, dim=1, largest=False)
+    truth = torch.gather(allI.permute(1, 0, 2).reshape(nq, -1), 1, sel)
+    del S, I, allS, allI
+    torch.cuda.empty_cache()
+    rec = {"workload": "synthetic %dx%d float32 L2 (clustered), %d shards of %d rows, shard-local graphs (lmd_build_graph, "
+                       "l_insert=%d), global row ids" % (n, dims, J.world, hi - lo, l_insert),
+           "gen_build_s": round(t_build, 2), "store_GB_per_gpu": round(full_gb, 2),
+           "store_GB_per_gpu_blocks_released": round(store.device_bytes / 1e9, 2),
+           "nccl_ranks": J.dist.get_world_size(), "allgather_bytes_per_rank": nq * k * 12, "runs": []}
+    store.set_stream(J.stream.cuda_stream)
+    searcher = sh.DatasetShardedSearcher(store, device=J.dev)
+    ids = torch.empty((nq, k), dtype=torch.int64, device=J.dev)
+    dd = torch.empty((nq, k), dtype=torch.float32, device=J.dev)
+    for L in Ls:
+        out = [None]
+
+        def full():
+            out[0] = searcher.search(q, k, L)
+
+        def local_only():
+            store.search_raw(q, nq, k, L, flags=lmd.SEARCH_ASYNC, out_ids=ids, out_dist=dd)
+        ms_full = J.time_steps(full)
+        ms_local = J.time_steps(local_only)
+        st = store.search_raw(q, nq, k, L, out_ids=ids, out_dist=dd)
+        kmax = J.reduce([st.traverse_ms + st.rerank_ms])[0]
+        rec["runs"].append({"L": L, "ms_per_step": round(ms_full, 4), "qps": round(nq / (ms_full * 1e-3), 1),
+                            "recall_at_%d" % k: round(wl.recall(out[0][0], truth), 4),
+                            "local_search_ms": round(ms_local, 4), "local_kernel_ms_max_over_gpus": round(kmax, 4),
+                            "allgather_plus_merge_ms": round(ms_full - ms_local, 4),
+                            "E_per_q": round(st.expansions / nq, 1), "V_per_q": round(st.distance_evals / nq, 1)})
+    store.close()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def guarded(J, name, fn, *a, **kw):
+    t0 = time.time()
+    try:
+        r = fn(J, *a, **kw)
+    except Exception as e:  # noqa: BLE001 - an extra must never take the headline line down
+        log("extra %s failed: %r" % (name, e))
+        r = {"error": repr(e)[:300]}
+    if isinstance(r, dict):
+        r["wall_s"] = round(time.time() - t0, 1)
+    log("extra", name, json.dumps(r)[:600])
+    return r
 
 
 def main():
@@ -199,12 +453,14 @@ def main():
     if have_cuda:
         torch.cuda.set_device(local)
     dist_on = world > 1 and a.impl == "ours"
+    dist = None
     if dist_on:
+        import datetime
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
-        dist.init_process_group("nccl", device_id=torch.device(dev))
+        dist.init_process_group("nccl", device_id=torch.device(dev), timeout=datetime.timedelta(seconds=600))
 
     # ---- workload: one index (replicated), N_BATCHES query batches per rank -------------------------------------
     if rank == 0 or not dist_on:
@@ -217,7 +473,10 @@ def main():
     bb = lay["block_bytes"]
     batches = [fx.make_dataset(a.nq, a.dims, kind=a.kind, seed=43 + 1000 * rank + 17 * b,
                                normalize=(a.metric == "COSINE")) for b in range(N_BATCHES)]
-    truth = load_or_build_truth(a, fx, x, batches[0], dev) if rank == 0 else None
+    # rank 0's first batch doubles as THE batch of the strong-scaling record (identical on every rank)
+    batch0 = batches[0] if rank == 0 else fx.make_dataset(a.nq, a.dims, kind=a.kind, seed=43,
+                                                          normalize=(a.metric == "COSINE"))
+    truth = load_or_build_truth(a, fx, x, batch0, dev) if rank == 0 else None
     workload = "synthetic %dx%d float32 %s (%s, seed 42), R=%d, %d-query batch per GPU, k=%d" % (
         a.n, a.dims, a.metric, a.kind, a.r, a.nq, a.k)
 
@@ -225,6 +484,8 @@ def main():
         return run_reference(a, fx, x, nbrs, counts, batches, truth, workload, bb)
 
     lmd = importlib.import_module("duckdb-lm-diskann_b200")
+    sh = importlib.import_module("duckdb-lm-diskann_b200.sharded")
+    wl = importlib.import_module("duckdb-lm-diskann_b200.workloads")
     t0 = time.time()
     blocks_dev = fx.pack_blocks(x, nbrs, counts, a.r, device=dev)  # node blocks, reference layout, built in HBM
     store = lmd.Store(a.dims, a.r, metric=lmd.METRIC_BY_NAME[a.metric], capacity=a.n, device=local, l_search=100)
@@ -236,7 +497,7 @@ def main():
                                                                 store.device_bytes / 1e9))
     keep_blocks_host = rank == 0 and not a.no_cpu
     blocks_np = blocks_dev.cpu().numpy() if keep_blocks_host else None
-    del blocks_dev
+    del blocks_dev, x, nbrs, counts
     torch.cuda.empty_cache()
 
     # ---- L: smallest of the sweep reaching the recall target (rank 0 decides) ------------------------------------
@@ -265,6 +526,9 @@ def main():
         t = torch.tensor([L], device=dev, dtype=torch.int64)
         dist.broadcast(t, 0)
         L = int(t.item())
+        tt = torch.from_numpy(truth).to(dev) if rank == 0 else torch.empty((a.nq, a.k), dtype=torch.int64, device=dev)
+        dist.broadcast(tt, 0)
+        truth = tt.cpu().numpy()
 
     # ---- device-resident arm ("value") ---------------------------------------------------------------------------
     d_q = [torch.from_numpy(b).to(dev) for b in batches]
@@ -280,16 +544,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def dev_step(i):
+        store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_ids,
+                         out_dist=d_dist, out_count=d_cnt)
+
     for i in range(a.warmup):
-        store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_ids, out_dist=d_dist,
-                         out_count=d_cnt)
+        dev_step(i)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
         e0.record(stream)
         for i in range(a.steps):
-            store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_ids, out_dist=d_dist,
-                             out_count=d_cnt)
+            dev_step(i)
         e1.record(stream)
         barrier()
         dev_ms = e0.elapsed_time(e1)
@@ -318,25 +584,87 @@ def main():
             store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist, stats=False)
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
-        # what one `ORDER BY array_distance(...) LIMIT k` statement costs: a batch of ONE through the same call
-        lat = []
-        for i in range(220):
-            t1 = time.perf_counter()
-            store.search_raw(h_q[0][i:i + 1], 1, a.k, L, route=route, out_ids=h_ids[:1], out_dist=h_dist[:1], stats=False)
-            lat.append(time.perf_counter() - t1)
-        lat_us = sorted(lat[20:])[100] * 1e6
+    # ... and with PAGEABLE buffers (what DuckDB's float* / std::vector<row_t> give GpuSearcher::Search): staged copies
+    p_ids = np.empty((a.nq, a.k), dtype=np.int64)
+    p_dist = np.empty((a.nq, a.k), dtype=np.float32)
+    for i in range(3):
+        store.search_raw(batches[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=p_ids, out_dist=p_dist, stats=False)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(a.steps):
+        store.search_raw(batches[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=p_ids, out_dist=p_dist, stats=False)
+    torch.cuda.synchronize()
+    e2e_page_s = time.perf_counter() - t0
+    # what one `ORDER BY array_distance(...) LIMIT k` statement costs: a batch of ONE (pageable) through the same call
+    lat = []
+    for i in range(220):
+        t1 = time.perf_counter()
+        store.search_raw(batches[0][i:i + 1], 1, a.k, L, route=route, out_ids=p_ids[:1], out_dist=p_dist[:1], stats=False)
+        lat.append(time.perf_counter() - t1)
+    lat_us = sorted(lat[20:])[100] * 1e6
+    # ---- sustained: >= 2 s of back-to-back device-resident steps, clocks sampled throughout --------------------------
+    sustained = None
+    if a.extras != "none":
+        n_sus = int(max(a.steps, min(20000, 2200.0 / max(dev_ms / a.steps, 1e-3))))
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as sus_clocks:
+            s0.record(stream)
+            for i in range(n_sus):
+                dev_step(i)
+            s1.record(stream)
+            barrier()
+        sus_ms = s0.elapsed_time(s1)
+        if dist_on:
+            t = torch.tensor([sus_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            sus_ms = float(t[0])
+        sustained = {"steps": n_sus, "seconds": round(sus_ms * 1e-3, 3), "ms_per_step": round(sus_ms / n_sus, 4),
+                     "value": round(a.nq * world * n_sus / (sus_ms * 1e-3), 1), "unit": "queries/s",
+                     "clocks": sus_clocks.summary()}
     if dist_on:
-        t = torch.tensor([dev_ms, e2e_s], device=dev, dtype=torch.float64)
+        t = torch.tensor([dev_ms, e2e_s, e2e_page_s], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, e2e_s = float(t[0]), float(t[1])
+        dev_ms, e2e_s, e2e_page_s = float(t[0]), float(t[1]), float(t[2])
+
+    # ---- rank 0, GPU side: results at the chosen L (default and strict fp) for recall / parity ----------------------
+    ids0 = dist0 = cnt0 = strict_res = None
+    if rank == 0:
+        ids0, dist0, cnt0, st0 = store.search(batches[0], a.k, L, route=route)
+        if not a.no_cpu:
+            strict_res = store.search(batches[0], a.k, L, route=route, flags=lmd.SEARCH_STRICT_FP, qstats=True)
+    store_bytes = store.device_bytes
+
+    # ---- other configs (all ranks) -----------------------------------------------------------------------------------
+    other = {}
+    if a.extras != "none":
+        J = Job(torch, dist, lmd, sh, wl, rank, world, local, dev, dist_on, a.steps, a.warmup)
+        J.stream = stream
+        other["c2_strong"] = guarded(J, "c2_strong", extra_c2_strong, store, batch0, truth, a.k, L, route)
+        if a.metric == "L2" and a.route == "exact":
+            other["c2_codec"] = guarded(J, "c2_codec", extra_codec, store, batches[0], truth if rank == 0 else None, a.k, L)
+    store.close()
+    del d_q
+    torch.cuda.empty_cache()
+    if a.extras != "none":
+        other["c3_strong"] = guarded(J, "c3_strong", extra_built, "c3", 1_000_000, 768, "COSINE", "clustered", 10_000, True,
+                                     a.k, [("exact_L32", lmd.ROUTE_EXACT, 32, 0), ("ternary_L80", lmd.ROUTE_TERNARY, 80, 0)])
+        other["c2_iid"] = guarded(J, "c2_iid", extra_built, "iid", 1_000_000, 128, "L2", "iid", 10_000 * world, False, a.k,
+                                  [("exact_L64", lmd.ROUTE_EXACT, 64, 0), ("exact_L256", lmd.ROUTE_EXACT, 256, 0)])
+        other["c4"] = guarded(J, "c4", extra_built, "c4", 10_000_000, 96, "L2", "clustered", 100_000, False, a.k,
+                              [("exact_L96", lmd.ROUTE_EXACT, 96, 0)], release=True)
+        if dist_on:
+            # 12.5 M rows per GPU: the 100 M x 96 configuration at N = 8, the same shard size below that
+            other["c5"] = guarded(J, "c5", extra_c5, 12_500_000, 96, a.k, [48, 64])
+        else:
+            other["c5"] = {"skipped": "dataset sharding needs N >= 2 (its all-gather is the point)"}
     if rank != 0:
         if dist_on:
             dist.barrier()
             dist.destroy_process_group()
         return 0
 
-    # ---- rank 0: recall at the chosen L, CPU baseline, report ------------------------------------------------------
-    ids0, dist0, cnt0, st0 = store.search(batches[0], a.k, L, route=route)
+    # ---- rank 0: recall at the chosen L, CPU baseline, parity, report ---------------------------------------------
     recall = fx.recall_at_k(ids0, truth)
     peaks = {}
     try:
@@ -348,9 +676,21 @@ def main():
     cpu = None
     parity = None
     if not a.no_cpu:
-        cpu, cpu_ids, nsamp = cpu_reference_qps(a, blocks_np, bb, batches, L, a.cpu_seconds)
-        cpu["recall_at_10"] = round(fx.recall_at_k(cpu_ids, truth[:nsamp]), 4)
-        parity = float((cpu_ids == ids0[:nsamp]).all(axis=1).mean())
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from parity import parity_report
+        cpu, cpu_res, nsamp = cpu_reference_qps(a, blocks_np, bb, batches, L, a.cpu_seconds)
+        cpu["recall_at_10"] = round(fx.recall_at_k(cpu_res[0], truth[:nsamp]), 4)
+        one, _, _ = cpu_reference_qps(a, blocks_np, bb, [b[:2000] for b in batches], L, min(4.0, a.cpu_seconds), nthreads=1)
+        cpu["single_thread"] = {"value": one["value"], "unit": "queries/s", "cores": 1, "sample": one["sample"]}
+        parity = {"against": "reference CPU run (%s) of the same %d queries" % (cpu["kind"], nsamp),
+                  "default": parity_report(ids0[:nsamp], dist0[:nsamp], cpu_res[0], cpu_res[1], cpu_res[2])}
+        if strict_res is not None:
+            sp = parity_report(strict_res[0][:nsamp], strict_res[1][:nsamp], cpu_res[0], cpu_res[1], cpu_res[2])
+            sp["dist_bits_identical"] = bool(np.array_equal(strict_res[1][:nsamp].view(np.uint32), cpu_res[1].view(np.uint32)))
+            sp["expansion_counts_identical"] = bool(np.array_equal(strict_res[4][:nsamp, 0].astype(np.int64),
+                                                                   cpu_res[3][:, 0].astype(np.int64)))
+            sp["flag"] = "LMD_SEARCH_STRICT_FP (reference summation order; parity tool, not the timed path)"
+            parity["strict_fp"] = sp
     total_q = a.nq * world * a.steps
     out = {
         "metric": "QPS @ recall@10>=0.95, 1Mx128 L2 (LM_DISKANN beam search + exact top-k)",
@@ -361,26 +701,39 @@ def main():
                    "entry": "slot 0", "query_batches_rotated": N_BATCHES,
                    "single_query_latency_us": round(lat_us, 1),
                    "l2_note": ("node store %.1f GB >> 126 MB L2; every step gathers ~%.1f GB of it" % (
-                       store.device_bytes / 1e9, alg_bytes / a.steps / 1e9)) if store.device_bytes > 4 * 126e6 else (
+                       store_bytes / 1e9, alg_bytes / a.steps / 1e9)) if store_bytes > 4 * 126e6 else (
                        "node store %.0f MB FITS in the 126 MB L2 and is not flushed between steps: a parity / "
-                       "small-index configuration, not a bandwidth measurement" % (store.device_bytes / 1e6)),
+                       "small-index configuration, not a bandwidth measurement" % (store_bytes / 1e6)),
                    "parallelism": "queries sharded, graph replicated (%d x %d queries per step)" % (world, a.nq)},
         "e2e": {"value": total_q / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": a.nq * a.dims * 4,
-                "d2h_bytes_per_step": a.nq * a.k * 12, "ms_per_step": e2e_s * 1e3 / a.steps},
+                "d2h_bytes_per_step": a.nq * a.k * 12, "ms_per_step": e2e_s * 1e3 / a.steps,
+                "buffers": "pinned host memory, read / written in place by the kernels"},
+        "e2e_pageable": {"value": total_q / e2e_page_s, "unit": "queries/s", "ms_per_step": e2e_page_s * 1e3 / a.steps,
+                         "buffers": "pageable host memory (numpy), staged through cudaMemcpyAsync inside the call"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": profiled_traffic(a, L), "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps, "rerank_kernel_ms": rerank_ms / a.steps,
+                     "traffic": profiled_traffic(a, L),
+                     "traffic_source": "profiles/traffic.json (ncu --set full capture of this workload by the builder, "
+                                       "not measured in this run)",
+                     "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps, "rerank_kernel_ms": rerank_ms / a.steps,
                      "algorithmic_bytes_per_launch": alg_bytes // a.steps,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
                      "E_per_query": E / (a.nq * a.steps), "V_per_query": V / (a.nq * a.steps)},
         "cpu_baseline": cpu,
         "clocks": clocks.summary(),
     }
+    if sustained:
+        out["sustained"] = sustained
     if parity is not None:
-        out["config"]["id_exact_queries_vs_reference_cpu"] = round(parity, 4)
+        out["config"]["parity"] = parity
+        out["config"]["id_exact_queries_vs_reference_cpu"] = round(
+            parity["default"]["id_identical_queries"] / max(parity["default"]["queries"], 1), 4)
+        out["config"]["id_mismatch_outside_ties"] = parity["default"]["id_mismatch_outside_ties"]
+        out["config"]["dist_max_rel_err"] = parity["default"]["dist_max_rel_err"]
     if sweep:
         out["config"]["L_sweep"] = sweep
-    store.close()
+    if other:
+        out["config"]["other_configs"] = other
     print(json.dumps(out), flush=True)
     if dist_on:
         dist.barrier()

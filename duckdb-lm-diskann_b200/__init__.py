@@ -26,6 +26,7 @@ SEARCH_ASYNC = 4
 SEARCH_STRICT_FP = 8
 SEARCH_NO_PREFILTER = 16
 SEARCH_TENSOR_RERANK = 32
+GROUP_QUERY_SHARDED, GROUP_DATASET_SHARDED = 0, 1
 EMPTY_ROW_ID = np.iinfo(np.int64).max  # core/GraphManager.cpp:154-156
 OK, ERR_INVALID_ARG, ERR_CUDA, ERR_OOM, ERR_STATE, ERR_UNSUPPORTED = range(6)
 METRIC_BY_NAME = {"L2": METRIC_L2, "COSINE": METRIC_COSINE, "IP": METRIC_IP}
@@ -56,6 +57,13 @@ class Stats(C.Structure):
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class GroupStats(C.Structure):
+    _fields_ = [("members", C.c_uint32), ("mode", C.c_uint32), ("peer_access", C.c_uint32), ("reserved", C.c_uint32),
+                ("queries", C.c_uint64 * 16), ("search_ms", C.c_float * 16), ("search_ms_max", C.c_float),
+                ("merge_ms", C.c_float), ("wall_ms", C.c_float), ("reserved2", C.c_uint32),
+                ("merge_input_bytes", C.c_uint64)]
 
 
 class BuildParams(C.Structure):
@@ -105,6 +113,11 @@ SYMBOLS = [
     ("lmd_filter_count", C.c_uint64, [_P]),
     ("lmd_search_batch_filtered", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                              _P, _P, _P, _P, C.POINTER(Stats)]),
+    ("lmd_group_create", C.c_int32, [C.POINTER(_P), C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    ("lmd_group_destroy", C.c_int32, [_P]),
+    ("lmd_group_size", C.c_uint32, [_P]),
+    ("lmd_group_search_batch", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P,
+                                          C.POINTER(GroupStats)]),
     ("lmd_merge_topk", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P]),
     ("lmd_merge_topk_async", C.c_int32, [C.c_int, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, _P, _P]),
     ("lmd_store_upload_vectors", C.c_int32, [_P, _P, _P, C.c_uint64]),
@@ -364,6 +377,50 @@ class Context:
         try:
             if self._h:
                 lib().lmd_ctx_destroy(self._h)
+                self._h = _P()
+        except TypeError:
+            pass
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+class Group:
+    """lmd_group: several stores on several devices of this ONE process searched as one (query- or dataset-sharded)."""
+
+    def __init__(self, stores, mode=GROUP_QUERY_SHARDED):
+        self.stores = list(stores)
+        self.mode = mode
+        arr = (_P * len(self.stores))(*[s._h for s in self.stores])
+        self._h = _P()
+        _check(lib().lmd_group_create(arr, len(self.stores), mode, C.byref(self._h)))
+
+    def search_raw(self, queries, nq, k, L=0, route=ROUTE_EXACT, flags=0, out_ids=None, out_dist=None, out_count=None,
+                   stats=True):
+        st = GroupStats() if stats else None
+        _check(lib().lmd_group_search_batch(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist),
+                                            _ptr(out_count), C.byref(st) if stats else None))
+        return st
+
+    def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0):
+        """queries [nq, dims] float32 numpy -> (ids [nq,k], dist [nq,k], count [nq], GroupStats)"""
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        nq = q.shape[0]
+        ids = np.full((nq, k), -1, dtype=np.int64)
+        dist = np.zeros((nq, k), dtype=np.float32)
+        count = np.zeros(nq, dtype=np.uint32)
+        st = self.search_raw(q, nq, k, L, route, flags, ids, dist, count)
+        return ids, dist, count, st
+
+    def close(self):
+        try:
+            if self._h:
+                lib().lmd_group_destroy(self._h)
                 self._h = _P()
         except TypeError:
             pass

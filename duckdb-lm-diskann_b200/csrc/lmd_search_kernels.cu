@@ -209,7 +209,10 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	}
 	// room behind the top L for distance ties (see list_insert): integer ternary distances tie all the time, fp32
 	// distances only for duplicate vectors
-	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots : (a.route != LMD_ROUTE_EXACT ? 64u : 0u);
+	// ... and, under LMD_SEARCH_STRICT_FP, whenever two different sums round to the same sqrtf (about once per thousand
+	// queries at L = 64): the oracle expands such an entry, so strict parity of the expansion counts needs the region too
+	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots
+	                                            : (a.route != LMD_ROUTE_EXACT ? 64u : (p.strict ? 32u : 0u));
 	// exact routing on a store with the int8 codec: the codes decide which rows are fetched (same results, fewer bytes)
 	uint32_t kroute = a.route;
 	if (a.route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && s->codes_gen == s->views_gen && !a.no_prefilter &&
@@ -272,7 +275,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl);
 	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps, s->tune.filter_mode,
 	                                  (int)s->tune.filter_log2);
-	if (kroute == LMD_ROUTE_EXACT && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
+	if (kroute == LMD_ROUTE_EXACT && !p.strict && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
 		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
 		// (10 M x 96, L = 48 / 128: 1.46 -> 1.37 / 3.53 -> 3.34 ms per 12.5 k queries; 1 M x 96, L = 64: 1.21 -> 1.13;
 		// profiles/r43_g_sweep_*.json; those kernels exist for lists of 64 and 128 entries, not 96). With the 4 KB filter

@@ -333,14 +333,36 @@ GpuSearcher::GpuSearcher(std::shared_ptr<DeviceNodeStore> store, Route route) : 
 	}
 }
 
+GpuSearcher::~GpuSearcher() {
+	for (auto &kv : contexts_) {
+		lmd_ctx_destroy(kv.second);
+	}
+}
+
+lmd_ctx *GpuSearcher::ThreadContext() {
+	std::lock_guard<std::mutex> g(mu_);
+	auto it = contexts_.find(std::this_thread::get_id());
+	if (it != contexts_.end()) {
+		return it->second;
+	}
+	lmd_ctx *c = nullptr;
+	Check(lmd_ctx_create(store_->Handle(), &c), "GpuSearcher: search context");
+	contexts_[std::this_thread::get_id()] = c;
+	return c;
+}
+
 void GpuSearcher::Search(const float *query_vector, const core::LmDiskannConfig &config,
                          core::IGraphManager *graph_manager, common::idx_t k_neighbors,
                          std::vector<common::row_t> &result_row_ids, common::idx_t search_list_size) {
 	result_row_ids.clear();
 	if (mirror_ && mirror_->HasPending()) {
-		mirror_->Flush(); // blocks the host allocated / dirtied / deleted since the last search
+		std::lock_guard<std::mutex> g(mu_);
+		if (mirror_->HasPending()) {
+			mirror_->Flush(); // blocks the host allocated / dirtied / deleted since the last search
+		}
 	}
 	if (graph_manager) {
+		std::lock_guard<std::mutex> g(mu_);
 		// the entry point can move between searches (first insert / deletion, core/GraphManager.cpp:119-121)
 		common::row_t rid = graph_manager->GetEntryPointRowId();
 		if (graph_manager->GetEntryPointPointer() == common::IndexPointer()) {
@@ -389,12 +411,113 @@ void GpuSearcher::SearchBatch(const float *queries, common::idx_t nq, common::id
                               common::idx_t search_list_size, common::row_t *out_ids, float *out_dist,
                               uint32_t *out_count, lmd_stats *stats) {
 	if (mirror_ && mirror_->HasPending()) {
-		mirror_->Flush();
+		std::lock_guard<std::mutex> g(mu_);
+		if (mirror_->HasPending()) {
+			mirror_->Flush();
+		}
 	}
-	Check(lmd_search_batch(store_->Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
-	                       static_cast<uint32_t>(search_list_size), static_cast<uint32_t>(route_), 0, out_ids, out_dist,
-	                       out_count, nullptr, stats),
+	Check(lmd_ctx_search_batch(ThreadContext(), nullptr, queries, nq, static_cast<uint32_t>(k_neighbors),
+	                           static_cast<uint32_t>(search_list_size), static_cast<uint32_t>(route_), 0, out_ids,
+	                           out_dist, out_count, nullptr, stats),
 	      "GpuSearcher::Search");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+GpuSearcherGroup::GpuSearcherGroup(std::vector<std::shared_ptr<DeviceNodeStore>> stores, ShardMode mode,
+                                   GpuSearcher::Route route)
+    : stores_(std::move(stores)), mode_(mode), route_(route) {
+	if (stores_.empty()) {
+		throw ::duckdb::InternalException("GpuSearcherGroup requires at least one DeviceNodeStore");
+	}
+	std::vector<lmd_store *> handles;
+	for (auto &s : stores_) {
+		if (!s) {
+			throw ::duckdb::InternalException("GpuSearcherGroup: null DeviceNodeStore");
+		}
+		handles.push_back(s->Handle());
+	}
+	Check(lmd_group_create(handles.data(), static_cast<uint32_t>(handles.size()), static_cast<uint32_t>(mode), &group_),
+	      "GpuSearcherGroup");
+	if (mode_ == ShardMode::QUERY) {
+		for (auto &s : stores_) {
+			singles_.push_back(std::make_unique<GpuSearcher>(s, route_));
+		}
+	}
+}
+
+GpuSearcherGroup::~GpuSearcherGroup() {
+	singles_.clear();
+	if (group_) {
+		lmd_group_destroy(group_);
+	}
+}
+
+std::vector<std::shared_ptr<DeviceNodeStore>> GpuSearcherGroup::MirrorReplicas(
+    const core::LmDiskannConfig &config, const core::IStorageManager &storage, const core::IGraphManager &graph,
+    const std::vector<common::row_t> &row_ids, const std::vector<int> &devices, common::idx_t block_bytes) {
+	std::vector<std::shared_ptr<DeviceNodeStore>> out;
+	for (int dev : devices) {
+		auto s = std::make_shared<DeviceNodeStore>(config, row_ids.empty() ? 1 : row_ids.size(), dev, block_bytes);
+		s->MirrorFrom(storage, graph, row_ids);
+		s->SyncEntryPoint(graph);
+		out.push_back(std::move(s));
+	}
+	return out;
+}
+
+void GpuSearcherGroup::Search(const float *query_vector, const core::LmDiskannConfig &config,
+                              core::IGraphManager *graph_manager, common::idx_t k_neighbors,
+                              std::vector<common::row_t> &result_row_ids, common::idx_t search_list_size) {
+	result_row_ids.clear();
+	if (mode_ == ShardMode::QUERY) {
+		// one query cannot be split: it goes to one replica (round-robin spreads concurrent scans over the devices)
+		const uint64_t pick = next_.fetch_add(1, std::memory_order_relaxed) % singles_.size();
+		singles_[pick]->Search(query_vector, config, graph_manager, k_neighbors, result_row_ids, search_list_size);
+		return;
+	}
+	// shard-local entry points are part of each shard's store; the host graph manager has no single one to sync
+	common::idx_t L = search_list_size > 0 ? search_list_size : config.l_search;
+	if (L == 0) {
+		L = k_neighbors > 20 ? k_neighbors + 20 : 40; // core/Searcher.cpp:261-265
+	}
+	if (k_neighbors == 0) {
+		return;
+	}
+	std::vector<common::row_t> ids(k_neighbors);
+	uint32_t count = 0;
+	SearchBatch(query_vector, 1, k_neighbors, L, ids.data(), nullptr, &count, nullptr);
+	result_row_ids.assign(ids.begin(), ids.begin() + count);
+}
+
+common::idx_t GpuSearcherGroup::GetInMemorySize() const {
+	common::idx_t total = 0;
+	for (auto &s : stores_) {
+		total += s->DeviceBytes();
+	}
+	return total;
+}
+
+void GpuSearcherGroup::SearchForInitialCandidates(const float *new_node_vector, common::idx_t dimensions,
+                                                  const core::LmDiskannConfig &config,
+                                                  core::IGraphManager *graph_manager,
+                                                  common::idx_t num_candidates_to_find,
+                                                  common::IndexPointer current_entry_point,
+                                                  std::vector<common::row_t> &candidate_row_ids_out) {
+	candidate_row_ids_out.clear();
+	if (dimensions != config.dimensions || num_candidates_to_find == 0 || current_entry_point == common::IndexPointer()) {
+		return; // core/Searcher.cpp:74-77
+	}
+	Search(new_node_vector, config, graph_manager, num_candidates_to_find, candidate_row_ids_out,
+	       std::max<common::idx_t>(num_candidates_to_find, config.l_insert)); // core/Searcher.cpp:281-282
+}
+
+void GpuSearcherGroup::SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors,
+                                   common::idx_t search_list_size, common::row_t *out_ids, float *out_dist,
+                                   uint32_t *out_count, lmd_group_stats *stats) {
+	Check(lmd_group_search_batch(group_, queries, nq, static_cast<uint32_t>(k_neighbors),
+	                             static_cast<uint32_t>(search_list_size), static_cast<uint32_t>(route_), 0, out_ids,
+	                             out_dist, out_count, stats),
+	      "GpuSearcherGroup::SearchBatch");
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -447,7 +570,7 @@ common::idx_t GpuSearcher::SearchBatchFiltered(const AllowedIds &allowed, const 
 	if (widen) {
 		L = FilteredListSize(L, allowed.Count(), store_->NodeCount());
 	}
-	Check(lmd_search_batch_filtered(store_->Handle(), allowed.Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
+	Check(lmd_ctx_search_batch(ThreadContext(), allowed.Handle(), queries, nq, static_cast<uint32_t>(k_neighbors),
 	                                L, static_cast<uint32_t>(route_), 0, out_ids, out_dist, out_count, nullptr, nullptr),
 	      "GpuSearcher::SearchBatchFiltered");
 	const common::idx_t reachable = std::min<common::idx_t>(allowed.Count(), k_neighbors);
@@ -472,7 +595,7 @@ common::idx_t GpuSearcher::SearchBatchFiltered(const AllowedIds &allowed, const 
 		for (common::idx_t i = 0; i < m; i++) {
 			std::memcpy(sub_q.data() + i * dims, queries + shortq[i] * dims, dims * sizeof(float));
 		}
-		Check(lmd_search_batch_filtered(store_->Handle(), allowed.Handle(), sub_q.data(), m,
+		Check(lmd_ctx_search_batch(ThreadContext(), allowed.Handle(), sub_q.data(), m,
 		                                static_cast<uint32_t>(k_neighbors), L, static_cast<uint32_t>(route_), 0,
 		                                sub_ids.data(), sub_dist.data(), sub_cnt.data(), nullptr, nullptr),
 		      "GpuSearcher::SearchBatchFiltered");

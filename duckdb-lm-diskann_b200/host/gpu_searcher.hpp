@@ -26,9 +26,12 @@
 
 #include "lmd_b200.h"
 
+#include <atomic>
 #include <cstdint>
 #include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <unordered_set>
 #include <vector>
@@ -193,6 +196,7 @@ public:
 	enum class Route : uint32_t { EXACT = LMD_ROUTE_EXACT, TERNARY = LMD_ROUTE_TERNARY };
 
 	explicit GpuSearcher(std::shared_ptr<DeviceNodeStore> store, Route route = Route::EXACT);
+	~GpuSearcher() override;
 
 	// core/ISearcher.hpp:30-34. `graph_manager` is used only to keep the device entry point equal to the graph's
 	// (the traversal itself reads the mirror). One query = a batch of one.
@@ -237,11 +241,67 @@ public:
 	}
 
 private:
+	// The reference's Search takes no lock and DuckDB scans from many threads (db/LmDiskannIndex.cpp:677-724): every
+	// host thread gets its own lmd_ctx (stream, counters, scratch), so concurrent Search calls run side by side on the
+	// device instead of queueing on the store's default context.
+	lmd_ctx *ThreadContext();
+
 	std::shared_ptr<DeviceNodeStore> store_;
 	MirroredStorage *mirror_ = nullptr;
 	Route route_;
+	std::mutex mu_; // entry-point sync, mirror flush, the context table
+	std::unordered_map<std::thread::id, lmd_ctx *> contexts_;
 	common::row_t synced_entry_ = 0;
 	bool entry_synced_ = false;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// GpuSearcherGroup: the same seam over SEVERAL devices of this one process (lmd_group_*).
+//   QUERY    every store is a replica of the whole index; a batch is split into contiguous slices, one per device.
+//            A single Search() is one query and goes to ONE replica, chosen round-robin, through a per-thread context.
+//   DATASET  store s is shard s (shard-local graph, its own entry point, global row ids); every device searches the
+//            whole batch and one kernel merges the per-shard lists over NVLink peer loads. Search() is a batch of one.
+// ---------------------------------------------------------------------------------------------------------------
+class GpuSearcherGroup : public core::ISearcher {
+public:
+	enum class ShardMode : uint32_t { QUERY = LMD_GROUP_QUERY_SHARDED, DATASET = LMD_GROUP_DATASET_SHARDED };
+
+	GpuSearcherGroup(std::vector<std::shared_ptr<DeviceNodeStore>> stores, ShardMode mode,
+	                 GpuSearcher::Route route = GpuSearcher::Route::EXACT);
+	~GpuSearcherGroup() override;
+	// Replicas of one host index on `devices`: each mirrored through the reference's storage / graph interfaces.
+	static std::vector<std::shared_ptr<DeviceNodeStore>> MirrorReplicas(const core::LmDiskannConfig &config,
+	                                                                    const core::IStorageManager &storage,
+	                                                                    const core::IGraphManager &graph,
+	                                                                    const std::vector<common::row_t> &row_ids,
+	                                                                    const std::vector<int> &devices,
+	                                                                    common::idx_t block_bytes = 0);
+
+	void Search(const float *query_vector, const core::LmDiskannConfig &config, core::IGraphManager *graph_manager,
+	            common::idx_t k_neighbors, std::vector<common::row_t> &result_row_ids,
+	            common::idx_t search_list_size = 0) override;
+	common::idx_t GetInMemorySize() const override; // all devices together
+	void SearchForInitialCandidates(const float *new_node_vector, common::idx_t dimensions,
+	                                const core::LmDiskannConfig &config, core::IGraphManager *graph_manager,
+	                                common::idx_t num_candidates_to_find, common::IndexPointer current_entry_point,
+	                                std::vector<common::row_t> &candidate_row_ids_out) override;
+	// queries [nq][dims] -> out_ids [nq][k] (-1 padded), out_dist / out_count may be null; host or device pointers
+	void SearchBatch(const float *queries, common::idx_t nq, common::idx_t k_neighbors, common::idx_t search_list_size,
+	                 common::row_t *out_ids, float *out_dist, uint32_t *out_count, lmd_group_stats *stats = nullptr);
+	common::idx_t Members() const {
+		return stores_.size();
+	}
+	ShardMode Mode() const {
+		return mode_;
+	}
+
+private:
+	std::vector<std::shared_ptr<DeviceNodeStore>> stores_;
+	std::vector<std::unique_ptr<GpuSearcher>> singles_; // QUERY mode: one searcher per replica for point queries
+	ShardMode mode_;
+	GpuSearcher::Route route_;
+	lmd_group *group_ = nullptr;
+	std::atomic<uint64_t> next_{0};
 };
 
 // ---------------------------------------------------------------------------------------------------------------

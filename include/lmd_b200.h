@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define LMD_ABI_VERSION 2
+#define LMD_ABI_VERSION 3
 
 typedef int32_t lmd_status;
 enum {
@@ -226,6 +226,39 @@ lmd_status lmd_merge_topk(int device, const int64_t *ids, const float *dist, uin
  * round trip in between. */
 lmd_status lmd_merge_topk_async(int device, const int64_t *ids, const float *dist, uint32_t shards, uint64_t nq,
                                 uint32_t k, int64_t *out_ids, float *out_dist, void *cuda_stream);
+
+/* --- device groups: ONE process, several devices. The reference's host is a single multi-threaded
+ *     process and core/ISearcher.hpp:30-37 is the seam the searcher sits behind, so both multi-GPU modes are reachable
+ *     through the C ABI without one process per GPU:
+ *       LMD_GROUP_QUERY_SHARDED    every store holds the whole index (replicas on different devices); member g searches
+ *                                  queries [lo_g, hi_g) (contiguous, balanced) into that slice of the caller's buffers.
+ *       LMD_GROUP_DATASET_SHARDED  store s holds shard s (shard-local graph and entry point, global row ids); every
+ *                                  member searches the full batch, then one kernel on the first member's device reads
+ *                                  the G per-shard [nq][k] lists in place (NVLink peer loads) and keeps the k smallest by
+ *                                  (distance, row id): the all-gather and the merge of the multi-process path
+ *                                  (duckdb-lm-diskann_b200/sharded.py, NCCL) fused into one kernel.
+ *     The stores stay the caller's (create / upload / finalize them first; destroy them after the group). queries,
+ *     out_ids, out_dist (may be NULL), out_count (may be NULL): host (pinned or pageable) or device memory. The call
+ *     returns when the results are in the caller's buffers. --- */
+enum { LMD_GROUP_QUERY_SHARDED = 0, LMD_GROUP_DATASET_SHARDED = 1 };
+typedef struct {
+	uint32_t members, mode;
+	uint32_t peer_access;     /* bit i: the merge read member i's lists in place (same device or peer loads) */
+	uint32_t reserved;
+	uint64_t queries[16];     /* queries searched by member i */
+	float search_ms[16];      /* CUDA-event time of queries-in + search on member i's stream */
+	float search_ms_max;
+	float merge_ms;           /* dataset sharding: the gather + merge kernel */
+	float wall_ms;            /* host clock around the whole call */
+	uint32_t reserved2;
+	uint64_t merge_input_bytes; /* dataset sharding: G * nq * k * 12 */
+} lmd_group_stats;
+lmd_status lmd_group_create(lmd_store *const *stores, uint32_t n, uint32_t mode, lmd_group **out);
+lmd_status lmd_group_destroy(lmd_group *g);
+uint32_t lmd_group_size(const lmd_group *g);
+lmd_status lmd_group_search_batch(lmd_group *g, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
+                                  uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                                  lmd_group_stats *stats);
 
 /* --- graph write side: replaces core/GraphManager.cpp:65-203 (AddNode, one row at a
  *     time) and :259-457 (RobustPrune) by a batch-parallel build on the device. Writes the same node blocks, including

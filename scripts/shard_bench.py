@@ -27,55 +27,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def gen(n, dims, seed, device, normalize, latent=16, noise=0.05, chunk=1 << 20):
-    g = torch.Generator(device=device)
-    g.manual_seed(seed)
-    a = np.random.default_rng(7).standard_normal((dims, latent))
-    q, _ = np.linalg.qr(a)
-    proj = torch.from_numpy(q.T.astype(np.float32)).to(device)
-    out = torch.empty((n, dims), dtype=torch.float32, device=device)
-    for s in range(0, n, chunk):
-        e = min(n, s + chunk)
-        z = torch.randn((e - s, latent), generator=g, device=device)
-        out[s:e] = z @ proj + noise * torch.randn((e - s, dims), generator=g, device=device)
-    if normalize:
-        out /= out.norm(dim=1, keepdim=True).clamp_min(1e-12)
-    return out
-
-
-def topk_scores(x, q, k, metric, base_id, q_tile=2500, b_tile=1 << 19):
-    """(scores [nq,k], ids [nq,k]) of the k best rows of x per query; score is monotone in the metric's distance and
-    comparable across shards (L2: |x|^2 - 2 q.x; IP / COSINE with unit rows: -q.x)."""
-    old = torch.backends.cuda.matmul.allow_tf32
-    torch.backends.cuda.matmul.allow_tf32 = False
-    nq = q.shape[0]
-    S = torch.empty((nq, k), device=q.device)
-    I = torch.empty((nq, k), dtype=torch.int64, device=q.device)
-    for q0 in range(0, nq, q_tile):
-        a = q[q0:q0 + q_tile]
-        bs = bi = None
-        for b0 in range(0, x.shape[0], b_tile):
-            b = x[b0:b0 + b_tile]
-            s = a @ b.T
-            s = (b * b).sum(1)[None, :] - 2.0 * s if metric == "L2" else -s
-            ts, ti = torch.topk(s, min(k, b.shape[0]), dim=1, largest=False)
-            ti = ti + (b0 + base_id)
-            if bs is None:
-                bs, bi = ts, ti
-            else:
-                cs, ci = torch.cat([bs, ts], 1), torch.cat([bi, ti], 1)
-                bs, sel = torch.topk(cs, k, dim=1, largest=False)
-                bi = torch.gather(ci, 1, sel)
-        S[q0:q0 + q_tile], I[q0:q0 + q_tile] = bs, bi
-    torch.backends.cuda.matmul.allow_tf32 = old
-    return S, I
-
-
-def recall(found, truth):
-    f = found.unsqueeze(2) == truth.unsqueeze(1)
-    return float(f.any(dim=2).float().sum() / truth.numel())
-
-
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mode", default="sharded", choices=["sharded", "replicated"])
@@ -105,6 +56,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     lmd = importlib.import_module("duckdb-lm-diskann_b200")
     sh = importlib.import_module("duckdb-lm-diskann_b200.sharded")
+    wl = importlib.import_module("duckdb-lm-diskann_b200.workloads")
+    gen, topk_scores, recall = wl.gen, wl.topk_scores, wl.recall
     cos = a.metric == "COSINE"
     route = {"exact": lmd.ROUTE_EXACT, "ternary": lmd.ROUTE_TERNARY, "int8": lmd.ROUTE_INT8}[a.route]
 
@@ -140,7 +93,7 @@ def main():
 
     # ground truth: exact top-k per shard (or of the whole replica), merged across shards
     t0 = time.time()
-    S, I = topk_scores(x, q, a.k, a.metric, lo)
+    S, I = topk_scores(x, q, a.k, a.metric, base_id=lo)
     if a.mode == "sharded" and world > 1:
         allS = torch.empty((world,) + S.shape, device=dev)
         allI = torch.empty((world,) + I.shape, dtype=torch.int64, device=dev)

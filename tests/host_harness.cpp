@@ -10,9 +10,13 @@
 #include "core/GraphNode.hpp"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 
 using namespace diskann;
@@ -154,6 +158,16 @@ struct Host {
 	std::unique_ptr<core::ISearcher> searcher; // held through the reference's interface, as Coordinator.hpp:115-118 does
 	std::unique_ptr<b200::GpuIndexScan> scan;
 	bool loaded = true;
+};
+
+// Several devices behind ONE core::ISearcher (b200::GpuSearcherGroup): member i has its own storage / graph fakes (the
+// same index in QUERY mode, shard i in DATASET mode) and a DeviceNodeStore mirrored through them.
+struct GroupHost {
+	core::LmDiskannConfig cfg;
+	std::vector<std::unique_ptr<MemStorage>> storages;
+	std::vector<std::unique_ptr<MemGraph>> graphs;
+	std::unique_ptr<b200::GpuSearcherGroup> group;
+	core::ISearcher *searcher = nullptr; // the group through the reference's interface
 };
 
 // Growable storage for the live-index test: blocks handed out of one buffer, IndexPointer value = slot + 1.
@@ -535,6 +549,128 @@ int lmdlive_export(void *p, uint8_t *out_blocks, int64_t *out_row_ids, uint64_t 
 		                 ? common::NumericLimits<common::row_t>::Maximum()
 		                 : h->graph->GetEntryPointRowId();
 		*block_bytes_out = h->bb;
+	});
+}
+
+// ---- one searcher, many host threads (DuckDB scans from many threads; the reference's Search takes no lock) ----------
+// `threads` threads each run `per_thread` single-query core::ISearcher::Search calls; returns wall seconds, and the number
+// of answers that differ from `expect` [nq][k] (-1 padded) in *mismatch.
+int lmdhost_concurrent_searches(void *p, const float *queries, uint64_t nq, uint64_t dims, uint64_t k, uint64_t L,
+                                uint32_t threads, uint64_t per_thread, const int64_t *expect, double *seconds,
+                                uint64_t *mismatch) {
+	Host *h = static_cast<Host *>(p);
+	return Guard([&]() {
+		std::atomic<uint64_t> bad{0};
+		std::atomic<int> failed{0};
+		std::string first_error;
+		std::mutex err_mu;
+		{ // warm every thread's context outside the timed region is not possible (threads are new): time includes it
+		}
+		const auto t0 = std::chrono::steady_clock::now();
+		std::vector<std::thread> pool;
+		for (uint32_t t = 0; t < threads; t++) {
+			pool.emplace_back([&, t]() {
+				try {
+					std::vector<common::row_t> res;
+					for (uint64_t i = 0; i < per_thread; i++) {
+						const uint64_t q = (t * 7919ull + i) % nq;
+						h->searcher->Search(queries + q * dims, h->cfg, h->graph.get(), k, res, L);
+						if (expect) {
+							for (uint64_t j = 0; j < k; j++) {
+								const int64_t want = expect[q * k + j];
+								const int64_t got = j < res.size() ? res[j] : -1;
+								if (want != got) {
+									bad++;
+									break;
+								}
+							}
+						}
+					}
+				} catch (const std::exception &e) {
+					std::lock_guard<std::mutex> g(err_mu);
+					if (!failed.exchange(1)) {
+						first_error = e.what();
+					}
+				}
+			});
+		}
+		for (auto &th : pool) {
+			th.join();
+		}
+		*seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+		*mismatch = bad.load();
+		if (failed.load()) {
+			throw std::runtime_error(first_error);
+		}
+	});
+}
+
+// ---- device groups ------------------------------------------------------------------------------------------------
+// members: blocks[i] (n[i] blocks), row_ids[i] (may be null), entry_rows[i], devices[i]. mode 0 = QUERY, 1 = DATASET.
+void *lmdgroup_create(const uint8_t *const *blocks, const uint64_t *n, uint64_t block_bytes, const int64_t *const *row_ids,
+                      const int64_t *entry_rows, uint32_t members, const int *devices, int mode, int metric, int vec_type,
+                      uint64_t dims, uint32_t r, uint32_t l_search, int route) {
+	GroupHost *out = nullptr;
+	int rc = Guard([&]() {
+		auto g = std::make_unique<GroupHost>();
+		g->cfg.metric_type = static_cast<common::LmDiskannMetricType>(metric);
+		g->cfg.node_vector_type = static_cast<common::LmDiskannVectorType>(vec_type);
+		g->cfg.dimensions = dims;
+		g->cfg.r = r;
+		g->cfg.l_search = l_search;
+		core::NodeLayoutOffsets lay = core::CalculateLayoutInternal(g->cfg);
+		std::vector<std::shared_ptr<b200::DeviceNodeStore>> stores;
+		for (uint32_t i = 0; i < members; i++) {
+			g->storages.push_back(std::make_unique<MemStorage>(blocks[i], n[i], block_bytes));
+			g->graphs.push_back(std::make_unique<MemGraph>(g->storages.back().get(), lay, row_ids ? row_ids[i] : nullptr,
+			                                               n[i], entry_rows[i]));
+			std::vector<common::row_t> all(n[i]);
+			for (uint64_t j = 0; j < n[i]; j++) {
+				all[j] = (row_ids && row_ids[i]) ? row_ids[i][j] : (int64_t)j;
+			}
+			auto one = b200::GpuSearcherGroup::MirrorReplicas(g->cfg, *g->storages.back(), *g->graphs.back(), all,
+			                                                  {devices[i]}, block_bytes);
+			stores.push_back(one[0]);
+		}
+		g->group = std::make_unique<b200::GpuSearcherGroup>(
+		    std::move(stores), mode ? b200::GpuSearcherGroup::ShardMode::DATASET : b200::GpuSearcherGroup::ShardMode::QUERY,
+		    route ? b200::GpuSearcher::Route::TERNARY : b200::GpuSearcher::Route::EXACT);
+		g->searcher = g->group.get();
+		out = g.release();
+	});
+	return rc == 0 ? out : nullptr;
+}
+
+void lmdgroup_destroy(void *p) {
+	delete static_cast<GroupHost *>(p);
+}
+
+uint64_t lmdgroup_in_memory_size(void *p) {
+	return static_cast<GroupHost *>(p)->searcher->GetInMemorySize();
+}
+
+int lmdgroup_search_batch(void *p, const float *queries, uint64_t nq, uint64_t k, uint64_t L, int64_t *out_ids,
+                          float *out_dist, uint32_t *out_count, float *ms3) {
+	GroupHost *g = static_cast<GroupHost *>(p);
+	return Guard([&]() {
+		lmd_group_stats st;
+		g->group->SearchBatch(queries, nq, k, L, out_ids, out_dist, out_count, &st);
+		if (ms3) {
+			ms3[0] = st.search_ms_max;
+			ms3[1] = st.merge_ms;
+			ms3[2] = st.wall_ms;
+		}
+	});
+}
+
+// core::ISearcher::Search through the virtual interface (one query)
+int lmdgroup_isearcher_search(void *p, const float *query, uint64_t k, uint64_t L, int64_t *out_ids, uint64_t *out_n) {
+	GroupHost *g = static_cast<GroupHost *>(p);
+	return Guard([&]() {
+		std::vector<common::row_t> res;
+		g->searcher->Search(query, g->cfg, g->graphs[0].get(), k, res, L);
+		*out_n = res.size();
+		std::copy(res.begin(), res.end(), out_ids);
 	});
 }
 

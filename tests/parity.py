@@ -39,3 +39,39 @@ def check_parity(ids_g, dist_g, cnt_g, ids_o, dist_o, cnt_o, tol=REL_TOL, what="
             what, q, j, ids_g[q, j], ids_o[q, j], d)
         ties += 1
     return ties, int(valid.sum())
+
+
+def parity_report(ids_g, dist_g, ids_o, dist_o, cnt_o, tol=REL_TOL):
+    """The same rules as check_parity() as COUNTS instead of assertions (bench.py prints them for the whole batch).
+    A differing id is "inside a tie" when the distance at that rank agrees to `tol` and the oracle's own neighbour at
+    rank j-1 / j+1 is within `tol` of it (or the rank is the k-th boundary); everything else is "outside ties"."""
+    ids_g, ids_o = np.asarray(ids_g), np.asarray(ids_o)
+    dist_g, dist_o = np.asarray(dist_g), np.asarray(dist_o)
+    valid = (ids_o >= 0) & (ids_g >= 0)
+    same = ids_g == ids_o
+    diff = ~same & ((ids_o >= 0) | (ids_g >= 0))
+    denom = np.maximum(np.maximum(np.abs(dist_g), np.abs(dist_o)).astype(np.float64), 1e-30)
+    rel = np.abs(dist_g.astype(np.float64) - dist_o.astype(np.float64)) / denom
+    rel_same = rel[same & valid]
+    inside = outside = 0
+    bad_q = set()
+    for q, j in np.argwhere(diff):
+        ok = bool(valid[q, j]) and bool(rel_close(dist_g[q, j], dist_o[q, j], tol))
+        if ok:
+            near = j == ids_o.shape[1] - 1 or j == int(cnt_o[q]) - 1
+            d = float(dist_o[q, j])
+            for jj in (j - 1, j + 1):
+                if 0 <= jj < ids_o.shape[1] and ids_o[q, jj] >= 0 and rel_close(dist_o[q, jj], d, tol):
+                    near = True
+            ok = near
+        if ok:
+            inside += 1
+        else:
+            outside += 1
+            bad_q.add(int(q))
+    return {"queries": int(ids_o.shape[0]),
+            "id_identical_queries": int(same.all(axis=1).sum()),
+            "id_mismatch_inside_ties": inside,
+            "id_mismatch_outside_ties": outside,
+            "queries_with_mismatch_outside_ties": len(bad_q),
+            "dist_max_rel_err": float(rel_same.max()) if rel_same.size else 0.0}

@@ -22,7 +22,7 @@ def test_header_symbols_exported(lmd):
     for n in names:
         assert hasattr(l, n), "liblmd_b200.so does not export %s" % n
     assert set(n for n, _, _ in lmd.SYMBOLS) == set(names), "python binding and header disagree"
-    assert lmd.lib().lmd_abi_version() == 2
+    assert lmd.lib().lmd_abi_version() == 3
 
 
 def test_header_is_plain_c(tmp_path):

