@@ -171,7 +171,9 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 		return LMD_ERR_INVALID_ARG;
 	}
 
-	if (!async) {
+	// the events only feed lmd_stats: a call without statistics (every point query of the adapter) skips five driver calls
+	const bool timed = !async && stats != nullptr;
+	if (timed) {
 		LMD_CUDA_OK(cudaEventRecord(ss.ev[0], st));
 	}
 	const float *d_q = static_cast<const float *>(a_q);
@@ -259,13 +261,13 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 	ta.strict = (flags & LMD_SEARCH_STRICT_FP) != 0;
 	ta.no_prefilter = (flags & LMD_SEARCH_NO_PREFILTER) != 0;
 	ta.d_counters = ss.d_counters;
-	if (!async) {
+	if (timed) {
 		LMD_CUDA_OK(cudaEventRecord(ss.ev[1], st));
 	}
 	if ((rc = launch_traverse(ta, st)) != LMD_OK) {
 		return rc;
 	}
-	if (!async) {
+	if (timed) {
 		LMD_CUDA_OK(cudaEventRecord(ss.ev[2], st));
 	}
 	uint32_t launches = 1;
@@ -291,7 +293,9 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 	if (async) {
 		return LMD_OK;
 	}
-	LMD_CUDA_OK(cudaEventRecord(ss.ev[3], st));
+	if (timed) {
+		LMD_CUDA_OK(cudaEventRecord(ss.ev[3], st));
+	}
 	if (stage_out && !pin_out) {
 		LMD_CUDA_OK(cudaMemcpyAsync(out_ids, d_ids, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
 		if (out_dist) {
@@ -308,7 +312,9 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 	if (stats) {
 		LMD_CUDA_OK(cudaMemcpyAsync(h_cnt, ss.d_counters, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
 	}
-	LMD_CUDA_OK(cudaEventRecord(ss.ev[4], st));
+	if (timed) {
+		LMD_CUDA_OK(cudaEventRecord(ss.ev[4], st));
+	}
 	cudaError_t e = cudaStreamSynchronize(st);
 	if (e != cudaSuccess) {
 		set_error("search kernels failed: %s", cudaGetErrorString(e));

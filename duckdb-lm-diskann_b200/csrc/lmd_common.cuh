@@ -38,7 +38,11 @@ void set_error(const char *fmt, ...);
 // (core/Searcher.cpp:35-37 + oracle/patches/searcher_fixed.patch).
 __host__ __device__ __forceinline__ uint32_t float_to_ordered(float f) {
 #ifdef __CUDA_ARCH__
-	uint32_t b = __float_as_uint(f);
+	// The bits are taken through an opaque move: given `__float_as_uint(f) | 0x80000000` the compiler emits
+	// neg.f32(abs.f32(f)), and PTX's abs / neg do not preserve a NaN's bits (a NaN distance came back as -0.0 and sorted
+	// first; tests/test_gpu_round2.py::test_special_values). Keys are integers from here on.
+	uint32_t b;
+	asm("mov.b32 %0, %1;" : "=r"(b) : "f"(f));
 #else
 	union {
 		float f;
@@ -52,7 +56,9 @@ __host__ __device__ __forceinline__ uint32_t float_to_ordered(float f) {
 __host__ __device__ __forceinline__ float ordered_to_float(uint32_t o) {
 	uint32_t b = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
 #ifdef __CUDA_ARCH__
-	return __uint_as_float(b);
+	float f; // opaque for the same reason (and / fabs)
+	asm("mov.b32 %0, %1;" : "=f"(f) : "r"(b));
+	return f;
 #else
 	union {
 		float f;
@@ -78,7 +84,7 @@ struct Tuning {
 	int filter_mode = -1;  // -1 = auto (1 when the store is small enough), 0 = u32 open addressing, 1 = 16-bit buckets
 	int warps_per_cta = 0; // 0 = whichever of 4 / 2 / 1 packs the most warps on an SM
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows
-	int tie_slots = -1;    // -1 = default (64 for ternary routing, 0 for exact)
+	int tie_slots = -1;    // -1 = default (plan_tie_slots(L) for the integer-valued routes, 32 under strict fp, else 0)
 	int prefetch_planes = 1; // ternary routing: prefetch the plane region of the likely next expansion into L2
 	int latency_mode = -1; // -1 = latency kernels for batches below ~10 queries per SM, 0 = never, 1 = always
 	int merge_min = 0;     // batch-merge new candidates when at least this many pass the threshold (0 = default 5)

@@ -105,14 +105,31 @@ inline int plan_family(uint32_t nq, uint32_t sm_count, int tune) {
 
 // Warps the chosen kernels want resident on an SM; the visited filter is shrunk until that many fit (DESIGN.md 6,
 // "Long lists"). `specialised` = 128-d or 96-d rows; `lpl` = list entries / 32 after rounding to the family's sizes.
-inline uint32_t plan_min_warps(int family, bool exact, bool specialised, bool filtered, int lpl) {
+//
+// The routes that read a sidecar block (ternary planes, int8 codes) are bound by instruction issue, not by bandwidth
+// (ncu: issue slots 48 % busy, no eligible warp 50 % of the cycles at 22-27 resident warps, profiles/r2_04_*): they want
+// 32 warps on an SM more than a filter that never forgets. Measured on 1 M rows, 10 k queries (profiles/r2_05_*_occ.json):
+// int8 route L = 56 0.80 -> 0.65 ms, ternary 768-d L = 80 1.91 -> 1.48 ms with the 4 KB filter and the short tie region
+// below. Longer lists keep the old rule (their filters would forget too much at 4 KB).
+inline uint32_t plan_min_warps(int family, bool exact, bool specialised, bool filtered, int lpl, uint32_t L = 0) {
 	if (family == 1) {
 		return 12;
 	}
 	if (family == 2) {
 		return 16;
 	}
+	if (!exact && !filtered && L > 0 && L <= 96) {
+		return 32;
+	}
 	return exact && specialised && (!filtered || lpl <= 4) ? 24u : 16u;
+}
+
+// Room behind the top L for distance ties on the integer-valued routes (ternary scores, int8 code distances tie all the
+// time; see list_insert): at least 8 entries, then whatever the list class (a multiple of 32 entries) leaves - a region
+// of 64 put L = 56 into the 128-entry class and doubled the cost of every list operation for 0 overflows fewer.
+inline uint32_t plan_tie_slots(uint32_t L) {
+	const int lpl = lpl_for(L + 8);
+	return lpl ? (uint32_t)lpl * 32u - L : 0u;
 }
 
 // 96-d rows (384 bytes): the G = 4 kernels also win on full batches when shared memory holds the G = 2 kernel at 24 warps

@@ -212,7 +212,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// ... and, under LMD_SEARCH_STRICT_FP, whenever two different sums round to the same sqrtf (about once per thousand
 	// queries at L = 64): the oracle expands such an entry, so strict parity of the expansion counts needs the region too
 	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots
-	                                            : (a.route != LMD_ROUTE_EXACT ? 64u : (p.strict ? 32u : 0u));
+	                                            : (a.route != LMD_ROUTE_EXACT ? plan_tie_slots(a.L) : (p.strict ? 32u : 0u));
 	// exact routing on a store with the int8 codec: the codes decide which rows are fetched (same results, fewer bytes)
 	uint32_t kroute = a.route;
 	if (a.route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && s->codes_gen == s->views_gen && !a.no_prefilter &&
@@ -272,7 +272,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// 1 M x 128, L = 128, 16 KB against 4 KB: 1 query 383 -> 348 us, 1 024 queries 564 -> 524 us
 	// (profiles/r50_small_batch_L128.json).
 	const bool exact = a.route == LMD_ROUTE_EXACT; // (with or without the pre-filter: rows are gathered either way)
-	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl);
+	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl, a.L);
 	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps, s->tune.filter_mode,
 	                                  (int)s->tune.filter_log2);
 	if (kroute == LMD_ROUTE_EXACT && !p.strict && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {

@@ -383,10 +383,84 @@ void GpuSearcher::Search(const float *query_vector, const core::LmDiskannConfig 
 	if (k_neighbors == 0) {
 		return; // PerformSearch with k = 0 keeps nothing (core/Searcher.cpp:224-227)
 	}
-	std::vector<common::row_t> ids(k_neighbors);
-	uint32_t count = 0;
-	SearchBatch(query_vector, 1, k_neighbors, L, ids.data(), nullptr, &count, nullptr);
-	result_row_ids.assign(ids.begin(), ids.begin() + count);
+	if (!combine_) {
+		std::vector<common::row_t> ids(k_neighbors);
+		uint32_t count = 0;
+		SearchBatch(query_vector, 1, k_neighbors, L, ids.data(), nullptr, &count, nullptr);
+		result_row_ids.assign(ids.begin(), ids.begin() + count);
+		return;
+	}
+	// Flat combining: queue the request; whoever finds no leader becomes one and carries everything queued so far.
+	PendingSearch mine {query_vector, k_neighbors, L, &result_row_ids};
+	std::unique_lock<std::mutex> lk(comb_mu_);
+	comb_queue_.push_back(&mine);
+	while (!mine.done) {
+		if (!comb_leader_) {
+			comb_leader_ = true;
+			std::vector<PendingSearch *> batch;
+			batch.swap(comb_queue_);
+			lk.unlock();
+			LeadBatch(batch); // never throws: errors are stored per request
+			lk.lock();
+			for (auto *p : batch) {
+				p->done = true;
+			}
+			comb_leader_ = false;
+			comb_cv_.notify_all();
+		} else {
+			comb_cv_.wait(lk);
+		}
+	}
+	lk.unlock();
+	if (mine.error) {
+		std::rethrow_exception(mine.error);
+	}
+}
+
+// One device launch per distinct (k, L) among the queued requests (normally one: scans of a session share both).
+void GpuSearcher::LeadBatch(std::vector<PendingSearch *> &batch) {
+	const common::idx_t dims = store_->Config().dimensions;
+	std::vector<bool> taken(batch.size(), false);
+	std::vector<float> queries;
+	std::vector<common::row_t> ids;
+	std::vector<uint32_t> counts;
+	std::vector<size_t> members;
+	for (size_t first = 0; first < batch.size(); first++) {
+		if (taken[first]) {
+			continue;
+		}
+		members.clear();
+		for (size_t i = first; i < batch.size(); i++) {
+			if (!taken[i] && batch[i]->k == batch[first]->k && batch[i]->L == batch[first]->L) {
+				taken[i] = true;
+				members.push_back(i);
+			}
+		}
+		const common::idx_t k = batch[first]->k, n = members.size();
+		try {
+			const float *q = batch[first]->query;
+			if (n > 1) {
+				queries.resize(n * dims);
+				for (size_t m = 0; m < n; m++) {
+					std::memcpy(queries.data() + m * dims, batch[members[m]]->query, dims * sizeof(float));
+				}
+				q = queries.data();
+			}
+			ids.assign(n * k, -1);
+			counts.assign(n, 0);
+			SearchBatch(q, n, k, batch[first]->L, ids.data(), nullptr, counts.data(), nullptr);
+			for (size_t m = 0; m < n; m++) {
+				auto &out = *batch[members[m]]->out;
+				out.assign(ids.begin() + m * k, ids.begin() + m * k + counts[m]);
+			}
+			comb_batches_.fetch_add(1, std::memory_order_relaxed);
+			comb_queries_.fetch_add(n, std::memory_order_relaxed);
+		} catch (...) {
+			for (size_t m : members) {
+				batch[m]->error = std::current_exception();
+			}
+		}
+	}
 }
 
 common::idx_t GpuSearcher::GetInMemorySize() const {
@@ -683,7 +757,7 @@ common::idx_t GpuIndexScan::Scan(GpuScanState &state, common::row_t *result, com
 			                     state.result_row_ids, state.l_search);
 			state.searched = true;
 		}
-		const common::idx_t cap = std::min<common::idx_t>(result_capacity, STANDARD_VECTOR_SIZE);
+		const common::idx_t cap = std::min<common::idx_t>(result_capacity, VECTOR_SIZE);
 		output_count = std::min<common::idx_t>(cap, state.result_row_ids.size());
 		std::copy(state.result_row_ids.begin(), state.result_row_ids.begin() + output_count, result);
 		state.result_row_ids.erase(state.result_row_ids.begin(), state.result_row_ids.begin() + output_count);

@@ -28,6 +28,7 @@
 
 #include <atomic>
 #include <cstdint>
+#include <condition_variable>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -239,6 +240,17 @@ public:
 	void AttachLiveMirror(MirroredStorage *mirror) {
 		mirror_ = mirror;
 	}
+	// Concurrent Search() calls (DuckDB scans from many threads) are COMBINED: while one thread's search is on the
+	// device, the calls that arrive wait, and the first of them then carries all of them as ONE batch. A lone caller
+	// pays nothing (it leads immediately, batch of one). false = every call goes to the device on its own context.
+	void SetCombining(bool on) {
+		combine_ = on;
+	}
+	// Batches led so far and queries they carried (statistics: queries / batches = the combining factor)
+	void CombiningStats(uint64_t &batches, uint64_t &queries) const {
+		batches = comb_batches_.load();
+		queries = comb_queries_.load();
+	}
 
 private:
 	// The reference's Search takes no lock and DuckDB scans from many threads (db/LmDiskannIndex.cpp:677-724): every
@@ -253,6 +265,22 @@ private:
 	std::unordered_map<std::thread::id, lmd_ctx *> contexts_;
 	common::row_t synced_entry_ = 0;
 	bool entry_synced_ = false;
+
+	// flat combining of single-query searches
+	struct PendingSearch {
+		const float *query;
+		common::idx_t k, L;
+		std::vector<common::row_t> *out;
+		bool done = false;
+		std::exception_ptr error;
+	};
+	void LeadBatch(std::vector<PendingSearch *> &batch);
+	bool combine_ = true;
+	std::mutex comb_mu_;
+	std::condition_variable comb_cv_;
+	std::vector<PendingSearch *> comb_queue_;
+	bool comb_leader_ = false;
+	std::atomic<uint64_t> comb_batches_{0}, comb_queries_{0};
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -327,7 +355,12 @@ struct GpuScanState {
 
 class GpuIndexScan {
 public:
-	static constexpr common::idx_t STANDARD_VECTOR_SIZE = 2048; // DuckDB v1.2.x
+	// DuckDB's STANDARD_VECTOR_SIZE (a macro in vector_size.hpp, 2048 in v1.2.x): used when its headers are present
+#ifdef STANDARD_VECTOR_SIZE
+	static constexpr common::idx_t VECTOR_SIZE = STANDARD_VECTOR_SIZE;
+#else
+	static constexpr common::idx_t VECTOR_SIZE = 2048;
+#endif
 
 	GpuIndexScan(core::ISearcher *searcher, core::IGraphManager *graph_manager, const core::LmDiskannConfig &config)
 	    : searcher_(searcher), graph_(graph_manager), config_(config) {
@@ -336,7 +369,7 @@ public:
 	std::unique_ptr<GpuScanState> InitializeScan(const float *query, common::idx_t query_dims, common::idx_t k) const;
 	// db/LmDiskannIndex.cpp:677-724: up to STANDARD_VECTOR_SIZE row ids per call, 0 when drained; errors rewrapped
 	// as IOException("Error during LM_DISKANN scan: ...")
-	common::idx_t Scan(GpuScanState &state, common::row_t *result, common::idx_t result_capacity = STANDARD_VECTOR_SIZE);
+	common::idx_t Scan(GpuScanState &state, common::row_t *result, common::idx_t result_capacity = VECTOR_SIZE);
 	// Batch form of the template's index join (hnsw_optimize_join.cpp:113-170): nq scans with the same k in one
 	// device launch; out [nq][k], -1 padded.
 	void MultiScan(const float *queries, common::idx_t nq, common::idx_t query_dims, common::idx_t k,

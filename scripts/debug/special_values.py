@@ -15,10 +15,13 @@ nbrs = np.full((n, r), -1, dtype=np.int64); nbrs[0, :n - 1] = np.arange(1, n)
 counts = np.zeros(n, dtype=np.int64); counts[0] = n - 1
 blocks = fx.pack_blocks(x, nbrs, counts, r).numpy()
 lay = fx.layout(dims, r)
+TUNE = [t.split("=") for t in sys.argv[1:]]
 for metric in (1, 3):
     for flags in (0, lmd.SEARCH_SEPARATE_RERANK, lmd.SEARCH_STRICT_FP):
         with lmd.Store(dims, r, metric=metric, capacity=n) as s:
             s.upload(blocks); s.set_entry(0)
+            for key, val in TUNE:
+                s.set_tuning(key, int(val))
             ids, dist, cnt, st = s.search(q, 40, 40, flags=flags)
         o = pyoracle.search(blocks, lay["block_bytes"], dims, r, q, 40, 40, metric=metric, entry_row_id=0)
         print("metric", metric, "flags", flags, "cnt", cnt, o[2])
@@ -26,4 +29,4 @@ for metric in (1, 3):
             print(" ours  ", [(int(i), hex(int(b))) for i, b in zip(ids[qi, 28:34], dist[qi, 28:34].view(np.uint32))])
             print(" oracle", [(int(i), hex(int(b))) for i, b in zip(o[0][qi, 28:34], o[1][qi, 28:34].view(np.uint32))])
             w = {int(i): d for i, d in zip(ids[qi, :n], dist[qi, :n])}
-            print("  row 8, 10 ours:", w.get(8), w.get(10))
+            print("  row 8, 10 ours:", w.get(8), w.get(10), "positions", list(ids[qi, :n]).index(8), list(ids[qi, :n]).index(10))

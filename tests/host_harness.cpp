@@ -605,6 +605,19 @@ int lmdhost_concurrent_searches(void *p, const float *queries, uint64_t nq, uint
 	});
 }
 
+void lmdhost_set_combining(void *p, int on) {
+	if (auto *g = dynamic_cast<b200::GpuSearcher *>(static_cast<Host *>(p)->searcher.get())) {
+		g->SetCombining(on != 0);
+	}
+}
+
+void lmdhost_combining_stats(void *p, uint64_t *batches, uint64_t *queries) {
+	*batches = *queries = 0;
+	if (auto *g = dynamic_cast<b200::GpuSearcher *>(static_cast<Host *>(p)->searcher.get())) {
+		g->CombiningStats(*batches, *queries);
+	}
+}
+
 // ---- device groups ------------------------------------------------------------------------------------------------
 // members: blocks[i] (n[i] blocks), row_ids[i] (may be null), entry_rows[i], devices[i]. mode 0 = QUERY, 1 = DATASET.
 void *lmdgroup_create(const uint8_t *const *blocks, const uint64_t *n, uint64_t block_bytes, const int64_t *const *row_ids,

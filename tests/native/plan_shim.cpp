@@ -14,6 +14,12 @@ int plan_family(uint32_t nq, uint32_t sm_count, int tune) {
 uint32_t plan_min_warps(int family, int exact, int specialised, int filtered, int lpl) {
 	return lmd::plan_min_warps(family, exact != 0, specialised != 0, filtered != 0, lpl);
 }
+uint32_t plan_min_warps_l(int family, int exact, int specialised, int filtered, int lpl, uint32_t L) {
+	return lmd::plan_min_warps(family, exact != 0, specialised != 0, filtered != 0, lpl, L);
+}
+uint32_t plan_tie_slots(uint32_t L) {
+	return lmd::plan_tie_slots(L);
+}
 int plan_96d_prefers_g4(uint32_t row_floats, int exact, int filtered, int family, int tune, int lpl, uint32_t filter_bytes) {
 	return lmd::plan_96d_prefers_g4(row_floats, exact != 0, filtered != 0, family, tune, lpl, filter_bytes) ? 1 : 0;
 }

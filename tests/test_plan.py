@@ -94,3 +94,22 @@ def test_96d_rows_take_g4_only_with_the_8kb_filter(plan):
     assert plan.plan_96d_prefers_g4(128, 1, 0, 0, -1, 2, 8192) == 0     # 128-d rows prefer G = 2 everywhere
     assert plan.plan_96d_prefers_g4(96, 1, 1, 0, -1, 2, 8192) == 0      # filtered
     assert plan.plan_96d_prefers_g4(96, 1, 0, 0, 0, 2, 8192) == 0       # latency_mode forced to the throughput kernels
+
+
+def test_sidecar_routes_want_32_warps_and_a_short_tie_region(plan):
+    """Round 2 (profiles/r2_05_*_occ.json): ternary / int8 routing up to L = 96 shrinks the visited filter until 32 warps
+    fit on an SM, and keeps the tie region inside the list class L falls into (at least 8 entries)."""
+    plan.plan_min_warps_l.restype = ctypes.c_uint32
+    plan.plan_tie_slots.restype = ctypes.c_uint32
+    assert plan.plan_min_warps_l(0, 0, 1, 0, 2, 56) == 32     # int8 / ternary route, L = 56
+    assert plan.plan_min_warps_l(0, 0, 0, 0, 3, 80) == 32     # ternary 768-d, L = 80
+    assert plan.plan_min_warps_l(0, 0, 1, 0, 4, 128) == 16    # long lists keep the old rule
+    assert plan.plan_min_warps_l(0, 0, 1, 1, 2, 56) == 16     # filtered kernels too
+    assert plan.plan_min_warps_l(0, 1, 1, 0, 2, 56) == 24     # exact routing: unchanged
+    assert [plan.plan_tie_slots(L) for L in (32, 56, 64, 80, 96, 120, 128, 250, 504, 512)] == \
+        [32, 8, 32, 16, 32, 8, 64, 134, 8, 0]
+    # the 4 KB filter is what the 32-warp budget leaves at L = 56 (list 512 B + 384 B + the int8 query image)
+    assert _filter(plan, 1_000_000, 56, 2, 32)[1:] == (11, 4096)
+    out = (ctypes.c_uint32 * 3)()  # ternary planes of 12 words; the pre-sidecar 2 KB cap ("plane_filter_cap") is off
+    plan.plan_filter(1_000_000, 32, 12, 80, _fixed(3, words=12, ternary=True), 0, 32, -1, 0, out)
+    assert tuple(out)[1:] == (11, 4096)
