@@ -399,7 +399,7 @@ def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64):
            "store_GB_per_gpu_blocks_released": round(store.device_bytes / 1e9, 2),
            "nccl_ranks": J.dist.get_world_size(), "allgather_bytes_per_rank": nq * k * 12, "runs": []}
     store.set_stream(J.stream.cuda_stream)
-    searcher = sh.DatasetShardedSearcher(store, device=J.dev)
+    searcher = sh.DatasetShardedSearcher(store, device=torch.device(J.dev))
     ids = torch.empty((nq, k), dtype=torch.int64, device=J.dev)
     dd = torch.empty((nq, k), dtype=torch.float32, device=J.dev)
     for L in Ls:

@@ -390,22 +390,27 @@ void GpuSearcher::Search(const float *query_vector, const core::LmDiskannConfig 
 		result_row_ids.assign(ids.begin(), ids.begin() + count);
 		return;
 	}
-	// Flat combining: queue the request; whoever finds no leader becomes one and carries everything queued so far.
+	// Combining: up to MAX_LEADERS searches are on the device at once, each on its thread's own context (that alone
+	// scales to ~16-32 host threads, profiles/r2_06_concurrent_point_queries.json); a call that finds every leader slot
+	// taken queues, and the next free leader carries everything queued so far as ONE batch.
 	PendingSearch mine {query_vector, k_neighbors, L, &result_row_ids};
 	std::unique_lock<std::mutex> lk(comb_mu_);
 	comb_queue_.push_back(&mine);
 	while (!mine.done) {
-		if (!comb_leader_) {
-			comb_leader_ = true;
+		if (!mine.taken && comb_leaders_ < MAX_LEADERS) {
+			comb_leaders_++;
 			std::vector<PendingSearch *> batch;
 			batch.swap(comb_queue_);
+			for (auto *p : batch) {
+				p->taken = true;
+			}
 			lk.unlock();
 			LeadBatch(batch); // never throws: errors are stored per request
 			lk.lock();
 			for (auto *p : batch) {
 				p->done = true;
 			}
-			comb_leader_ = false;
+			comb_leaders_--;
 			comb_cv_.notify_all();
 		} else {
 			comb_cv_.wait(lk);

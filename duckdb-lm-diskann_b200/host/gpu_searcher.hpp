@@ -240,9 +240,9 @@ public:
 	void AttachLiveMirror(MirroredStorage *mirror) {
 		mirror_ = mirror;
 	}
-	// Concurrent Search() calls (DuckDB scans from many threads) are COMBINED: while one thread's search is on the
-	// device, the calls that arrive wait, and the first of them then carries all of them as ONE batch. A lone caller
-	// pays nothing (it leads immediately, batch of one). false = every call goes to the device on its own context.
+	// Concurrent Search() calls (DuckDB scans from many threads): up to MAX_LEADERS of them are on the device side by
+	// side, each through its thread's own lmd_ctx; calls beyond that wait, and the next free leader carries all of them as
+	// ONE batch. A lone caller pays nothing. false = every call goes to the device on its own context, however many.
 	void SetCombining(bool on) {
 		combine_ = on;
 	}
@@ -271,15 +271,16 @@ private:
 		const float *query;
 		common::idx_t k, L;
 		std::vector<common::row_t> *out;
-		bool done = false;
+		bool taken = false, done = false; // taken: part of some leader's batch
 		std::exception_ptr error;
 	};
+	static constexpr int MAX_LEADERS = 16;
 	void LeadBatch(std::vector<PendingSearch *> &batch);
 	bool combine_ = true;
 	std::mutex comb_mu_;
 	std::condition_variable comb_cv_;
 	std::vector<PendingSearch *> comb_queue_;
-	bool comb_leader_ = false;
+	int comb_leaders_ = 0;
 	std::atomic<uint64_t> comb_batches_{0}, comb_queries_{0};
 };
 
