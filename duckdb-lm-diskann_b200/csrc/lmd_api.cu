@@ -131,9 +131,10 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 		set_error("the int8 edge codec is defined for the L2 metric only");
 		return LMD_ERR_UNSUPPORTED;
 	}
-	while (!route_ready(s, route)) {
+	const uint32_t prep = route | ((flags & LMD_SEARCH_TENSOR_RERANK) ? LMD_PREP_NORMS : 0u);
+	while (!route_ready(s, prep)) {
 		rd.unlock();
-		lmd_status st = store_prepare(s, route);
+		lmd_status st = store_prepare(s, prep);
 		if (st != LMD_OK) {
 			return st;
 		}
@@ -162,7 +163,7 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 		return LMD_ERR_INVALID_ARG;
 	}
 	const bool dev_io = !stage_q && !stage_out; // nothing to copy: device-resident or zero-copy pinned buffers
-	const bool separate = route != LMD_ROUTE_EXACT || (flags & LMD_SEARCH_SEPARATE_RERANK);
+	const bool separate = route != LMD_ROUTE_EXACT || (flags & (LMD_SEARCH_SEPARATE_RERANK | LMD_SEARCH_TENSOR_RERANK));
 	const bool want_qstats = (flags & LMD_SEARCH_PER_QUERY_STATS) && out_qstats;
 	const bool async = (flags & LMD_SEARCH_ASYNC) != 0;
 	lmd_status rc;

@@ -92,6 +92,7 @@ struct Tuning {
 	int code_sigmas = 0;   // int8 codec grid: scale = code_sigmas / 10 * max sigma / 127 (0 = 4.0 sigmas)
 	int plane_filter_cap = 0; // 1 = the old 2 KB visited-filter cap for ternary routing over wide planes (pre-sidecar rule)
 	int prefilter = 1;     // exact routing on a codec store: 1 = int8 lower-bound pre-filter, 0 = plain traversal
+	int pf_g = 2;          // rows in flight per team of the pre-filtered kernels (1 or 2)
 };
 
 // Everything ONE in-flight search call owns: its stream, events, statistics counters and staging scratch. The store has
@@ -171,6 +172,8 @@ struct lmd_store {
 	uint32_t code_block_bytes = 0, code_data_off = 0;
 	uint64_t codes_gen = 0;
 	bool blocks_released = false;        // lmd_store_release_blocks: d_blocks is gone (search-only store)
+	float *d_norms = nullptr;            // [capacity] squared row norms: the view the tensor-core rerank's epilogue reads
+	uint64_t norms_gen = 0;
 
 	// graph-build scratch (lmd_build.cu), allocated on first use and kept
 	uint32_t *d_inbox = nullptr, *d_inbox_cnt = nullptr, *d_touched = nullptr;
@@ -251,6 +254,10 @@ struct RerankArgs {
 	unsigned long long *d_counters = nullptr;
 };
 lmd_status launch_rerank(const RerankArgs &a, cudaStream_t st);
+// LMD_SEARCH_TENSOR_RERANK (lmd_rerank_tc.cu): tcgen05 contraction staged through bulk async copies
+lmd_status launch_rerank_tensor(const RerankArgs &a, cudaStream_t st);
+lmd_status build_row_norms(lmd_store *s); // the caller holds s->mu exclusively
+#define LMD_PREP_NORMS 0x100u             // or-ed into the route given to route_ready() / store_prepare()
 
 lmd_status launch_merge_topk(const int64_t *d_ids, const float *d_dist, uint32_t shards, uint64_t nq, uint32_t k,
                              int64_t *d_out_ids, float *d_out_dist, cudaStream_t st);

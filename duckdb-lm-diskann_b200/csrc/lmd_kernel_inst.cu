@@ -16,6 +16,9 @@ namespace lmd {
 #if LMD_INST_KIND == 0
 lmd_status LMD_CAT(LMD_CAT(dispatch_traverse_m, LMD_INST_METRIC), LMD_CAT(_r, LMD_INST_ROUTE))(
     KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st) {
+#if LMD_INST_ROUTE == 3
+	LMD_DISPATCH_SHAPE_PF(traverse_kernel, LMD_INST_METRIC, LMD_INST_ROUTE)
+#endif
 	LMD_DISPATCH_SHAPE(traverse_kernel, LMD_INST_METRIC, LMD_INST_ROUTE)
 	set_error("no traversal kernel for this configuration (L=%u)", p.L);
 	return LMD_ERR_UNSUPPORTED;

@@ -69,6 +69,7 @@ struct KParams {
 	const float *__restrict__ code_off; // [row_floats]
 	float code_scale;
 	uint32_t prefilter;     // exact routing: 1 = the int8 lower bound decides which neighbours' rows are fetched at all
+	uint32_t pf_g;          // host side only: rows in flight per team of the pre-filtered kernels (1 or 2)
 };
 
 #define FULL 0xFFFFFFFFu
@@ -756,7 +757,7 @@ __device__ __forceinline__ bool slot_allowed(const KParams &p, uint32_t slot) {
 // offered every node whose routing distance gets evaluated and admits only allowed rows; results and the rerank
 // candidates come from RH alone.
 template <int TEAM, int CH, int G, int LPL, int METRIC, int ROUTE, int FILT = 0>
-__global__ void __launch_bounds__(128) traverse_kernel(const KParams p) {
+__global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) ? 8 : 1) traverse_kernel(const KParams p) {
 	extern __shared__ __align__(16) uint8_t smem[];
 	const int lane = threadIdx.x & 31;
 	uint8_t *wbase = smem + (threadIdx.x >> 5) * p.warp_smem_bytes;
@@ -1279,6 +1280,15 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 4, 4, METRIC, ##__VA_ARGS__)                                                \
 	} else if (p.row_floats == 96) {                                                                                   \
 		LMD_DISPATCH_LPL_COARSE(KERNEL, 8, 3, 4, METRIC, ##__VA_ARGS__)                                                \
+	}
+
+// Exact routing behind the int8 pre-filter gathers ~6 rows per expansion instead of ~26: one row in flight per team
+// (G = 1, 64 registers, 32 warps per SM) against the plain kernels' two ("pf_g" tuning key; measurements in DESIGN.md).
+#define LMD_DISPATCH_SHAPE_PF(KERNEL, METRIC, ...)                                                                     \
+	if (p.row_floats == 128 && p.pf_g == 1) {                                                                          \
+		LMD_DISPATCH_LPL(KERNEL, 8, 4, 1, METRIC, ##__VA_ARGS__)                                                       \
+	} else if (p.row_floats == 96 && p.pf_g == 1) {                                                                    \
+		LMD_DISPATCH_LPL(KERNEL, 8, 3, 1, METRIC, ##__VA_ARGS__)                                                       \
 	}
 
 #define LMD_DISPATCH_SHAPE(KERNEL, METRIC, ...)                                                                        \

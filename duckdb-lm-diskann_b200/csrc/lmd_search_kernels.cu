@@ -255,6 +255,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.list_cap = (uint32_t)lpl * 32;
 	p.merge_min = (uint32_t)(s->tune.merge_min > 0 ? s->tune.merge_min : 5);
 	p.prefetch_planes = s->tune.prefetch_planes ? 1u : 0u;
+	p.pf_g = s->tune.pf_g == 1 ? 1u : 2u;
 	const bool generic = p.strict || !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	size_t fixed = (size_t)lpl * 32 * 8 + 384 + (generic ? (size_t)p.row_floats * 4 : 0) +
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0) +
@@ -294,6 +295,9 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 }
 
 lmd_status launch_rerank(const RerankArgs &a, cudaStream_t st) {
+	if (a.tensor) {
+		return launch_rerank_tensor(a, st);
+	}
 	const lmd_store *s = a.s;
 	KParams p = base_params(s, a.d_queries, a.nq, a.k, a.L);
 	p.out_ids = a.d_out_ids;

@@ -238,6 +238,10 @@ bool route_ready(const lmd_store *s, uint32_t route) {
 	if (s->dirty) {
 		return false;
 	}
+	if ((route & LMD_PREP_NORMS) && (!s->d_norms || s->norms_gen != s->views_gen)) {
+		return false;
+	}
+	route &= ~LMD_PREP_NORMS;
 	if (route == LMD_ROUTE_TERNARY && s->side_t_gen != s->views_gen) {
 		return false;
 	}
@@ -254,6 +258,10 @@ lmd_status store_prepare(lmd_store *s, uint32_t route) {
 	if (rc != LMD_OK || s->n == 0) {
 		return rc;
 	}
+	if ((route & LMD_PREP_NORMS) && (!s->d_norms || s->norms_gen != s->views_gen) && (rc = build_row_norms(s)) != LMD_OK) {
+		return rc;
+	}
+	route &= ~LMD_PREP_NORMS;
 	if (route == LMD_ROUTE_TERNARY && s->side_t_gen != s->views_gen && (rc = build_plane_side(s)) != LMD_OK) {
 		return rc;
 	}

@@ -515,6 +515,7 @@ lmd_status lmd_store_destroy(lmd_store *s) {
 		cudaStreamSynchronize(s->stream);
 	}
 	cudaFree(s->d_blocks);
+	cudaFree(s->d_norms);
 	cudaFree(s->d_vecs);
 	cudaFree(s->d_nbrs);
 	cudaFree(s->d_row_ids);
@@ -1119,6 +1120,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		s->tune.plane_filter_cap = value ? 1 : 0;
 	} else if (k == "prefilter") {
 		s->tune.prefilter = value ? 1 : 0;
+	} else if (k == "pf_g") {
+		s->tune.pf_g = value == 1 ? 1 : 2;
 	} else {
 		set_error("lmd_set_tuning: unknown key %s", key);
 		return LMD_ERR_INVALID_ARG;

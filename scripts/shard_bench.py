@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--metric", default="L2")
     ap.add_argument("--route", default="exact", choices=["exact", "ternary", "int8"])
     ap.add_argument("--codec", action="store_true", help="enable the int8 edge codec (exact route: lower-bound pre-filter)")
+    ap.add_argument("--flags", type=int, default=0, help="extra LMD_SEARCH_* flags, e.g. 32 = LMD_SEARCH_TENSOR_RERANK")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--tag", default="")
@@ -138,11 +139,11 @@ def main():
             dd = torch.empty((a.nq, a.k), dtype=torch.float32, device=dev)
 
             def step():
-                store.search_raw(q, a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=ids, out_dist=dd)
+                store.search_raw(q, a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC | a.flags, out_ids=ids, out_dist=dd)
                 return ids, dd
         for _ in range(a.warmup):
             out = step()
-        st = store.search_raw(q, a.nq, a.k, L, route=route, out_ids=torch.empty((a.nq, a.k), dtype=torch.int64, device=dev))
+        st = store.search_raw(q, a.nq, a.k, L, route=route, flags=a.flags, out_ids=torch.empty((a.nq, a.k), dtype=torch.int64, device=dev))
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -174,7 +175,7 @@ def main():
         log(row)
     if rank == 0:
         print(json.dumps({"driver": "scripts/shard_bench.py", "tag": a.tag, "mode": a.mode, "n_total": a.n,
-                          "dims": a.dims, "r": a.r, "metric": a.metric, "route": a.route, "tune": a.tune, "n_gpus": world,
+                          "dims": a.dims, "r": a.r, "metric": a.metric, "route": a.route, "flags": a.flags, "tune": a.tune, "n_gpus": world,
                           "rows_per_gpu": hi - lo, "queries_per_step_total": a.nq if a.mode == "sharded" else a.nq * world,
                           "k": a.k, "l_insert": a.l_insert, "steps": a.steps, "warmup": a.warmup,
                           "gen_s": round(t_gen, 2), "upload_build_s": round(t_build, 2),

@@ -351,3 +351,73 @@ def test_scratch_capacities_are_tracked_per_array(lmd, make_index):
         assert int(b[4][:, 0].sum()) == b[3].expansions and int(b[4][:, 1].sum()) == b[3].distance_evals
         assert np.array_equal(b[4][:4000], c[4]) and np.array_equal(b[0][:4000], c[0])
         assert int(a[4][:, 0].sum()) == a[3].expansions
+
+
+# ---- rerank as a tensor-core contraction (row a3): tcgen05 kind::tf32, split fp32, bulk-copy staging ---------------------
+@pytest.mark.parametrize("metric,dims,r,L,kind", [("COSINE", 768, 32, 80, "clustered"), ("L2", 128, 32, 64, "iid"),
+                                                  ("IP", 100, 24, 200, "iid"), ("L2", 768, 32, 256, "clustered"),
+                                                  ("COSINE", 128, 32, 300, "iid"), ("L2", 256, 16, 20, "iid")])
+def test_tensor_rerank_matches_the_fma_rerank(lmd, make_index, metric, dims, r, L, kind):
+    """LMD_SEARCH_TENSOR_RERANK against rerank_kernel on the same candidate lists: same rows, distances within 1e-5
+    relative (IP: relative to |q| |x|, the quantity its summation error scales with)."""
+    ix = make_index(1500, dims, r, metric=metric, kind=kind, nq=200)
+    k = 10
+    with _store(lmd, ix, dims, r, metric) as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        fma = s.search(ix["queries"], k, L, flags=lmd.SEARCH_SEPARATE_RERANK)
+        tc = s.search(ix["queries"], k, L, flags=lmd.SEARCH_TENSOR_RERANK)
+        tc2 = s.search(ix["queries"][:3], k, L, flags=lmd.SEARCH_TENSOR_RERANK)       # fewer queries than SMs
+        if metric != "L2":
+            tt = s.search(ix["queries"], k, L, route=lmd.ROUTE_TERNARY, flags=lmd.SEARCH_TENSOR_RERANK)
+            tf = s.search(ix["queries"], k, L, route=lmd.ROUTE_TERNARY)
+    assert tc[3].launches == 2 and tc[3].reranked == fma[3].reranked
+    assert np.array_equal(tc[2], fma[2])
+    if metric == "IP":
+        x = np.asarray(ix["x"])
+        scale = np.linalg.norm(ix["queries"], axis=1)[:, None] * np.linalg.norm(x, axis=1).max()
+        assert (np.abs(tc[1] - fma[1]) <= 1e-5 * scale).all()
+        same = (tc[0] == fma[0]) | (np.abs(tc[1] - fma[1]) <= 1e-5 * scale)
+        assert same.all()
+    else:
+        check_parity(tc[0], tc[1], tc[2], fma[0], fma[1], fma[2], what="tensor rerank %s D=%d L=%d" % (metric, dims, L))
+        if metric != "L2":
+            check_parity(tt[0], tt[1], tt[2], tf[0], tf[1], tf[2], what="ternary route + tensor rerank")
+    assert np.array_equal(tc2[0], tc[0][:3])
+
+
+def test_tensor_rerank_cancellation_bound(lmd, make_index):
+    """SURVEY.md section 7 hard part 4: the contraction needs |q|^2 + |x|^2 - 2 q.x, which cancels for near-duplicate
+    rows. The squared distance is off by at most ~2^-20 (|q|^2 + |x|^2) - fine on the test distributions (checked above),
+    not relative to a distance that goes to 0. This pins the absolute bound (and is why the kernel is not the default)."""
+    dims, r = 128, 32
+    ix = make_index(1500, dims, r, metric="L2", kind="iid", nq=64)
+    x = np.asarray(ix["x"])
+    rng = np.random.default_rng(3)
+    q = (x[rng.integers(0, 1500, 64)] + 1e-3 * rng.standard_normal((64, dims))).astype(np.float32)
+    with _store(lmd, ix, dims, r, "L2") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        fma = s.search(q, 10, 64, flags=lmd.SEARCH_SEPARATE_RERANK)
+        tc = s.search(q, 10, 64, flags=lmd.SEARCH_TENSOR_RERANK)
+    q2 = (q.astype(np.float64) ** 2).sum(1)
+    shared = {}
+    for qi in range(64):
+        f = dict(zip(fma[0][qi].tolist(), fma[1][qi].tolist()))
+        for i, d in zip(tc[0][qi].tolist(), tc[1][qi].tolist()):
+            if i in f:
+                assert abs(d * d - f[i] * f[i]) <= 2.0 ** -20 * (2 * q2[qi] + 1.0), (qi, i, d, f[i])
+                shared[qi] = shared.get(qi, 0) + 1
+    assert min(shared.values()) >= 8
+
+
+def test_tensor_rerank_rejects_what_it_cannot_tile(lmd, make_index):
+    ix = make_index(1200, 96, 32, metric="L2", kind="clustered", nq=8)
+    with _store(lmd, ix, 96, 32, "L2") as s:
+        s.upload(ix["blocks_np"])
+        s.set_entry(0)
+        with pytest.raises(lmd.LmdError) as e:
+            s.search(ix["queries"], 5, 32, flags=lmd.SEARCH_TENSOR_RERANK)
+        assert e.value.status == lmd.ERR_UNSUPPORTED
+        with pytest.raises(lmd.LmdError):
+            s.search(ix["queries"], 5, 32, flags=lmd.SEARCH_TENSOR_RERANK | lmd.SEARCH_STRICT_FP)
