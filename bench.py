@@ -64,6 +64,9 @@ def parse():
     ap.add_argument("--sweep", action="store_true", help="also print the whole L sweep (stderr)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-codec", action="store_true",
+                    help="headline without the int8 code sidecar (the plain exact traversal instead of the pre-filtered one)")
+    ap.add_argument("--depth", type=int, default=2, help="batches in flight (search contexts used in turn)")
     ap.add_argument("--extras", default="auto", choices=["auto", "none"],
                     help="auto = also run the other BASELINE configs / strong scaling / sustained records")
     return ap.parse_args()
@@ -183,12 +186,12 @@ def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0
                 done, i, batches[0].shape[0], L, nthreads, dt)}, ids0, batches[0].shape[0]
 
 
-def profiled_traffic(a, L):
+def profiled_traffic(a, L, prefiltered=False):
     """DRAM bytes per traversal launch from the committed `ncu --set full` capture of this exact workload
     (profiles/traffic.json, dram__bytes_read.sum + dram__bytes_write.sum), or None."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        key = "n%d_d%d_r%d_%s_q%d_k%d_L%d" % (a.n, a.dims, a.r, a.kind, a.nq, a.k, L)
+        key = "n%d_d%d_r%d_%s_q%d_k%d_L%d%s" % (a.n, a.dims, a.r, a.kind, a.nq, a.k, L, "_pf" if prefiltered else "")
         return t.get(key, {}).get("dram_bytes_per_launch")
     except Exception:
         return None
@@ -198,12 +201,49 @@ def profiled_traffic(a, L):
 # other_configs: BASELINE.json configs C2 (strong), C3, C4, C5 on the GPUs of this run. Every record is timed like the
 # headline (barrier + CUDA events on the searching stream, max over ranks); local failures are reported in the record.
 # ------------------------------------------------------------------------------------------------------------------
+class Pipeline:
+    """`depth` batches in flight: step i is enqueued on search context i % depth (lmd_ctx: own stream, counters, scratch)
+    of the same store. The tail of a persistent-kernel launch - warps that find the query counter exhausted while others
+    still work - is filled by the next batch's kernel (profiles/r2_10_pipe_*.json: 10k-query batches +3 % plain, +11 %
+    pre-filtered, +23 % int8 route; 1 250-query batches +66 %). Timed on `main`, which brackets all streams by events."""
+
+    def __init__(self, torch, store, dev, depth=2):
+        self.torch, self.depth = torch, depth
+        self.ctxs = [store.context() for _ in range(depth)]
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]
+        for c, st in zip(self.ctxs, self.streams):
+            c.set_stream(st.cuda_stream)
+        self.main = torch.cuda.Stream(device=dev)
+
+    def begin(self):
+        e0 = self.torch.cuda.Event(enable_timing=True)
+        e0.record(self.main)
+        for st in self.streams:
+            st.wait_event(e0)
+        return e0
+
+    def end(self):
+        for st in self.streams:
+            ev = self.torch.cuda.Event()
+            ev.record(st)
+            self.main.wait_event(ev)
+        e1 = self.torch.cuda.Event(enable_timing=True)
+        e1.record(self.main)
+        return e1
+
+    def close(self):
+        self.torch.cuda.synchronize()
+        for c in self.ctxs:
+            c.close()
+
+
 class Job:
     def __init__(self, torch, dist, lmd, sh, wl, rank, world, local, dev, dist_on, steps, warmup):
         self.torch, self.dist, self.lmd, self.sh, self.wl = torch, dist, lmd, sh, wl
         self.rank, self.world, self.local, self.dev, self.dist_on = rank, world, local, dev, dist_on
-        self.steps, self.warmup = max(5, min(steps, 20)), max(3, min(warmup, 5))
+        self.steps, self.warmup = max(6, min(steps, 20)), max(4, min(warmup, 6))
         self.stream = torch.cuda.current_stream(dev)
+        self.depth = 2  # batches in flight (Pipeline)
 
     def barrier(self):
         if self.dist_on:
@@ -222,17 +262,24 @@ class Job:
         if self.reduce([1.0 if err else 0.0])[0] != 0.0:
             raise RuntimeError(err or "another rank failed in its local phase")
 
-    def time_steps(self, step):
-        """ms per step of `step()` (enqueues on the current stream): warm-up, barrier, events, max over ranks."""
+    def time_steps(self, step, pipe=None):
+        """ms per step of `step(i)` (enqueues; on the pipeline's contexts when one is given, else on the current stream):
+        warm-up, barrier, events, max over ranks."""
         torch = self.torch
-        for _ in range(self.warmup):
-            step()
+        for i in range(self.warmup):
+            step(i)
         self.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(self.stream)
-        for _ in range(self.steps):
-            step()
-        e1.record(self.stream)
+        if pipe is not None:
+            e0 = pipe.begin()
+            for i in range(self.steps):
+                step(i)
+            e1 = pipe.end()
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(self.stream)
+            for i in range(self.steps):
+                step(i)
+            e1.record(self.stream)
         self.barrier()
         return self.reduce([e0.elapsed_time(e1) / self.steps])[0]
 
@@ -240,14 +287,19 @@ class Job:
         """This rank searches q_local (its slice / its own batch); no collective on the path. -> record"""
         torch, lmd = self.torch, self.lmd
         nq = q_local.shape[0]
-        ids = torch.empty((max(nq, 1), k), dtype=torch.int64, device=self.dev)
-        dd = torch.empty((max(nq, 1), k), dtype=torch.float32, device=self.dev)
+        pipe = Pipeline(torch, store, self.dev, self.depth)
+        outs = [(torch.empty((max(nq, 1), k), dtype=torch.int64, device=self.dev),
+                 torch.empty((max(nq, 1), k), dtype=torch.float32, device=self.dev)) for _ in range(self.depth)]
+        ids, dd = outs[0]
         store.set_stream(self.stream.cuda_stream)
 
-        def step():
+        def step(i):
             if nq:
-                store.search_raw(q_local, nq, k, L, route=route, flags=lmd.SEARCH_ASYNC | flags, out_ids=ids, out_dist=dd)
-        ms = self.time_steps(step)
+                j = i % self.depth
+                store.search_raw(q_local, nq, k, L, route=route, flags=lmd.SEARCH_ASYNC | flags, out_ids=outs[j][0],
+                                 out_dist=outs[j][1], ctx=pipe.ctxs[j])
+        ms = self.time_steps(step, pipe)
+        pipe.close()
         st = store.search_raw(q_local, nq, k, L, route=route, flags=flags, out_ids=ids, out_dist=dd) if nq else None
         hits = self.wl.recall_hits(ids[:nq], truth_local) if nq and truth_local is not None else 0
         tot = truth_local.numel() if nq and truth_local is not None else 0
@@ -259,7 +311,8 @@ class Job:
                 "qps": round(total_q / (ms * 1e-3), 1), "recall_at_%d" % k: round(hits / max(tot, 1), 4),
                 "kernel_ms_max_over_gpus": round(kmax, 4), "E_per_q": round(E / max(nqs, 1), 1),
                 "V_per_q": round(V / max(nqs, 1), 1), "rows_fetched_per_q": round(F / max(nqs, 1), 1),
-                "algorithmic_GBps_per_gpu": round(ab / max(self.world, 1) / max(kmax, 1e-9) / 1e6, 1)}
+                "algorithmic_GBps_per_gpu": round(ab / max(self.world, 1) / max(kmax, 1e-9) / 1e6, 1),
+                "batches_in_flight": self.depth}
 
 
 def extra_c2_strong(J, store, batch0, truth0, k, L, route):
@@ -274,23 +327,15 @@ def extra_c2_strong(J, store, batch0, truth0, k, L, route):
 
 
 def extra_codec(J, store, batch_local, truth_local, k, L):
-    """Row f4: the int8 edge codec on the headline index - exact routing with the lower-bound pre-filter (same results,
+    """Row f4 on the headline index (its int8 code sidecar is already built): the plain exact traversal
+    (LMD_SEARCH_NO_PREFILTER), exact routing behind the lower-bound pre-filter (= the headline; same ids and distance bits,
     fewer rows fetched) and int8 routing + exact rerank (parity unpinned). One full batch per GPU like the headline."""
     torch, lmd = J.torch, J.lmd
     q = torch.from_numpy(batch_local).to(J.dev)
     t = torch.from_numpy(truth_local).to(J.dev) if truth_local is not None else None
     tot = batch_local.shape[0] * J.world
-    out = {"plain": J.query_sharded(store, q, t, k, L, lmd.ROUTE_EXACT, tot)}
-    t0 = time.time()
-    err = None
-    try:
-        store.enable_codec()
-        store.finalize()
-    except Exception as e:  # noqa: BLE001
-        err = repr(e)
-    J.agree(err)
-    out["codec_build_s"] = round(time.time() - t0, 2)
-    out["prefilter"] = J.query_sharded(store, q, t, k, L, lmd.ROUTE_EXACT, tot)
+    out = {"plain": J.query_sharded(store, q, t, k, L, lmd.ROUTE_EXACT, tot, flags=lmd.SEARCH_NO_PREFILTER),
+           "prefilter": J.query_sharded(store, q, t, k, L, lmd.ROUTE_EXACT, tot)}
     rows = []
     for l in (56, 64, 80, 96):
         rows.append(J.query_sharded(store, q, t, k, l, lmd.ROUTE_INT8, tot))
@@ -405,10 +450,10 @@ def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64):
     for L in Ls:
         out = [None]
 
-        def full():
+        def full(i):
             out[0] = searcher.search(q, k, L)
 
-        def local_only():
+        def local_only(i):
             store.search_raw(q, nq, k, L, flags=lmd.SEARCH_ASYNC, out_ids=ids, out_dist=dd)
         ms_full = J.time_steps(full)
         ms_local = J.time_steps(local_only)
@@ -493,8 +538,15 @@ def main():
     store.upload(blocks_dev)
     store.set_entry(0)
     store.finalize()
-    log("store ready in %.1f s: %d nodes, %.2f GB mirrored" % (time.time() - t0, store.node_count,
-                                                                store.device_bytes / 1e9))
+    # L2 + exact routing: the int8 code sidecar lets the traversal skip rows whose lower bound already exceeds the list's
+    # worst distance. Ids, distance bits and expansion counts are those of the plain traversal (tests/test_gpu_round2.py
+    # ::test_prefilter_changes_nothing_but_the_bytes; the parity report below is computed from THIS store's results).
+    use_codec = a.metric == "L2" and a.route == "exact" and not a.no_codec
+    if use_codec:
+        store.enable_codec()
+    log("store ready in %.1f s: %d nodes, %.2f GB mirrored%s" % (time.time() - t0, store.node_count,
+                                                                  store.device_bytes / 1e9,
+                                                                  " (incl. int8 code sidecar)" if use_codec else ""))
     keep_blocks_host = rank == 0 and not a.no_cpu
     blocks_np = blocks_dev.cpu().numpy() if keep_blocks_host else None
     del blocks_dev, x, nbrs, counts
@@ -530,14 +582,16 @@ def main():
         dist.broadcast(tt, 0)
         truth = tt.cpu().numpy()
 
-    # ---- device-resident arm ("value") ---------------------------------------------------------------------------
+    # ---- device-resident arm ("value"): a.depth batches in flight on as many search contexts ------------------------
     d_q = [torch.from_numpy(b).to(dev) for b in batches]
-    d_ids = torch.empty((a.nq, a.k), dtype=torch.int64, device=dev)
-    d_dist = torch.empty((a.nq, a.k), dtype=torch.float32, device=dev)
-    d_cnt = torch.empty(a.nq, dtype=torch.int32, device=dev)
-    stream = torch.cuda.Stream(device=dev)  # searches are enqueued on this stream; the events below bracket it
+    depth = max(1, a.depth)
+    d_out = [(torch.empty((a.nq, a.k), dtype=torch.int64, device=dev), torch.empty((a.nq, a.k), dtype=torch.float32, device=dev),
+              torch.empty(a.nq, dtype=torch.int32, device=dev)) for _ in range(depth)]
+    d_ids, d_dist, d_cnt = d_out[0]
+    stream = torch.cuda.Stream(device=dev)  # the store's own (statistics) calls run here
     torch.cuda.set_stream(stream)
     store.set_stream(stream.cuda_stream)
+    pipe = Pipeline(torch, store, dev, depth)
 
     def barrier():
         if dist_on:
@@ -545,22 +599,22 @@ def main():
         torch.cuda.synchronize()
 
     def dev_step(i):
-        store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_ids,
-                         out_dist=d_dist, out_count=d_cnt)
+        j = i % depth
+        store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=d_out[j][0],
+                         out_dist=d_out[j][1], out_count=d_out[j][2], ctx=pipe.ctxs[j])
 
     for i in range(a.warmup):
         dev_step(i)
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
-        e0.record(stream)
+        e0 = pipe.begin()
         for i in range(a.steps):
             dev_step(i)
-        e1.record(stream)
+        e1 = pipe.end()
         barrier()
         dev_ms = e0.elapsed_time(e1)
-        # per-kernel numbers for the roofline: same batches, synchronous calls with statistics
-        kern_ms, rerank_ms, alg_bytes, launches, E, V = 0.0, 0.0, 0, 0, 0, 0
+        # per-kernel numbers for the roofline: same batches, one at a time, synchronous calls with statistics
+        kern_ms, rerank_ms, alg_bytes, launches, E, V, F = 0.0, 0.0, 0, 0, 0, 0, 0
         for i in range(a.steps):
             st = store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=d_ids, out_dist=d_dist,
                                   out_count=d_cnt)
@@ -570,19 +624,44 @@ def main():
             launches += st.launches
             E += st.expansions
             V += st.distance_evals
+            F += st.exact_fetches
+        # the plain exact traversal on the same batches (the kernel the pre-filter is measured against)
+        plain_ms, plain_bytes = 0.0, 0
+        if use_codec:
+            for i in range(3):  # warm-up: the first launch of a kernel variant pays for its lazy load
+                store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_NO_PREFILTER,
+                                 out_ids=d_ids, out_dist=d_dist, out_count=d_cnt)
+            for i in range(min(a.steps, 10)):
+                st = store.search_raw(d_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_NO_PREFILTER,
+                                      out_ids=d_ids, out_dist=d_dist, out_count=d_cnt)
+                plain_ms += st.traverse_ms
+                plain_bytes += st.algorithmic_bytes
         barrier()
         # ---- host-buffer arm ("e2e"): pinned queries in, ids + distances out, through the C ABI --------------------
+        # The kernels read the pinned queries and write the pinned results in place (zero copy). Two calls are in flight
+        # (one per context); before a context is used again its stream is synchronised and the step's first result row
+        # is read by the host, so every step's ids and distances have landed in host memory inside the timed region.
         h_q = [torch.from_numpy(b).pin_memory() for b in batches]
-        h_ids = torch.empty((a.nq, a.k), dtype=torch.int64).pin_memory()
-        h_dist = torch.empty((a.nq, a.k), dtype=torch.float32).pin_memory()
-        # each call is synchronous: it returns when ids + distances of the step are in the caller's host buffers
-        for i in range(max(a.warmup, 3)):
-            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist, stats=False)
+        h_out = [(torch.empty((a.nq, a.k), dtype=torch.int64).pin_memory(),
+                  torch.empty((a.nq, a.k), dtype=torch.float32).pin_memory()) for _ in range(depth)]
+        seen = 0
+
+        def e2e_step(i):
+            j = i % depth
+            pipe.streams[j].synchronize()
+            s_ = int(h_out[j][0][0, 0])  # the host reads the previous result of this buffer pair
+            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, flags=lmd.SEARCH_ASYNC, out_ids=h_out[j][0],
+                             out_dist=h_out[j][1], ctx=pipe.ctxs[j])
+            return s_
+        for i in range(max(a.warmup, 4)):
+            e2e_step(i)
         barrier()
         t0 = time.perf_counter()
         for i in range(a.steps):
-            store.search_raw(h_q[i % N_BATCHES], a.nq, a.k, L, route=route, out_ids=h_ids, out_dist=h_dist, stats=False)
-        torch.cuda.synchronize()
+            seen += e2e_step(i)
+        for j in range(depth):
+            pipe.streams[j].synchronize()
+            seen += int(h_out[j][0][0, 0])
         e2e_s = time.perf_counter() - t0
     # ... and with PAGEABLE buffers (what DuckDB's float* / std::vector<row_t> give GpuSearcher::Search): staged copies
     p_ids = np.empty((a.nq, a.k), dtype=np.int64)
@@ -607,12 +686,11 @@ def main():
     if a.extras != "none":
         n_sus = int(max(a.steps, min(20000, 2200.0 / max(dev_ms / a.steps, 1e-3))))
         barrier()
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with ClockSampler(local) as sus_clocks:
-            s0.record(stream)
+            s0 = pipe.begin()
             for i in range(n_sus):
                 dev_step(i)
-            s1.record(stream)
+            s1 = pipe.end()
             barrier()
         sus_ms = s0.elapsed_time(s1)
         if dist_on:
@@ -634,14 +712,16 @@ def main():
         if not a.no_cpu:
             strict_res = store.search(batches[0], a.k, L, route=route, flags=lmd.SEARCH_STRICT_FP, qstats=True)
     store_bytes = store.device_bytes
+    pipe.close()
 
     # ---- other configs (all ranks) -----------------------------------------------------------------------------------
     other = {}
     if a.extras != "none":
         J = Job(torch, dist, lmd, sh, wl, rank, world, local, dev, dist_on, a.steps, a.warmup)
         J.stream = stream
+        J.depth = depth
         other["c2_strong"] = guarded(J, "c2_strong", extra_c2_strong, store, batch0, truth, a.k, L, route)
-        if a.metric == "L2" and a.route == "exact":
+        if use_codec:
             other["c2_codec"] = guarded(J, "c2_codec", extra_codec, store, batches[0], truth if rank == 0 else None, a.k, L)
     store.close()
     del d_q
@@ -704,24 +784,43 @@ def main():
                        store_bytes / 1e9, alg_bytes / a.steps / 1e9)) if store_bytes > 4 * 126e6 else (
                        "node store %.0f MB FITS in the 126 MB L2 and is not flushed between steps: a parity / "
                        "small-index configuration, not a bandwidth measurement" % (store_bytes / 1e6)),
-                   "parallelism": "queries sharded, graph replicated (%d x %d queries per step)" % (world, a.nq)},
+                   "parallelism": "queries sharded, graph replicated (%d x %d queries per step)" % (world, a.nq),
+                   "batches_in_flight": depth,
+                   "traversal": ("exact routing behind the int8 lower-bound pre-filter (results bit-identical to the plain "
+                                 "traversal; %.1f of %.1f evaluated rows fetched per query)" % (
+                                     F / (a.nq * a.steps), V / (a.nq * a.steps))) if use_codec else "plain exact traversal"},
         "e2e": {"value": total_q / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": a.nq * a.dims * 4,
                 "d2h_bytes_per_step": a.nq * a.k * 12, "ms_per_step": e2e_s * 1e3 / a.steps,
-                "buffers": "pinned host memory, read / written in place by the kernels"},
+                "buffers": "pinned host memory, read / written in place by the kernels; %d calls in flight, every step's "
+                           "result read by the host before its buffers are reused" % depth},
         "e2e_pageable": {"value": total_q / e2e_page_s, "unit": "queries/s", "ms_per_step": e2e_page_s * 1e3 / a.steps,
                          "buffers": "pageable host memory (numpy), staged through cudaMemcpyAsync inside the call"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": profiled_traffic(a, L),
+                     "traffic": profiled_traffic(a, L, use_codec),
                      "traffic_source": "profiles/traffic.json (ncu --set full capture of this workload by the builder, "
                                        "not measured in this run)",
-                     "kernel": "traverse_kernel", "kernel_ms": kern_ms / a.steps, "rerank_kernel_ms": rerank_ms / a.steps,
+                     "kernel": "traverse_kernel" + (" (exact routing, int8 pre-filter)" if use_codec else ""),
+                     "kernel_ms": kern_ms / a.steps, "rerank_kernel_ms": rerank_ms / a.steps,
+                     "kernel_ms_note": "CUDA-event duration of one launch at a time (lmd_stats.traverse_ms); with %d batches "
+                                       "in flight a step takes ms_per_step" % depth,
+                     "achieved_in_flight": alg_bytes / a.steps / (dev_ms / a.steps * 1e-3) / 1e9 / world if world else None,
                      "algorithmic_bytes_per_launch": alg_bytes // a.steps,
+                     "bytes_formula": ("E * code_block_bytes + F * 4D + Q * (4D + 12k)" if use_codec else
+                                       "E * 4R + V * 4D + Q * (4D + 12k)"),
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
-                     "E_per_query": E / (a.nq * a.steps), "V_per_query": V / (a.nq * a.steps)},
+                     "E_per_query": E / (a.nq * a.steps), "V_per_query": V / (a.nq * a.steps),
+                     "rows_fetched_per_query": F / (a.nq * a.steps)},
         "cpu_baseline": cpu,
         "clocks": clocks.summary(),
     }
+    if use_codec and plain_ms > 0:
+        n_pl = min(a.steps, 10)
+        pa = plain_bytes / (plain_ms * 1e-3) / 1e9
+        out["roofline_plain_kernel"] = {"kernel": "traverse_kernel (plain exact traversal, LMD_SEARCH_NO_PREFILTER)",
+                                        "kernel_ms": plain_ms / n_pl, "achieved": pa, "peak": peak, "frac": pa / peak,
+                                        "algorithmic_bytes_per_launch": plain_bytes // n_pl,
+                                        "bytes_formula": "E * 4R + V * 4D + Q * (4D + 12k)"}
     if sustained:
         out["sustained"] = sustained
     if parity is not None:

@@ -262,6 +262,8 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 	ta.strict = (flags & LMD_SEARCH_STRICT_FP) != 0;
 	ta.no_prefilter = (flags & LMD_SEARCH_NO_PREFILTER) != 0;
 	ta.d_counters = ss.d_counters;
+	uint32_t kroute_used = route;
+	ta.kroute_out = &kroute_used;
 	if (timed) {
 		LMD_CUDA_OK(cudaEventRecord(ss.ev[1], st));
 	}
@@ -359,8 +361,7 @@ static lmd_status search_impl(lmd_store *s, SearchState &ss, const lmd_filter *f
 		// (the reference's 8 + 8R becomes 4R); padding is never counted.
 		const uint64_t vec = (uint64_t)s->cfg.dims * 4;
 		uint64_t bytes = nq * ((uint64_t)s->cfg.dims * 4 + (uint64_t)k * 12);
-		const bool prefiltered = route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && !ta.no_prefilter && !filter &&
-		                         !ta.strict && !s->tune.strict_fp && s->tune.prefilter != 0;
+		const bool prefiltered = kroute_used == 3; // LMD_KROUTE_EXACT_PF: launch_traverse decides (store, flags, batch size)
 		if (route == LMD_ROUTE_INT8 || prefiltered) {
 			// one code block per expansion (neighbour slots + code norms + R int8 codes), then an exact row per fetched node
 			bytes += h_cnt[1] * (uint64_t)s->code_block_bytes + h_cnt[7] * vec + (route == LMD_ROUTE_INT8 ? vec * nq : 0);

@@ -91,7 +91,7 @@ struct Tuning {
 	int strict_fp = 0;     // 1 = every kernel of this store accumulates distances in the reference's order (parity tool)
 	int code_sigmas = 0;   // int8 codec grid: scale = code_sigmas / 10 * max sigma / 127 (0 = 4.0 sigmas)
 	int plane_filter_cap = 0; // 1 = the old 2 KB visited-filter cap for ternary routing over wide planes (pre-sidecar rule)
-	int prefilter = 1;     // exact routing on a codec store: 1 = int8 lower-bound pre-filter, 0 = plain traversal
+	int prefilter = 1;     // exact routing on a codec store: 1 = int8 lower-bound pre-filter for batches that fill the GPU, 2 = for every batch, 0 = plain traversal
 	int pf_g = 2;          // rows in flight per team of the pre-filtered kernels (1 or 2)
 };
 
@@ -238,6 +238,7 @@ struct TraverseArgs {
 	bool strict = false;                 // LMD_SEARCH_STRICT_FP
 	bool no_prefilter = false;           // LMD_SEARCH_NO_PREFILTER
 	unsigned long long *d_counters = nullptr; // the calling SearchState's counters (null = the store's own)
+	uint32_t *kroute_out = nullptr;           // receives the kernel-side route that was launched (3 = exact + pre-filter)
 };
 lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st);
 

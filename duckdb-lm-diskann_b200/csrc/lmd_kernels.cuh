@@ -757,7 +757,7 @@ __device__ __forceinline__ bool slot_allowed(const KParams &p, uint32_t slot) {
 // offered every node whose routing distance gets evaluated and admits only allowed rows; results and the rerank
 // candidates come from RH alone.
 template <int TEAM, int CH, int G, int LPL, int METRIC, int ROUTE, int FILT = 0>
-__global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) ? 8 : 1) traverse_kernel(const KParams p) {
+__global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) ? 8 : 0) traverse_kernel(const KParams p) {
 	extern __shared__ __align__(16) uint8_t smem[];
 	const int lane = threadIdx.x & 31;
 	uint8_t *wbase = smem + (threadIdx.x >> 5) * p.warp_smem_bytes;
@@ -933,7 +933,9 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 						s_nb[pos] = id;
 					}
 					__syncwarp();
-					prefetch_rows<(CH > 0 ? CH * TEAM / 8 : 0)>(p, s_nb, m, lane);
+					if (CH == 0 || m > (32 / TEAM) * G) { // one pass gathers them all anyway: nothing to pull ahead
+						prefetch_rows<(CH > 0 ? CH * TEAM / 8 : 0)>(p, s_nb, m, lane);
+					}
 					compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, m, lane);
 					__syncwarp();
 					have = lane < m;

@@ -214,10 +214,19 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	uint32_t tie_slots = s->tune.tie_slots >= 0 ? (uint32_t)s->tune.tie_slots
 	                                            : (a.route != LMD_ROUTE_EXACT ? plan_tie_slots(a.L) : (p.strict ? 32u : 0u));
 	// exact routing on a store with the int8 codec: the codes decide which rows are fetched (same results, fewer bytes)
+	// ... for batches that fill the GPU. Small batches (one query, index-join chunks) are latency-bound, not byte-bound: they
+	// keep the plain kernels that gather a whole expansion in one pass (one query 230 us against 271 us pre-filtered;
+	// "prefilter" = 2 forces the pre-filter for every batch size).
 	uint32_t kroute = a.route;
+	const bool specialised_shape = !p.strict && (p.row_floats == 128 || p.row_floats == 96);
+	const bool small_batch = specialised_shape && plan_family(a.nq, (uint32_t)s->sm_count, s->tune.latency_mode) != 0;
 	if (a.route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && s->codes_gen == s->views_gen && !a.no_prefilter &&
-	    !a.d_allowed && !p.strict && s->tune.prefilter && s->cfg.metric == LMD_METRIC_L2) {
+	    !a.d_allowed && !p.strict && s->tune.prefilter && s->cfg.metric == LMD_METRIC_L2 &&
+	    (!small_batch || s->tune.prefilter == 2)) {
 		kroute = LMD_KROUTE_EXACT_PF;
+	}
+	if (a.kroute_out) {
+		*a.kroute_out = kroute;
 	}
 	if (a.route == LMD_ROUTE_TERNARY) {
 		p.side = s->d_side_t;

@@ -1119,7 +1119,7 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 	} else if (k == "plane_filter_cap") {
 		s->tune.plane_filter_cap = value ? 1 : 0;
 	} else if (k == "prefilter") {
-		s->tune.prefilter = value ? 1 : 0;
+		s->tune.prefilter = value == 2 ? 2 : (value ? 1 : 0);
 	} else if (k == "pf_g") {
 		s->tune.pf_g = value == 1 ? 1 : 2;
 	} else {

@@ -222,6 +222,9 @@ def test_prefilter_changes_nothing_but_the_bytes(lmd, oracle, make_index, n, dim
         s.set_entry(0)
         plain = s.search(ix["queries"], k, L, qstats=True)
         s.enable_codec()
+        auto = s.search(ix["queries"], k, L, qstats=True)  # 128 queries: a small batch keeps the plain latency kernels
+        assert auto[3].exact_fetches == plain[3].exact_fetches and np.array_equal(auto[0], plain[0])
+        s.set_tuning("prefilter", 2)                       # ... unless the pre-filter is forced for every batch size
         pf = s.search(ix["queries"], k, L, qstats=True)
         off = s.search(ix["queries"], k, L, qstats=True, flags=lmd.SEARCH_NO_PREFILTER)
         # ... also with a visited filter that forgets, and with the one-by-one admission path
