@@ -124,6 +124,7 @@ SYMBOLS = [
     ("lmd_build_graph", C.c_int32, [_P, C.POINTER(BuildParams), C.POINTER(BuildStats)]),
     ("lmd_robust_prune_batch", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_float, _P, _P]),
     ("lmd_store_download_blocks", C.c_int32, [_P, C.c_uint64, C.c_uint64, _P]),
+    ("lmd_store_download_row_ids", C.c_int32, [_P, C.c_uint64, C.c_uint64, _P]),
     ("lmd_last_error", C.c_char_p, []),
     ("lmd_abi_version", C.c_uint32, []),
     ("lmd_set_tuning", C.c_int32, [_P, C.c_char_p, C.c_int64]),
@@ -278,6 +279,12 @@ class Store:
         if out is None:
             out = np.empty((n, self.block_bytes), dtype=np.uint8)
         _check(lib().lmd_store_download_blocks(self._h, first_slot, n, _ptr(out)))
+        return out
+
+    def download_row_ids(self, first_slot=0, n=None):
+        n = self.node_count - first_slot if n is None else n
+        out = np.empty(n, dtype=np.int64)
+        _check(lib().lmd_store_download_row_ids(self._h, first_slot, n, _ptr(out)))
         return out
 
     def enable_codec(self, codec=CODEC_INT8):

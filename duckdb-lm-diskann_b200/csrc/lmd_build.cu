@@ -310,6 +310,25 @@ lmd_status lmd_store_download_blocks(lmd_store *s, uint64_t first_slot, uint64_t
 	return LMD_OK;
 }
 
+lmd_status lmd_store_download_row_ids(lmd_store *s, uint64_t first_slot, uint64_t n, int64_t *out_row_ids) {
+	if (!s || (!out_row_ids && n)) {
+		set_error("lmd_store_download_row_ids: null argument");
+		return LMD_ERR_INVALID_ARG;
+	}
+	std::shared_lock<std::shared_mutex> g(s->mu);
+	if (first_slot + n > s->n) {
+		set_error("lmd_store_download_row_ids: slots [%llu, %llu) are beyond the %llu mirrored nodes",
+		          (unsigned long long)first_slot, (unsigned long long)(first_slot + n), (unsigned long long)s->n);
+		return LMD_ERR_INVALID_ARG;
+	}
+	if (n == 0) {
+		return LMD_OK;
+	}
+	LMD_CUDA_OK(cudaSetDevice(s->device));
+	LMD_CUDA_OK(cudaMemcpy(out_row_ids, s->d_row_ids + first_slot, n * sizeof(int64_t), cudaMemcpyDefault));
+	return LMD_OK;
+}
+
 lmd_status lmd_robust_prune_batch(lmd_store *s, const int64_t *node_row_ids, const int64_t *cand_row_ids, uint64_t m,
                                   uint32_t c, float alpha, int64_t *out_ids, uint32_t *out_count) {
 	if (!s || !node_row_ids || !cand_row_ids || !out_ids || !out_count) {

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <iostream>
 #include <stdexcept>
+#include <unordered_set>
 
 namespace diskann {
 namespace b200 {
@@ -169,14 +170,21 @@ common::idx_t DeviceNodeStore::WriteBack(core::IStorageManager &storage, core::I
 	if (batch_nodes == 0) {
 		batch_nodes = 1;
 	}
+	// Blocks carry no id of their own: every downloaded block is paired with the row id the STORE holds for its slot
+	// (stores filled by MirrorFrom / Apply may have skipped or reordered rows), and only rows the caller asked for are
+	// written.
+	const std::unordered_set<common::row_t> wanted(row_ids.begin(), row_ids.end());
+	const common::idx_t total = NodeCount();
 	std::vector<uint8_t> stage(static_cast<size_t>(batch_nodes) * block_bytes_);
+	std::vector<common::row_t> slot_ids(batch_nodes);
 	common::idx_t written = 0;
-	for (common::idx_t first = 0; first < row_ids.size(); first += batch_nodes) {
-		const common::idx_t now = std::min<common::idx_t>(batch_nodes, row_ids.size() - first);
+	for (common::idx_t first = 0; first < total; first += batch_nodes) {
+		const common::idx_t now = std::min<common::idx_t>(batch_nodes, total - first);
 		Check(lmd_store_download_blocks(store_, first, now, stage.data()), "DeviceNodeStore::WriteBack");
+		Check(lmd_store_download_row_ids(store_, first, now, slot_ids.data()), "DeviceNodeStore::WriteBack");
 		for (common::idx_t i = 0; i < now; i++) {
 			common::IndexPointer ptr;
-			if (!graph.TryGetNodePointer(row_ids[first + i], ptr)) {
+			if (!wanted.count(slot_ids[i]) || !graph.TryGetNodePointer(slot_ids[i], ptr)) {
 				continue;
 			}
 			common::data_ptr_t dst = storage.GetMutableNodeBlockData(ptr);
@@ -188,10 +196,13 @@ common::idx_t DeviceNodeStore::WriteBack(core::IStorageManager &storage, core::I
 			written++;
 		}
 	}
-	if (!row_ids.empty()) {
+	if (total > 0) {
+		// AddNode makes the first inserted node the entry point (core/GraphManager.cpp:119-121): slot 0's row
+		common::row_t first_row = 0;
+		Check(lmd_store_download_row_ids(store_, 0, 1, &first_row), "DeviceNodeStore::WriteBack");
 		common::IndexPointer first_ptr;
-		if (graph.TryGetNodePointer(row_ids[0], first_ptr)) {
-			graph.SetEntryPoint(first_ptr, row_ids[0]);
+		if (graph.TryGetNodePointer(first_row, first_ptr)) {
+			graph.SetEntryPoint(first_ptr, first_row);
 		}
 	}
 	return written;

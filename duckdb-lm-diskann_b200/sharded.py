@@ -85,6 +85,10 @@ def _cuda_local_search(store, queries_dev, nq, k, L, route):
     ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
     d = torch.empty((nq, k), dtype=torch.float32, device=dev)
     cur = torch.cuda.current_stream(dev).cuda_stream
+    if not cur:
+        # default stream: the store searches on its own non-blocking stream, which nothing orders against pending
+        # default-stream work that may still be producing `queries_dev`
+        torch.cuda.current_stream(dev).synchronize()
     if getattr(store, "_bound_stream", 0) != cur:
         store.set_stream(cur or None)
         store._bound_stream = cur

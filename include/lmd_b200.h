@@ -296,6 +296,9 @@ lmd_status lmd_robust_prune_batch(lmd_store *s, const int64_t *node_row_ids, con
 /* Reads n mirrored blocks starting at slot `first_slot` back (host or device buffer): how a built graph reaches the
  * host's storage (IStorageManager::AllocateNodeBlock + memcpy). */
 lmd_status lmd_store_download_blocks(lmd_store *s, uint64_t first_slot, uint64_t n, void *out_blocks);
+/* The row ids of the same slots (host or device buffer): a block does not carry its own id, so whoever hands downloaded
+ * blocks back to the host's storage pairs them through this (core/GraphManager.hpp:122 is the reference's row id map). */
+lmd_status lmd_store_download_row_ids(lmd_store *s, uint64_t first_slot, uint64_t n, int64_t *out_row_ids);
 
 /* --- misc --- */
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
