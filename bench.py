@@ -67,6 +67,9 @@ def parse():
     ap.add_argument("--no-codec", action="store_true",
                     help="headline without the int8 code sidecar (the plain exact traversal instead of the pre-filtered one)")
     ap.add_argument("--depth", type=int, default=2, help="batches in flight (search contexts used in turn)")
+    ap.add_argument("--single-process", action="store_true",
+                    help="ONE process drives --gpus devices through lmd_group (query-sharded replicas) instead of one "
+                         "torch.distributed rank per GPU; prints its own JSON line (not the driver's contract)")
     ap.add_argument("--extras", default="auto", choices=["auto", "none"],
                     help="auto = also run the other BASELINE configs / strong scaling / sustained records")
     return ap.parse_args()
@@ -482,8 +485,60 @@ def guarded(J, name, fn, *a, **kw):
     return r
 
 
+def run_single_process(a):
+    """The headline workload through lmd_group: one host thread, a.gpus devices, one replica of the index on each, a batch
+    of a.gpus x a.nq queries per step in pinned host memory, results written to pinned host memory (the e2e definition).
+    Shows that the multi-GPU modes are reachable from a single-process host (DuckDB) and cost what the ranks cost."""
+    import torch
+    fx = importlib.import_module("duckdb-lm-diskann_b200.fixtures")
+    lmd = importlib.import_module("duckdb-lm-diskann_b200")
+    n_dev = min(a.gpus, torch.cuda.device_count())
+    x, nbrs, counts = load_or_build_index(a, fx, "cuda:0")
+    L = a.L or 56
+    stores = []
+    for d in range(n_dev):
+        torch.cuda.set_device(d)
+        blocks = fx.pack_blocks(x, nbrs, counts, a.r, device="cuda:%d" % d)
+        st = lmd.Store(a.dims, a.r, metric=lmd.METRIC_BY_NAME[a.metric], capacity=a.n, device=d, l_search=100)
+        st.upload(blocks)
+        st.set_entry(0)
+        st.finalize()
+        if a.metric == "L2" and not a.no_codec:
+            st.enable_codec()
+        del blocks
+        torch.cuda.empty_cache()
+        stores.append(st)
+    nq = a.nq * n_dev
+    qs = [torch.from_numpy(fx.make_dataset(nq, a.dims, kind=a.kind, seed=43 + 17 * b)).pin_memory() for b in range(2)]
+    ids = torch.empty((nq, a.k), dtype=torch.int64).pin_memory()
+    dd = torch.empty((nq, a.k), dtype=torch.float32).pin_memory()
+    truth = fx.brute_force_topk(x, qs[0][:2000].numpy(), a.k, a.metric, device="cuda:0")
+    out = {}
+    for mode_name, mode in (("query_sharded", lmd.GROUP_QUERY_SHARDED),):
+        with lmd.Group(stores, mode) as g:
+            for i in range(max(a.warmup, 3)):
+                g.search_raw(qs[i % 2], nq, a.k, L, out_ids=ids, out_dist=dd, stats=False)
+            t0 = time.perf_counter()
+            for i in range(a.steps):
+                g.search_raw(qs[i % 2], nq, a.k, L, out_ids=ids, out_dist=dd, stats=False)
+            dt = time.perf_counter() - t0
+            st = g.search_raw(qs[0], nq, a.k, L, out_ids=ids, out_dist=dd)
+            rec = fx.recall_at_k(ids[:2000].numpy(), truth)
+            out[mode_name] = {"qps": nq * a.steps / dt, "ms_per_step": dt * 1e3 / a.steps, "recall_at_10": round(rec, 4),
+                              "search_ms_per_member": [round(st.search_ms[i], 4) for i in range(n_dev)],
+                              "wall_ms_one_call": round(st.wall_ms, 4)}
+    print(json.dumps({"mode": "single process, lmd_group", "n_gpus": n_dev, "steps": a.steps, "L": L,
+                      "workload": "synthetic %dx%d %s, %d x %d queries per step, pinned host buffers" % (
+                          a.n, a.dims, a.metric, n_dev, a.nq), "results": out}), flush=True)
+    for st in stores:
+        st.close()
+    return 0
+
+
 def main():
     a = parse()
+    if a.single_process:
+        return run_single_process(a)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))

@@ -24,7 +24,9 @@ ap.add_argument("--reps", type=int, default=200)
 a = ap.parse_args()
 lmd = importlib.import_module("duckdb-lm-diskann_b200")
 sys.path.insert(0, os.path.join(ROOT, "scripts"))
-from shard_bench import gen  # noqa: E402
+import importlib as _il  # noqa: E402
+_wl = _il.import_module("duckdb-lm-diskann_b200.workloads")
+gen = _wl.gen
 
 dev = torch.device("cuda", 0)
 x = gen(a.n, a.dims, 42, dev, a.metric == "COSINE")

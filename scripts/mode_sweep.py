@@ -5,7 +5,9 @@ import argparse, importlib, json, os, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "scripts"))
-from shard_bench import gen  # noqa: E402
+import importlib as _il  # noqa: E402
+_wl = _il.import_module("duckdb-lm-diskann_b200.workloads")
+gen = _wl.gen
 ap = argparse.ArgumentParser()
 ap.add_argument("--rows", dest="n", type=int, default=1_000_000)
 ap.add_argument("--dims", type=int, default=128)
