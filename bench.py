@@ -736,6 +736,9 @@ def main():
         store.search_raw(batches[0][i:i + 1], 1, a.k, L, route=route, out_ids=p_ids[:1], out_dist=p_dist[:1], stats=False)
         lat.append(time.perf_counter() - t1)
     lat_us = sorted(lat[20:])[100] * 1e6
+    st1 = store.search_raw(batches[0][:1], 1, a.k, L, route=route, out_ids=p_ids[:1], out_dist=p_dist[:1])
+    log("single query: median %.1f us of %d calls (min %.1f, max %.1f), kernel %.1f us, launches %d" % (
+        lat_us, len(lat) - 20, min(lat[20:]) * 1e6, max(lat[20:]) * 1e6, st1.traverse_ms * 1e3, st1.launches))
     # ---- sustained: >= 2 s of back-to-back device-resident steps, clocks sampled throughout --------------------------
     sustained = None
     if a.extras != "none":

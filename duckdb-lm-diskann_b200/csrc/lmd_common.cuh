@@ -93,6 +93,7 @@ struct Tuning {
 	int plane_filter_cap = 0; // 1 = the old 2 KB visited-filter cap for ternary routing over wide planes (pre-sidecar rule)
 	int prefilter = 1;     // exact routing on a codec store: 1 = int8 lower-bound pre-filter for batches that fill the GPU, 2 = for every batch, 0 = plain traversal
 	int pf_g = 2;          // rows in flight per team of the pre-filtered kernels (1 or 2)
+	int row_prefetch = 2;  // L2 prefetch of the rows of a gather: 2 = auto, 1 = always, 0 = never
 };
 
 // Everything ONE in-flight search call owns: its stream, events, statistics counters and staging scratch. The store has

@@ -70,6 +70,7 @@ struct KParams {
 	float code_scale;
 	uint32_t prefilter;     // exact routing: 1 = the int8 lower bound decides which neighbours' rows are fetched at all
 	uint32_t pf_g;          // host side only: rows in flight per team of the pre-filtered kernels (1 or 2)
+	uint32_t row_prefetch;  // 2 = auto (see the gather), 1 = always prefetch the rows of a gather into L2, 0 = never
 };
 
 #define FULL 0xFFFFFFFFu
@@ -933,7 +934,10 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 						s_nb[pos] = id;
 					}
 					__syncwarp();
-					if (CH == 0 || m > (32 / TEAM) * G) { // one pass gathers them all anyway: nothing to pull ahead
+					// Pull every line of every row into L2 first - unless ONE pass of a throughput kernel (G <= 2: at most
+					// 8 rows, 4 loads per lane) gathers them all anyway. The small-batch kernels (G = 4 / 8) keep it: a lane
+					// cannot have 32 loads in flight, the prefetches can.
+					if (p.row_prefetch == 1 || (p.row_prefetch != 0 && (CH == 0 || G > 2 || m > (32 / TEAM) * G))) {
 						prefetch_rows<(CH > 0 ? CH * TEAM / 8 : 0)>(p, s_nb, m, lane);
 					}
 					compute_batch<TEAM, CH, G, METRIC>(Q, p, s_nb, s_d, s_d2, m, lane);

@@ -265,6 +265,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.merge_min = (uint32_t)(s->tune.merge_min > 0 ? s->tune.merge_min : 5);
 	p.prefetch_planes = s->tune.prefetch_planes ? 1u : 0u;
 	p.pf_g = s->tune.pf_g == 1 ? 1u : 2u;
+	p.row_prefetch = (uint32_t)s->tune.row_prefetch;
 	const bool generic = p.strict || !(p.row_floats == 128 || p.row_floats == 96 || p.row_floats == 768);
 	size_t fixed = (size_t)lpl * 32 * 8 + 384 + (generic ? (size_t)p.row_floats * 4 : 0) +
 	               (a.route == LMD_ROUTE_TERNARY ? (size_t)p.words * 16 : 0) +
