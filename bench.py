@@ -59,8 +59,9 @@ def parse():
     ap.add_argument("--recall", type=float, default=0.95)
     ap.add_argument("--kind", default="clustered")
     ap.add_argument("--metric", default="L2", choices=["L2", "COSINE", "IP"])
-    ap.add_argument("--route", default="exact", choices=["exact", "ternary"],
-                    help="ternary = LM-DiskANN compressed-neighbour routing + exact rerank (COSINE / IP only)")
+    ap.add_argument("--route", default="exact", choices=["exact", "ternary", "int8"],
+                    help="ternary = LM-DiskANN compressed-neighbour routing + exact rerank (COSINE / IP only); int8 = the "
+                         "L2-capable int8 edge codec + exact rerank (PARITY UNPINNED: no reference code executes it)")
     ap.add_argument("--sweep", action="store_true", help="also print the whole L sweep (stderr)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
@@ -167,6 +168,8 @@ def cpu_reference_qps(a, blocks_np, block_bytes, batches, L, seconds, nthreads=0
     (the parity / recall sample)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle
+    if a.route == "int8":
+        a = argparse.Namespace(**{**vars(a), "route": "exact"})  # the CPU arm of an int8-route run is the reference's exact search
     kind = "reference" if pyoracle.have_ref("fixed") and a.route == "exact" else "port"
     impl = "fixed" if kind == "reference" else "port"  # the reference never executes ternary routing
     metric = {"L2": 1, "COSINE": 2, "IP": 3}[a.metric]
@@ -589,7 +592,7 @@ def main():
     t0 = time.time()
     blocks_dev = fx.pack_blocks(x, nbrs, counts, a.r, device=dev)  # node blocks, reference layout, built in HBM
     store = lmd.Store(a.dims, a.r, metric=lmd.METRIC_BY_NAME[a.metric], capacity=a.n, device=local, l_search=100)
-    route = lmd.ROUTE_TERNARY if a.route == "ternary" else lmd.ROUTE_EXACT
+    route = {"ternary": lmd.ROUTE_TERNARY, "int8": lmd.ROUTE_INT8}.get(a.route, lmd.ROUTE_EXACT)
     store.upload(blocks_dev)
     store.set_entry(0)
     store.finalize()
@@ -810,7 +813,7 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    achieved = alg_bytes / ((kern_ms + rerank_ms) * 1e-3) / 1e9
     cpu = None
     parity = None
     if not a.no_cpu:
@@ -844,6 +847,8 @@ def main():
                        "small-index configuration, not a bandwidth measurement" % (store_bytes / 1e6)),
                    "parallelism": "queries sharded, graph replicated (%d x %d queries per step)" % (world, a.nq),
                    "batches_in_flight": depth,
+                   "parity_note": ("int8 routing: PARITY UNPINNED - the parity block compares with the reference's EXACT search"
+                                   if a.route == "int8" else None),
                    "traversal": ("exact routing behind the int8 lower-bound pre-filter (results bit-identical to the plain "
                                  "traversal; %.1f of %.1f evaluated rows fetched per query)" % (
                                      F / (a.nq * a.steps), V / (a.nq * a.steps))) if use_codec else "plain exact traversal"},
@@ -858,13 +863,16 @@ def main():
                      "traffic": profiled_traffic(a, L, use_codec),
                      "traffic_source": "profiles/traffic.json (ncu --set full capture of this workload by the builder, "
                                        "not measured in this run)",
-                     "kernel": "traverse_kernel" + (" (exact routing, int8 pre-filter)" if use_codec else ""),
+                     "kernel": "traverse_kernel" + (" (exact routing, int8 pre-filter)" if use_codec else
+                                                    " (int8 routing; the rerank kernel's bytes and time are included)"
+                                                    if a.route == "int8" else ""),
                      "kernel_ms": kern_ms / a.steps, "rerank_kernel_ms": rerank_ms / a.steps,
                      "kernel_ms_note": "CUDA-event duration of one launch at a time (lmd_stats.traverse_ms); with %d batches "
                                        "in flight a step takes ms_per_step" % depth,
                      "achieved_in_flight": alg_bytes / a.steps / (dev_ms / a.steps * 1e-3) / 1e9 / world if world else None,
                      "algorithmic_bytes_per_launch": alg_bytes // a.steps,
                      "bytes_formula": ("E * code_block_bytes + F * 4D + Q * (4D + 12k)" if use_codec else
+                                       "E * code_block_bytes + C * 4D + Q * (8D + 12k + 16L)" if a.route == "int8" else
                                        "E * 4R + V * 4D + Q * (4D + 12k)"),
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
                      "E_per_query": E / (a.nq * a.steps), "V_per_query": V / (a.nq * a.steps),

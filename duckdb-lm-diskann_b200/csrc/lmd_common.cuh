@@ -94,6 +94,7 @@ struct Tuning {
 	int prefilter = 1;     // exact routing on a codec store: 1 = int8 lower-bound pre-filter for batches that fill the GPU, 2 = for every batch, 0 = plain traversal
 	int pf_g = 2;          // rows in flight per team of the pre-filtered kernels (1 or 2)
 	int row_prefetch = 2;  // L2 prefetch of the rows of a gather: 2 = auto, 1 = always, 0 = never
+	int nbr_prefetch = 0;  // neighbour rows of admitted candidates into L2: 0 = never, 1 = small-batch kernels, 2 = always
 };
 
 // Everything ONE in-flight search call owns: its stream, events, statistics counters and staging scratch. The store has

@@ -71,6 +71,7 @@ struct KParams {
 	uint32_t prefilter;     // exact routing: 1 = the int8 lower bound decides which neighbours' rows are fetched at all
 	uint32_t pf_g;          // host side only: rows in flight per team of the pre-filtered kernels (1 or 2)
 	uint32_t row_prefetch;  // 2 = auto (see the gather), 1 = always prefetch the rows of a gather into L2, 0 = never
+	uint32_t nbr_prefetch;  // 1 = prefetch the neighbour rows of admitted candidates (small-batch kernels)
 };
 
 #define FULL 0xFFFFFFFFu
@@ -986,6 +987,14 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 				float worst = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
 				const bool pass = have && (n < L || d < worst);
 				uint32_t amask = __ballot_sync(FULL, pass);
+				if (!SIDE && p.nbr_prefetch && pass) {
+					// small batches: the next expansion is often one of the candidates admitted right now - pull their
+					// neighbour rows into L2 while the list is being merged (the runner-up's row is already there)
+					const uint32_t *nx = p.nbrs + (uint64_t)myid * p.r;
+					for (uint32_t l = 0; l < nbr_lines; l++) {
+						asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + l * 32));
+					}
+				}
 				if (__popc(amask) >= (int)p.merge_min) {
 					// same result as the one-by-one loop below, in one merge (see list_merge_batch)
 					const uint64_t bkey = warp_sort_keys(pass ? make_key(d, myid) : LMD_KEY_NONE, lane);

@@ -261,6 +261,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 		lpl = lpl_coarse(lpl); // the filtered kernels exist for these list sizes only
 		p.allowed = a.d_allowed;
 	}
+	p.nbr_prefetch = (s->tune.nbr_prefetch == 2 || (s->tune.nbr_prefetch == 1 && p.latency)) ? 1u : 0u;
 	p.list_cap = (uint32_t)lpl * 32;
 	p.merge_min = (uint32_t)(s->tune.merge_min > 0 ? s->tune.merge_min : 5);
 	p.prefetch_planes = s->tune.prefetch_planes ? 1u : 0u;

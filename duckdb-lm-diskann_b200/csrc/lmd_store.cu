@@ -1120,6 +1120,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		s->tune.plane_filter_cap = value ? 1 : 0;
 	} else if (k == "prefilter") {
 		s->tune.prefilter = value == 2 ? 2 : (value ? 1 : 0);
+	} else if (k == "nbr_prefetch") {
+		s->tune.nbr_prefetch = (int)value;
 	} else if (k == "row_prefetch") {
 		s->tune.row_prefetch = value == 0 ? 0 : (value == 1 ? 1 : 2);
 	} else if (k == "pf_g") {

@@ -27,12 +27,13 @@ for codec in (0, 1):
         store.enable_codec()
     for pre in ((1, 2) if codec else (1,)):
         store.set_tuning("prefilter", pre)
-        for rp in (2, 1, 0):
+        for rp, nbp in ((2, 0), (2, 1), (0, 0)):
             store.set_tuning("row_prefetch", rp)
+            store.set_tuning("nbr_prefetch", nbp)
             a = med(lambda i: store.search_raw(qp[i % 512:i % 512 + 1], 1, 10, 56, out_ids=ids_p, out_dist=d_p, stats=False))
             b = med(lambda i: store.search_raw(qn[i % 512:i % 512 + 1], 1, 10, 56, out_ids=ids_n, out_dist=d_n, stats=False))
             st = store.search_raw(qp[0:1], 1, 10, 56, out_ids=ids_p, out_dist=d_p)
-            rows.append({"codec": codec, "prefilter": pre, "row_prefetch": rp, "pinned_us": a, "pageable_us": b,
+            rows.append({"codec": codec, "prefilter": pre, "row_prefetch": rp, "nbr_prefetch": nbp, "pinned_us": a, "pageable_us": b,
                          "kernel_us": round(st.traverse_ms * 1e3, 1)})
             print(rows[-1], file=sys.stderr, flush=True)
 print(json.dumps({"probe": "single-query latency, 1M x 128, L=56", "rows": rows}))

@@ -15,12 +15,15 @@ ap.add_argument("--L", type=int, default=56)
 ap.add_argument("--steps", type=int, default=60)
 ap.add_argument("--codec", action="store_true")
 ap.add_argument("--route", default="exact")
+ap.add_argument("--tune", nargs="*", default=[])
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 x = wl.gen(a.rows, a.dims, 42, dev)
 store, _ = wl.build_store(lmd, x, 32, "L2", 0)
 if a.codec:
     store.enable_codec()
+for kv in a.tune:
+    store.set_tuning(kv.split("=")[0], int(kv.split("=")[1]))
 route = {"exact": lmd.ROUTE_EXACT, "int8": lmd.ROUTE_INT8}[a.route]
 qs = [wl.gen(a.nq, a.dims, 43 + 17 * b, dev) for b in range(4)]
 out = []
@@ -57,4 +60,4 @@ for depth in (1, 2, 3, 4):
     for c in ctxs:
         c.close()
 print(json.dumps({"probe": "batches in flight", "rows": a.rows, "dims": a.dims, "nq": a.nq, "L": a.L, "codec": a.codec,
-                  "route": a.route, "results": out}))
+                  "route": a.route, "tune": a.tune, "results": out}))

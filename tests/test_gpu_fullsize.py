@@ -180,3 +180,51 @@ def test_store_larger_than_the_device_is_refused(lmd):
     assert e.value.status == lmd.ERR_OOM
     with lmd.Store(96, 32, capacity=1000) as s:  # the device is still usable afterwards
         assert s.node_count == 0
+
+
+def test_full_size_filtered_ternary(lmd, oracle):
+    """VERDICT r1 next #1c: a filtered search WITH ternary routing at the 1 M size (1 M x 128 cosine, 30 % of the rows
+    allowed, L = 96): properties over the whole 10 k batch + parity with the oracle's dual-heap restatement on a sample.
+    Parity unpinned by the reference (it implements neither); the tie region is set to the oracle-exact size."""
+    import torch
+    dev = torch.device("cuda", 0)
+    DIMS, L = 128, 96
+    x = _gen(torch, N, 42, dev, DIMS, True)
+    q = _gen(torch, NQ, 43, dev, DIMS, True)
+    g = torch.Generator(device=dev)
+    g.manual_seed(9)
+    allowed_mask = torch.rand(N, generator=g, device=dev) < 0.3
+    allowed = torch.nonzero(allowed_mask).squeeze(1)
+    with lmd.Store(DIMS, R, metric=METRIC["COSINE"], capacity=N, l_search=100) as s:
+        s.upload_vectors(x)
+        s.build_graph(l_insert=64)
+        s.set_tuning("tie_slots", 64)
+        ids = torch.empty((NQ, K), dtype=torch.int64, device=dev)
+        dist = torch.empty((NQ, K), dtype=torch.float32, device=dev)
+        cnt = torch.empty((NQ,), dtype=torch.int32, device=dev)
+        with s.make_filter(allowed) as f:
+            assert f.count == int(allowed.numel())
+            st = s.search_raw(q, NQ, K, L, route=lmd.ROUTE_TERNARY, out_ids=ids, out_dist=dist, out_count=cnt, filter=f)
+            plain = torch.empty((NQ, K), dtype=torch.int64, device=dev)
+            st_plain = s.search_raw(q, NQ, K, L, route=lmd.ROUTE_TERNARY, out_ids=plain)
+            # the exploration is the unfiltered search's: same expansions
+            assert st.expansions == st_plain.expansions and st.launches == 2
+            valid = ids >= 0
+            assert bool(((valid.sum(1)) == cnt).all()) and bool((cnt > 0).all())
+            assert bool(allowed_mask[ids.clamp_min(0)][valid].all())          # only allowed rows come back
+            dd = torch.where(valid, dist, torch.full_like(dist, float("inf")))
+            assert bool((dd[:, 1:] >= dd[:, :-1]).all())
+            sel = valid.reshape(-1)
+            xr = x[ids.reshape(-1)[sel]].double()
+            qr = q.repeat_interleave(K, dim=0)[sel].double()
+            ref = 1.0 - ((xr * qr).sum(1) / (xr.pow(2).sum(1).sqrt() * qr.pow(2).sum(1).sqrt())).clamp(-1.0, 1.0)
+            assert bool(((dist.reshape(-1)[sel].double() - ref).abs() <= 1e-5 * ref.abs() + 2e-6).all())
+            # sample parity against the oracle's filtered (dual heap) search on the index as the device built it
+            sample = np.arange(0, NQ, NQ // 100)[:100]
+            blocks = s.download_blocks(0, N)
+            qs = q[torch.from_numpy(sample).to(dev)].cpu().numpy()
+            o = oracle.search(blocks, s.block_bytes, DIMS, R, qs, K, L, metric=METRIC["COSINE"], route=1, entry_row_id=0,
+                              allowed=allowed_mask.cpu().numpy().astype(np.uint8))
+            check_parity(ids.cpu().numpy()[sample], dist.cpu().numpy()[sample], cnt.cpu().numpy()[sample].astype(np.uint32),
+                         o[0], o[1], o[2], what="1M filtered ternary sample")
+            assert st.tie_overflows == 0
