@@ -634,10 +634,12 @@ __device__ __forceinline__ int find_unexpanded(const uint64_t *s_list, int n, in
 	return -1;
 }
 
-// Ternary planes of the query (core/ternary_quantization.hpp:146-199 EncodeTernary) as 32-bit halves:
-// s_qp[g] holds bits [32g, 32g+32) of the positive plane, s_qn likewise.
+// Ternary planes of the query (core/ternary_quantization.hpp:146-199 EncodeTernary), one 16-byte entry per 64-bit word w:
+// s_q4[w] = {pos bits [64w, 64w+32), pos bits [64w+32, 64w+64), neg likewise} - the layout of a sidecar entry, so that a
+// word of the query is ONE broadcast 128-bit shared-memory load. (s_qn is unused; kept in the signature of the callers.)
 __device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t qi, int lane, uint32_t *s_qp,
                                                     uint32_t *s_qn) {
+	(void)s_qn;
 	const float *src = p.queries + (uint64_t)qi * p.q_stride;
 	for (uint32_t g = 0; g < p.words * 2; g++) {
 		uint32_t f = g * 32 + lane;
@@ -645,11 +647,21 @@ __device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t q
 		uint32_t bp = __ballot_sync(FULL, v > 0.0f);
 		uint32_t bn = __ballot_sync(FULL, v < 0.0f);
 		if (lane == 0) {
-			s_qp[g] = bp;
-			s_qn[g] = bn;
+			s_qp[(g >> 1) * 4 + (g & 1)] = bp;
+			s_qp[(g >> 1) * 4 + 2 + (g & 1)] = bn;
 		}
 	}
 	__syncwarp();
+}
+
+// One 64-bit word of core/ternary_quantization.hpp:269-296 (Dot_scalar): pop(q+ & v+) - pop(q+ & v-) - pop(q- & v+) +
+// pop(q- & v-). A vector's positive and negative planes are disjoint (a dimension is > 0 or < 0, EncodeTernary :146-199;
+// the sidecar zeroes dead neighbours), so (q+ & v+) and (q- & v-) are disjoint too and one popcount of their union counts
+// both - half the popcounts (the slow instruction here) for the same integer.
+__device__ __forceinline__ int ternary_word(const uint4 q, const uint4 v) {
+	const uint32_t agree0 = (q.x & v.x) | (q.z & v.z), agree1 = (q.y & v.y) | (q.w & v.w);
+	const uint32_t differ0 = (q.x & v.z) | (q.z & v.x), differ1 = (q.y & v.w) | (q.w & v.y);
+	return __popc(agree0) + __popc(agree1) - __popc(differ0) - __popc(differ1);
 }
 
 // core/ternary_quantization.hpp:269-296 (Dot_scalar) + core/distance.hpp:229-235 for neighbour j of the expanded node.
@@ -660,8 +672,10 @@ __device__ __forceinline__ void encode_query_planes(const KParams &p, uint32_t q
 template <int WORDS>
 __device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_t *side_blk, uint32_t j,
                                                   const uint32_t *s_qp, const uint32_t *s_qn) {
+	(void)s_qn;
 	const uint32_t words = WORDS > 0 ? (uint32_t)WORDS : p.words;
 	const uint4 *pl = reinterpret_cast<const uint4 *>(side_blk + p.side_data_off) + j;
+	const uint4 *q4 = reinterpret_cast<const uint4 *>(s_qp);
 	int score = 0;
 	if (WORDS > 0) {
 		uint4 v[WORDS > 0 ? WORDS : 1];
@@ -671,16 +685,11 @@ __device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_
 		}
 #pragma unroll
 		for (int w = 0; w < WORDS; w++) {
-			const uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
-			score += __popc(qp0 & v[w].x) + __popc(qp1 & v[w].y) + __popc(qn0 & v[w].z) + __popc(qn1 & v[w].w);
-			score -= __popc(qp0 & v[w].z) + __popc(qp1 & v[w].w) + __popc(qn0 & v[w].x) + __popc(qn1 & v[w].y);
+			score += ternary_word(q4[w], v[w]);
 		}
 	} else {
 		for (uint32_t w = 0; w < words; w++) {
-			const uint4 v = __ldg(pl + w * p.r);
-			const uint32_t qp0 = s_qp[2 * w], qp1 = s_qp[2 * w + 1], qn0 = s_qn[2 * w], qn1 = s_qn[2 * w + 1];
-			score += __popc(qp0 & v.x) + __popc(qp1 & v.y) + __popc(qn0 & v.z) + __popc(qn1 & v.w);
-			score -= __popc(qp0 & v.z) + __popc(qp1 & v.w) + __popc(qn0 & v.x) + __popc(qn1 & v.y);
+			score += ternary_word(q4[w], __ldg(pl + w * p.r));
 		}
 	}
 	float sim = (float)score;
