@@ -410,7 +410,32 @@ __device__ __forceinline__ bool bucket_test_and_set(uint32_t *tab, uint32_t bmas
 	return true;
 }
 
+// ---- visited filter, mode 2: direct-mapped 16-bit entries ----------------------------------------------------------
+// One load, one compare, one store - a quarter of the bucket filter's instructions - for the kernels that are bound by
+// instruction issue and for which a forgotten node is cheap (the compressed routes compute every neighbour's routing
+// distance anyway; behind the int8 pre-filter a re-met node that was turned away before is turned away again without a row
+// fetch). Same bijective hash as mode 1: entry index = h >> 15, entry = 15-bit tag | 0x8000, so (index, tag) identifies the
+// node exactly below 2^(log2(entries) + 15) nodes. A colliding node simply replaces the resident one (same contract as
+// the other modes: forgetting costs a re-evaluation, never a result). Lanes of one warp racing on an entry: either write
+// may win; a node listed twice in one neighbour row is evaluated twice and dropped as a duplicate at insert.
+__device__ __forceinline__ bool direct_test_and_set(uint32_t *tab, uint32_t hmask, uint32_t id, uint32_t &evictions) {
+	uint32_t h = (id * 0x9E3779B1u) & hmask;
+	h ^= h >> 15;
+	const uint32_t entry = (h & 0x7FFFu) | 0x8000u;
+	uint16_t *slot = reinterpret_cast<uint16_t *>(tab) + (h >> 15);
+	const uint32_t old = *slot;
+	if (old == entry) {
+		return false;
+	}
+	*slot = (uint16_t)entry;
+	evictions += old != 0u ? 1u : 0u;
+	return true;
+}
+
 __device__ __forceinline__ bool visited_test_and_set(const KParams &p, uint32_t *tab, uint32_t id, uint32_t &evictions) {
+	if (p.filter_mode == 2) {
+		return direct_test_and_set(tab, p.filter_hmask, id, evictions);
+	}
 	if (p.filter_mode) {
 		return bucket_test_and_set(tab, p.filter_bmask, p.filter_hmask, id, evictions);
 	}

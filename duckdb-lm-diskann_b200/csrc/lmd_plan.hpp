@@ -31,8 +31,31 @@ inline FilterPlan plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32
 	FilterPlan f;
 	const double expect = 0.8 * (double)r * 1.05 * (double)L;
 	int mode = tune_mode;
-	if (mode != 0 && mode != 1) {
+	if (mode != 0 && mode != 1 && mode != 2) {
 		mode = 1;
+	}
+	if (mode == 2) {
+		// direct-mapped 16-bit entries (lmd_kernels.cuh direct_test_and_set): 2 bytes per entry, exact below 2^(lg + 15)
+		// nodes; sized like mode 1 at twice the slack (a collision forgets at once), shrunk to the warp budget
+		uint32_t lg2 = 10;
+		if (tune_log2 >= 6 && tune_log2 <= 16) {
+			lg2 = (uint32_t)tune_log2;
+		} else {
+			while (lg2 < 15 && (double)(1u << lg2) * 0.35 < expect) {
+				lg2++;
+			}
+			const size_t budget2 = ((size_t)227 * 1024 - (size_t)min_warps / 4 * 1024) / min_warps;
+			while (lg2 > 9 && fixed_bytes + ((size_t)2 << lg2) > budget2) {
+				lg2--;
+			}
+		}
+		while (lg2 < 16 && nodes >= (1ull << (lg2 + 15))) {
+			lg2++;
+		}
+		f.mode = 2;
+		f.lg = lg2;
+		f.bytes = 2u << lg2;
+		return f;
 	}
 	auto fits_exact = [&](uint32_t lg) { return lg >= 4 && nodes < (1ull << (lg - 3 + 15)); };
 	uint32_t lg;
@@ -88,6 +111,19 @@ inline FilterPlan plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32
 	f.lg = lg;
 	f.bytes = (uint32_t)((mode == 1 ? 2u : 4u) << lg);
 	return f;
+}
+
+// Which visited filter a launch gets when the "filter_mode" key is not set: the kernels that read a routing sidecar (ternary,
+// int8 route, exact route behind the int8 pre-filter) are bound by instruction issue and re-meet forgotten nodes cheaply,
+// so they take the direct-mapped filter (mode 2: a quarter of the instructions per test); the plain exact kernels are
+// bound by the bytes every re-evaluated row costs and keep the two-choice buckets (mode 1). Measured on 1 M rows, 10 k
+// queries (profiles/r2_19_*_fm.json): int8 route L = 56 0.66 -> 0.57 ms, ternary 768-d L = 80 1.42 -> 1.25 ms,
+// pre-filtered exact L = 56 1.03 -> 0.99 ms; same ids and distances (tests: results do not depend on the filter).
+inline int plan_filter_mode(int tune_mode, bool reads_sidecar, bool filtered) {
+	if (tune_mode == 0 || tune_mode == 1 || tune_mode == 2) {
+		return tune_mode;
+	}
+	return reads_sidecar && !filtered ? 2 : 1;
 }
 
 // Which traversal family serves an exact, unfiltered search over 128-d / 96-d rows: 0 = throughput kernels (2 rows in

@@ -285,7 +285,8 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// (profiles/r50_small_batch_L128.json).
 	const bool exact = a.route == LMD_ROUTE_EXACT; // (with or without the pre-filter: rows are gathered either way)
 	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl, a.L);
-	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps, s->tune.filter_mode,
+	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps,
+	                                  plan_filter_mode(s->tune.filter_mode, kroute != LMD_ROUTE_EXACT, a.d_allowed != nullptr),
 	                                  (int)s->tune.filter_log2);
 	if (kroute == LMD_ROUTE_EXACT && !p.strict && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
 		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
@@ -299,7 +300,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	p.filter_mask = (1u << fp.lg) - 1;
 	p.filter_shift = 32 - fp.lg;
 	p.filter_bmask = (1u << (fp.lg - 3)) - 1;
-	p.filter_hmask = (uint32_t)((1ull << (fp.lg - 3 + 15)) - 1);
+	p.filter_hmask = fp.mode == 2 ? (uint32_t)((1ull << (fp.lg + 15)) - 1) : (uint32_t)((1ull << (fp.lg - 3 + 15)) - 1);
 	p.res_off = (uint32_t)((fixed - res_bytes + fp.bytes + 15) / 16 * 16);
 	p.warp_smem_bytes = (uint32_t)(p.res_off + (res_bytes + 15) / 16 * 16);
 	return dispatch_traverse(p, s, a.nq, lpl, kroute, st);

@@ -17,6 +17,9 @@ uint32_t plan_min_warps(int family, int exact, int specialised, int filtered, in
 uint32_t plan_min_warps_l(int family, int exact, int specialised, int filtered, int lpl, uint32_t L) {
 	return lmd::plan_min_warps(family, exact != 0, specialised != 0, filtered != 0, lpl, L);
 }
+int plan_filter_mode(int tune_mode, int reads_sidecar, int filtered) {
+	return lmd::plan_filter_mode(tune_mode, reads_sidecar != 0, filtered != 0);
+}
 uint32_t plan_tie_slots(uint32_t L) {
 	return lmd::plan_tie_slots(L);
 }

@@ -113,3 +113,17 @@ def test_sidecar_routes_want_32_warps_and_a_short_tie_region(plan):
     out = (ctypes.c_uint32 * 3)()  # ternary planes of 12 words; the pre-sidecar 2 KB cap ("plane_filter_cap") is off
     plan.plan_filter(1_000_000, 32, 12, 80, _fixed(3, words=12, ternary=True), 0, 32, -1, 0, out)
     assert tuple(out)[1:] == (11, 4096)
+
+
+def test_direct_mapped_filter_for_the_sidecar_routes(plan):
+    """profiles/r2_19_*_fm.json: mode 2 (direct-mapped 16-bit entries) for the issue-bound kernels, mode 1 otherwise."""
+    assert plan.plan_filter_mode(-1, 1, 0) == 2 and plan.plan_filter_mode(-1, 0, 0) == 1
+    assert plan.plan_filter_mode(-1, 1, 1) == 1                      # filtered kernels keep the buckets
+    assert [plan.plan_filter_mode(m, 1, 0) for m in (0, 1, 2)] == [0, 1, 2]   # an explicit key wins
+    out = (ctypes.c_uint32 * 3)()
+    plan.plan_filter(1_000_000, 32, 0, 56, _fixed(2) + 128, 0, 32, 2, 0, out)   # int8 route, L = 56, 32 warps
+    assert tuple(out) == (2, 11, 4096)
+    plan.plan_filter(1_000_000, 32, 0, 56, _fixed(2) + 128, 0, 24, 2, 0, out)   # exact + pre-filter, 24 warps
+    assert tuple(out) == (2, 12, 8192)
+    plan.plan_filter(100_000_000, 32, 0, 56, _fixed(2) + 128, 0, 32, 2, 0, out)  # 100 M nodes need 2^(lg + 15) > nodes
+    assert tuple(out) == (2, 12, 8192)
