@@ -417,7 +417,9 @@ __device__ __forceinline__ bool bucket_test_and_set(uint32_t *tab, uint32_t bmas
 // fetch). Same bijective hash as mode 1: entry index = h >> 15, entry = 15-bit tag | 0x8000, so (index, tag) identifies the
 // node exactly below 2^(log2(entries) + 15) nodes. A colliding node simply replaces the resident one (same contract as
 // the other modes: forgetting costs a re-evaluation, never a result). Lanes of one warp racing on an entry: either write
-// may win; a node listed twice in one neighbour row is evaluated twice and dropped as a duplicate at insert.
+// may win. Two lanes can never hold the SAME node: the neighbour-slot view drops the second occurrence of a row id inside
+// one row when it is built (lmd_store.cu first_occurrence(); the reference's visited set skips it just the same,
+// Searcher.cpp:135-139) - an in-warp __match_any_sync here cost the ternary kernel 30 %.
 __device__ __forceinline__ bool direct_test_and_set(uint32_t *tab, uint32_t hmask, uint32_t id, uint32_t &evictions) {
 	uint32_t h = (id * 0x9E3779B1u) & hmask;
 	h ^= h >> 15;
@@ -929,6 +931,7 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 				if (id != LMD_INVALID_SLOT && id != entry_guard) {
 					isnew = visited_test_and_set(p, s_filter, id, n_evict);
 				}
+
 				const uint32_t mask = __ballot_sync(FULL, isnew);
 				const int m = __popc(mask);
 				if (m == 0) {

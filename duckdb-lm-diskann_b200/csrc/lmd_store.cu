@@ -194,6 +194,19 @@ __global__ void unpack_vectors_kernel(const uint8_t *__restrict__ blocks, uint64
 	}
 }
 
+// A row id listed twice among the first `count` entries of one block: the reference evaluates the first occurrence and
+// skips the second (it is in `visited_nodes` by then, core/Searcher.cpp:135-139), for every query alike - so the derived
+// neighbour-slot view keeps the first occurrence only. The blocks themselves are never changed. (The reference's own
+// RobustPrune and lmd_build_graph never write such rows; a host may.)
+__device__ __forceinline__ bool first_occurrence(const int64_t *ids, uint32_t j, int64_t rid) {
+	for (uint32_t e = 0; e < j; e++) {
+		if (ids[e] == rid) {
+			return false;
+		}
+	}
+	return true;
+}
+
 // One thread per (node, j): resolve neighbour j of the mirrored block to a slot.
 // core/GraphManager.cpp:241-254: only the first `count` ids are neighbours, INT64_MAX entries are dropped;
 // core/Searcher.cpp:146-148: a row id that does not resolve is skipped.
@@ -212,7 +225,7 @@ __global__ void build_sidecar_kernel(const uint8_t *__restrict__ blocks, uint64_
 	uint32_t out = LMD_INVALID_SLOT;
 	if (j < count) {
 		int64_t rid = reinterpret_cast<const int64_t *>(blk + ids_off)[j];
-		if (rid != INT64_MAX) {
+		if (rid != INT64_MAX && first_occurrence(reinterpret_cast<const int64_t *>(blk + ids_off), j, rid)) {
 			if (identity) {
 				out = (rid >= 0 && (uint64_t)rid < n) ? (uint32_t)rid : LMD_INVALID_SLOT;
 			} else {
@@ -257,7 +270,7 @@ __global__ void refresh_slots_kernel(const uint8_t *__restrict__ blocks, uint64_
 		uint32_t out = LMD_INVALID_SLOT;
 		if (j < count) {
 			int64_t rid = reinterpret_cast<const int64_t *>(blk + ids_off)[j];
-			if (rid != INT64_MAX) {
+			if (rid != INT64_MAX && first_occurrence(reinterpret_cast<const int64_t *>(blk + ids_off), j, rid)) {
 				out = identity ? ((rid >= 0 && (uint64_t)rid < n_nodes) ? (uint32_t)rid : LMD_INVALID_SLOT)
 				               : map_lookup(map_keys, map_vals, map_mask, rid);
 			}

@@ -426,3 +426,48 @@ def test_tensor_rerank_rejects_what_it_cannot_tile(lmd, make_index):
         assert e.value.status == lmd.ERR_UNSUPPORTED
         with pytest.raises(lmd.LmdError):
             s.search(ix["queries"], 5, 32, flags=lmd.SEARCH_TENSOR_RERANK | lmd.SEARCH_STRICT_FP)
+
+
+# ---- a neighbour row that names the same node twice (all visited-filter kinds, all routes) ----------------------------
+@pytest.mark.parametrize("metric,route", [("L2", "exact"), ("L2", "prefilter"), ("L2", "int8"), ("COSINE", "ternary")])
+def test_duplicate_neighbour_ids_in_a_row(lmd, oracle, fixtures_mod, metric, route):
+    """The reference's visited set drops the second occurrence (core/Searcher.cpp:135-139). The atomic filters do the same;
+    the direct-mapped filter (mode 2) has no atomics and needs the in-warp match: no id may come back twice, the expansion
+    counts stay the oracle's."""
+    n, dims, r = 1500, 128, 32
+    ix = fixtures_mod.build_index(n, dims, r, metric=metric, device="cpu", kind="iid")
+    blocks = ix["blocks"].numpy().copy()
+    lay = ix["layout"]
+    ids_view = blocks[:, lay["ids_off"]:lay["ids_off"] + 8 * r].view(np.int64)
+    cnt_view = blocks[:, 0:2].view(np.uint16)
+    rng = np.random.default_rng(6)
+    for node in range(n):  # every row: two of its entries repeat another two
+        c = int(cnt_view[node, 0])
+        if c >= 6:
+            a, b = rng.choice(c, 2, replace=False)
+            ids_view[node, a] = ids_view[node, b]
+            ids_view[node, (a + 1) % c] = ids_view[node, (b + 3) % c]
+    if metric == "COSINE":  # the planes of a repeated entry must be the repeated node's (ternary routing reads them)
+        blocks = fixtures_mod.pack_blocks(ix["x"], np.where(np.arange(r)[None, :] < cnt_view.astype(np.int64),
+                                                            ids_view, -1), cnt_view[:, 0].astype(np.int64), r).numpy()
+    q = fixtures_mod.make_dataset(64, dims, kind="iid", seed=46, normalize=(metric == "COSINE"))
+    k, L = 10, 48
+    kw = {"route": {"ternary": lmd.ROUTE_TERNARY, "int8": lmd.ROUTE_INT8}.get(route, lmd.ROUTE_EXACT)}
+    o_route = {"ternary": 1, "int8": 2}.get(route, 0)
+    with lmd.Store(dims, r, metric=METRIC[metric], capacity=n) as s:
+        s.upload(blocks)
+        s.set_entry(0)
+        s.set_tuning("tie_slots", 64)
+        if route in ("prefilter", "int8"):
+            s.enable_codec()
+            s.set_tuning("prefilter", 2)
+            oracle.set_codec(*s.get_codec())
+        o = oracle.search(blocks, lay["block_bytes"], dims, r, q, k, L, metric=METRIC[metric], entry_row_id=0, route=o_route)
+        for mode in (0, 1, 2):
+            s.set_tuning("filter_mode", mode)
+            ids, dist, cnt, st, qs = s.search(q, k, L, qstats=True, **kw)
+            for row in ids:
+                v = row[row >= 0]
+                assert len(set(v.tolist())) == len(v), (mode, row)
+            check_parity(ids, dist, cnt, o[0], o[1], o[2], what="duplicate neighbours, filter mode %d" % mode)
+            assert np.array_equal(qs[:, 0].astype(np.int64), o[3][:, 0].astype(np.int64)), mode
