@@ -125,6 +125,8 @@ SYMBOLS = [
     ("lmd_robust_prune_batch", C.c_int32, [_P, _P, _P, C.c_uint64, C.c_uint32, C.c_float, _P, _P]),
     ("lmd_store_download_blocks", C.c_int32, [_P, C.c_uint64, C.c_uint64, _P]),
     ("lmd_store_download_row_ids", C.c_int32, [_P, C.c_uint64, C.c_uint64, _P]),
+    ("lmd_static_scratch_bytes", C.c_uint64, []),
+    ("lmd_search_batch_static", C.c_int32, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, _P, _P]),
     ("lmd_last_error", C.c_char_p, []),
     ("lmd_abi_version", C.c_uint32, []),
     ("lmd_set_tuning", C.c_int32, [_P, C.c_char_p, C.c_int64]),
@@ -346,6 +348,12 @@ class Store:
         _check(call(_ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist), _ptr(out_count),
                     _ptr(out_qstats), C.byref(st)))
         return st
+
+    def search_static(self, queries, nq, k, L, route, out_ids, out_dist, out_count, flags=0, cuda_stream=None):
+        """lmd_search_batch_static: device / pinned buffers only, the kernels' scratch in the library's static device
+        array (no allocation inside the call; see include/lmd_b200.h for the limit and the sharing rule)."""
+        _check(lib().lmd_search_batch_static(self._h, _ptr(queries), nq, k, L, route, flags, _ptr(out_ids), _ptr(out_dist),
+                                             _ptr(out_count), cuda_stream or None))
 
     def search(self, queries, k, L=0, route=ROUTE_EXACT, flags=0, qstats=False, filter=None, ctx=None):
         """Host-buffer search: queries [nq, dims] float32 numpy -> (ids [nq,k] int64, dist [nq,k] f32,

@@ -12,7 +12,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "liblmd_b200.so")
-SOURCES = ["lmd_store.cu", "lmd_sidecar.cu", "lmd_search_kernels.cu", "lmd_api.cu", "lmd_group.cu", "lmd_rerank_tc.cu", "lmd_build.cu"]
+SOURCES = ["lmd_store.cu", "lmd_sidecar.cu", "lmd_search_kernels.cu", "lmd_api.cu", "lmd_group.cu", "lmd_rerank_tc.cu", "lmd_build.cu", "lmd_static.cu"]
 # lmd_kernel_inst.cu is compiled once per kernel family: (object suffix, extra defines)
 INSTANCES = [("trav_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=0", "-DLMD_INST_METRIC=%d" % m, "-DLMD_INST_ROUTE=%d" % r])
              for m, r in ((1, 0), (2, 0), (3, 0), (2, 1), (3, 1), (1, 2), (1, 3))] + \

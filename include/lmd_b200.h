@@ -300,6 +300,31 @@ lmd_status lmd_store_download_blocks(lmd_store *s, uint64_t first_slot, uint64_t
  * blocks back to the host's storage pairs them through this (core/GraphManager.hpp:122 is the reference's row id map). */
 lmd_status lmd_store_download_row_ids(lmd_store *s, uint64_t first_slot, uint64_t n, int64_t *out_row_ids);
 
+/* --- searching without allocating. NO COUNTERPART IN THE REFERENCE: added for
+ *     callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The search of lmd_search_batch (same kernels, same results) with the kernels' scratch - the work counter / statistics
+ * block and, for the ternary and int8 routes, the nq * L candidate keys handed to the rerank kernel - in ONE file-scope
+ * __device__ array of LMD_STATIC_SCRATCH_BYTES that every device loading the library holds until the process exits. The
+ * call allocates nothing: no cudaMalloc / cudaFree / cudaHostAlloc, no allocating library routine.
+ *   - queries [nq][dims], out_ids / out_dist [nq][k], out_count [nq]: device memory or pinned (mapped) host memory, all
+ *     four required; pageable memory is refused (staging it would allocate);
+ *   - limit: 256 + nq * L * 8 <= LMD_STATIC_SCRATCH_BYTES for the ternary / int8 routes (16 383 queries at L = 64); the
+ *     exact route uses the 256-byte counter block only; beyond the limit -> LMD_ERR_INVALID_ARG with the sizes in
+ *     lmd_last_error();
+ *   - the store must already be prepared for the route - one earlier lmd_search_batch on that route (any batch size)
+ *     after the last change to the store does it: building a view or sidecar allocates, so an unprepared route ->
+ *     LMD_ERR_STATE;
+ *   - cuda_stream: the cudaStream_t to enqueue on (NULL = the default stream); flags: 0, or LMD_SEARCH_ASYNC to return
+ *     without synchronising;
+ *   - ALL calls on a device share the array and it keeps the last call's contents (the counter block is cleared on the
+ *     stream before each launch; the candidate region is rewritten before it is read): two calls that overlap on the GPU
+ *     RACE - serialise them (one stream, or events between streams). */
+#define LMD_STATIC_SCRATCH_BYTES (8u << 20)
+uint64_t lmd_static_scratch_bytes(void);
+lmd_status lmd_search_batch_static(lmd_store *s, const float *queries, uint64_t nq, uint32_t k, uint32_t L, uint32_t route,
+                                   uint32_t flags, int64_t *out_ids, float *out_dist, uint32_t *out_count,
+                                   void *cuda_stream);
+
 /* --- misc --- */
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
 uint32_t lmd_abi_version(void);
