@@ -81,6 +81,7 @@ __host__ __device__ __forceinline__ float key_dist(uint64_t k) {
 // ---- the store ---------------------------------------------------------------------------------
 struct Tuning {
 	int filter_log2 = 0;   // log2(entries of the visited filter), 0 = heuristic
+	int filter_entries = 0; // filter_mode 3: entries of the modulo-mapped table
 	int filter_mode = -1;  // -1 = auto (1 when the store is small enough), 0 = u32 open addressing, 1 = 16-bit buckets
 	int warps_per_cta = 0; // 0 = whichever of 4 / 2 / 1 packs the most warps on an SM
 	int ctas_per_sm = 0;   // 0 = as many as shared memory allows

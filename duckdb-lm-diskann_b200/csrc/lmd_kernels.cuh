@@ -49,6 +49,7 @@ struct KParams {
 	uint32_t filter_mode;               // 0 = u32 open addressing, 1 = two-choice buckets of 8 x 16-bit entries
 	uint32_t filter_bmask, filter_hmask; // mode 1: buckets - 1, 2^(log2(buckets) + 15) - 1
 	uint32_t filter_bytes;              // bytes of the table (either mode)
+	uint32_t filter_entries, filter_magic; // mode 3: entries S (any multiple of 8), ceil(2^40 / S)
 	uint32_t prefetch_planes;           // ternary routing: also prefetch the runner-up's plane region
 	uint32_t warp_smem_bytes;
 	// filtered search: bit `slot` set = the row passes the host's filter
@@ -434,7 +435,28 @@ __device__ __forceinline__ bool direct_test_and_set(uint32_t *tab, uint32_t hmas
 	return true;
 }
 
+// Mode 3: the direct-mapped filter over ANY number of entries S, so the table can take exactly the shared memory that is
+// left at the CTA count the kernel wants (a power of two wastes up to half of it). slot = id mod S, tag = id div S + 1:
+// the pair identifies the node exactly for id < min(65535 S, 2^40 / S); the quotient comes from one wide multiply by
+// ceil(2^40 / S). No mixing: row ids next to each other never collide, and a collision only forgets.
+__device__ __forceinline__ bool modulo_test_and_set(uint32_t *tab, uint32_t entries, uint32_t magic, uint32_t id,
+                                                    uint32_t &evictions) {
+	const uint32_t q = (uint32_t)(((uint64_t)id * magic) >> 40);
+	const uint32_t entry = q + 1u;
+	uint16_t *slot = reinterpret_cast<uint16_t *>(tab) + (id - q * entries);
+	const uint32_t old = *slot;
+	if (old == entry) {
+		return false;
+	}
+	*slot = (uint16_t)entry;
+	evictions += old != 0u ? 1u : 0u;
+	return true;
+}
+
 __device__ __forceinline__ bool visited_test_and_set(const KParams &p, uint32_t *tab, uint32_t id, uint32_t &evictions) {
+	if (p.filter_mode == 3) {
+		return modulo_test_and_set(tab, p.filter_entries, p.filter_magic, id, evictions);
+	}
 	if (p.filter_mode == 2) {
 		return direct_test_and_set(tab, p.filter_hmask, id, evictions);
 	}

@@ -23,14 +23,33 @@ inline int lpl_coarse(int lpl) {
 // shrunk until at least `min_warps` warps fit on an SM: the gathers need warps in flight more than a perfect filter.
 struct FilterPlan {
 	uint32_t mode, lg, bytes;
+	uint32_t entries = 0; // mode 3 only: entries of the modulo-mapped table (lg is not used by the kernel then)
 };
+
+// Mode 3 (lmd_kernels.cuh modulo_test_and_set) identifies a node exactly by (id mod S, id div S) while the quotient fits
+// the 16-bit tag and the multiply-shift division is exact: nodes < min(65535 S, 2^40 / S), S >= 512 (32-bit magic).
+inline bool modulo_filter_fits(uint64_t nodes, uint32_t entries) {
+	return entries >= 512 && entries % 8 == 0 && nodes < 65535ull * entries && nodes < (1ull << 40) / entries;
+}
 // `nodes`, `r`, `words`: the store's node count, graph degree and ternary plane words; `ternary`: the route;
 // `tune_mode` / `tune_log2`: the "filter_mode" / "filter_log2" tuning keys (negative / 0 = not set).
 inline FilterPlan plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32_t L, size_t fixed_bytes, bool ternary,
-                              uint32_t min_warps, int tune_mode, int tune_log2) {
+                              uint32_t min_warps, int tune_mode, int tune_log2, int tune_entries = 0) {
 	FilterPlan f;
 	const double expect = 0.8 * (double)r * 1.05 * (double)L;
 	int mode = tune_mode;
+	if (mode == 3) {
+		// "filter_entries" key: direct-mapped table of any size; a store too large for it takes the power-of-two table
+		const uint32_t e = tune_entries >= 512 ? (uint32_t)tune_entries / 8 * 8 : 3504;
+		if (modulo_filter_fits(nodes, e)) {
+			f.mode = 3;
+			f.lg = 12;
+			f.entries = e;
+			f.bytes = 2 * e;
+			return f;
+		}
+		mode = 2;
+	}
 	if (mode != 0 && mode != 1 && mode != 2) {
 		mode = 1;
 	}
@@ -120,10 +139,37 @@ inline FilterPlan plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32
 // queries (profiles/r2_19_*_fm.json): int8 route L = 56 0.66 -> 0.57 ms, ternary 768-d L = 80 1.42 -> 1.25 ms,
 // pre-filtered exact L = 56 1.03 -> 0.99 ms; same ids and distances (tests: results do not depend on the filter).
 inline int plan_filter_mode(int tune_mode, bool reads_sidecar, bool filtered) {
-	if (tune_mode == 0 || tune_mode == 1 || tune_mode == 2) {
+	if (tune_mode >= 0 && tune_mode <= 3) {
 		return tune_mode;
 	}
 	return reads_sidecar && !filtered ? 2 : 1;
+}
+
+// The pre-filtered exact kernel (72 registers: 7 CTAs of 4 warps by the register file) held 6 CTAs per SM because the
+// 8 KB power-of-two filter is what shared memory cut off; the modulo-mapped filter takes exactly what 28 warps leave
+// (3 504 entries = 7 008 bytes at L = 56, D = 128). One batch at a time it changes nothing (0.99 ms); with two batches in
+// flight - the way bench.py and the adapter's combining run it - 0.895 -> 0.82 ms per 10 k queries (profiles/r2_31_*).
+// Returns entries = 0 when the rule does not apply (long lists: fewer than 2 048 entries left; stores beyond the exact
+// range of the 16-bit tag) and the caller keeps plan_filter().
+inline FilterPlan plan_filter_modulo(uint64_t nodes, size_t fixed_bytes, uint32_t warps) {
+	FilterPlan f;
+	f.mode = 0;
+	f.lg = 0;
+	f.bytes = 0;
+	const size_t budget = ((size_t)227 * 1024 - (size_t)warps / 4 * 1024) / warps / 16 * 16;
+	if (budget <= fixed_bytes + 4096) {
+		return f;
+	}
+	uint32_t e = (uint32_t)((budget - fixed_bytes) / 2 / 8 * 8);
+	e = e > 8192 ? 8192 : e;
+	if (!modulo_filter_fits(nodes, e)) {
+		return f;
+	}
+	f.mode = 3;
+	f.lg = 12;
+	f.entries = e;
+	f.bytes = 2 * e;
+	return f;
 }
 
 // Which traversal family serves an exact, unfiltered search over 128-d / 96-d rows: 0 = throughput kernels (2 rows in

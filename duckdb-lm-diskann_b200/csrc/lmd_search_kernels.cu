@@ -285,9 +285,16 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	// (profiles/r50_small_batch_L128.json).
 	const bool exact = a.route == LMD_ROUTE_EXACT; // (with or without the pre-filter: rows are gathered either way)
 	const uint32_t min_warps = plan_min_warps((int)p.latency, exact, specialised, a.d_allowed != nullptr, lpl, a.L);
-	const FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps,
-	                                  plan_filter_mode(s->tune.filter_mode, kroute != LMD_ROUTE_EXACT, a.d_allowed != nullptr),
-	                                  (int)s->tune.filter_log2);
+	FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps,
+	                            plan_filter_mode(s->tune.filter_mode, kroute != LMD_ROUTE_EXACT, a.d_allowed != nullptr),
+	                            (int)s->tune.filter_log2, s->tune.filter_entries);
+	if (kroute == LMD_KROUTE_EXACT_PF && specialised && s->tune.filter_mode < 0 && s->tune.filter_log2 == 0) {
+		// a 7th CTA per SM for the pre-filtered kernel: the filter takes exactly what 28 warps leave (lmd_plan.hpp)
+		const FilterPlan fm = plan_filter_modulo(s->n, fixed, 28);
+		if (fm.entries && fm.bytes < fp.bytes) {
+			fp = fm;
+		}
+	}
 	if (kroute == LMD_ROUTE_EXACT && !p.strict && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
 		// 384-byte rows, and shared memory holds the G = 2 kernel at 24 warps or fewer: 4 rows in flight per team win
 		// (10 M x 96, L = 48 / 128: 1.46 -> 1.37 / 3.53 -> 3.34 ms per 12.5 k queries; 1 M x 96, L = 64: 1.21 -> 1.13;
@@ -297,6 +304,8 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	}
 	p.filter_mode = fp.mode;
 	p.filter_bytes = fp.bytes;
+	p.filter_entries = fp.entries;
+	p.filter_magic = fp.entries ? (uint32_t)(((1ull << 40) + fp.entries - 1) / fp.entries) : 0u;
 	p.filter_mask = (1u << fp.lg) - 1;
 	p.filter_shift = 32 - fp.lg;
 	p.filter_bmask = (1u << (fp.lg - 3)) - 1;

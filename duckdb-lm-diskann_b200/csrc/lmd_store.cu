@@ -1114,6 +1114,8 @@ lmd_status lmd_set_tuning(lmd_store *s, const char *key, int64_t value) {
 		s->tune.latency_mode = (int)value;
 	} else if (k == "prefetch_planes") {
 		s->tune.prefetch_planes = (int)value;
+	} else if (k == "filter_entries") {
+		s->tune.filter_entries = (int)value;
 	} else if (k == "filter_mode") {
 		s->tune.filter_mode = (int)value;
 	} else if (k == "warps_per_cta") {

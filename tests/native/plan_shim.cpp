@@ -34,4 +34,14 @@ void plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32_t L, uint64_
 	out[1] = f.lg;
 	out[2] = f.bytes;
 }
+// out[0..2] = mode, entries, bytes of the modulo-mapped filter (entries 0 = the rule does not apply)
+void plan_filter_modulo(uint64_t nodes, uint64_t fixed_bytes, uint32_t warps, uint32_t *out) {
+	const lmd::FilterPlan f = lmd::plan_filter_modulo(nodes, (size_t)fixed_bytes, warps);
+	out[0] = f.mode;
+	out[1] = f.entries;
+	out[2] = f.bytes;
+}
+int modulo_filter_fits(uint64_t nodes, uint32_t entries) {
+	return lmd::modulo_filter_fits(nodes, entries) ? 1 : 0;
+}
 }

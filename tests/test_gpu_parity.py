@@ -209,6 +209,10 @@ def test_filter_size_does_not_change_results(lmd, make_index, metric, route):
             for lg in (6, 8, 11, 13):
                 s.set_tuning("filter_log2", lg)
                 outs.append(s.search(ix["queries"], 10, 128, route=route))
+        s.set_tuning("filter_mode", 3)  # direct-mapped by row id modulo the table size, any size
+        for entries in (512, 1000, 3504):
+            s.set_tuning("filter_entries", entries)
+            outs.append(s.search(ix["queries"], 10, 128, route=route))
     for o in outs[1:]:
         assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1])
     assert outs[0][3].filter_evictions > 0 and outs[4][3].filter_evictions > 0  # the 64-entry filters really did forget

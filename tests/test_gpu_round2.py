@@ -463,7 +463,8 @@ def test_duplicate_neighbour_ids_in_a_row(lmd, oracle, fixtures_mod, metric, rou
             s.set_tuning("prefilter", 2)
             oracle.set_codec(*s.get_codec())
         o = oracle.search(blocks, lay["block_bytes"], dims, r, q, k, L, metric=METRIC[metric], entry_row_id=0, route=o_route)
-        for mode in (0, 1, 2):
+        s.set_tuning("filter_entries", 1000)  # mode 3: modulo-mapped table, any size
+        for mode in (0, 1, 2, 3):
             s.set_tuning("filter_mode", mode)
             ids, dist, cnt, st, qs = s.search(q, k, L, qstats=True, **kw)
             for row in ids:

@@ -127,3 +127,23 @@ def test_direct_mapped_filter_for_the_sidecar_routes(plan):
     assert tuple(out) == (2, 12, 8192)
     plan.plan_filter(100_000_000, 32, 0, 56, _fixed(2) + 128, 0, 32, 2, 0, out)  # 100 M nodes need 2^(lg + 15) > nodes
     assert tuple(out) == (2, 12, 8192)
+
+
+def test_modulo_filter_takes_what_28_warps_leave(plan):
+    """The pre-filtered exact kernel: 7 CTAs of 4 warps per SM, the filter sized to the byte."""
+    plan.plan_filter_modulo.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint32)]
+    plan.plan_filter_modulo.restype = None
+    plan.modulo_filter_fits.argtypes = [ctypes.c_uint64, ctypes.c_uint32]
+    out = (ctypes.c_uint32 * 3)()
+    fixed = 64 * 8 + 384 + 128  # list of 64 keys, the warp's fixed block, the int8 query of a 128-d row
+    plan.plan_filter_modulo(1_000_000, fixed, 28, out)
+    assert list(out) == [3, 3504, 7008]
+    assert 7 * (4 * (fixed + out[2]) + 1024) <= 227 * 1024 < 7 * (4 * (fixed + out[2] + 16) + 1024)
+    plan.plan_filter_modulo(1_000_000, 128 * 8 + 384 + 128, 28, out)   # a 128-entry list leaves 3 248 entries
+    assert list(out) == [3, 3248, 6496]
+    plan.plan_filter_modulo(1_000_000, 512 * 8 + 384 + 128, 28, out)   # long lists: the rule steps aside
+    assert out[1] == 0
+    plan.plan_filter_modulo(400_000_000, fixed, 28, out)               # beyond the exact range of (slot, 16-bit tag)
+    assert out[1] == 0
+    assert plan.modulo_filter_fits(229_000_000, 3504) and not plan.modulo_filter_fits(230_000_000, 3504)
+    assert not plan.modulo_filter_fits(1000, 64) and not plan.modulo_filter_fits(1000, 1001)
