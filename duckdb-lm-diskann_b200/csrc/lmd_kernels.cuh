@@ -56,6 +56,7 @@ struct KParams {
 	const uint32_t *__restrict__ allowed;
 	uint32_t res_off; // byte offset of the results list RH inside the warp's shared memory
 	uint32_t latency; // host side only: dispatch to the latency variants
+	uint32_t cta_warps; // host side only: warps per CTA the plan asks for (0 = the packing that fits most warps)
 	// LMD_SEARCH_STRICT_FP: distances accumulated exactly as core/distance.hpp:56-99 does - one lane per row, element by
 	// element, separate multiply and add (no FMA) - so that every comparison of the traversal sees the reference's own
 	// bits. Served by the generic-shape kernels only (the query sits in shared memory); a parity tool, never timed.
@@ -1233,7 +1234,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 	// a batch too small to give every SM a CTA of 4 warps runs one warp per CTA: the warps then spread over the SMs
 	// instead of sharing a few SMs' load / shared-memory pipes (small index-join chunks, single queries)
 	const bool spread = s->tune.warps_per_cta == 0 && nq <= (uint32_t)s->sm_count * 4;
-	const uint64_t cache_key = (uint64_t)(uintptr_t)kernel * 0x9E3779B97F4A7C15ull + p.warp_smem_bytes * 2ull + (spread ? 1 : 0);
+	const uint64_t cache_key = (uint64_t)(uintptr_t)kernel * 0x9E3779B97F4A7C15ull + p.warp_smem_bytes * 2ull + (spread ? 1 : 0) + ((uint64_t)p.cta_warps << 40);
 	int best_w = 0, best_ctas = 0;
 	std::lock_guard<std::mutex> cache_guard(s->cache_mu);
 	auto hit = s->launch_cache.find(cache_key);
@@ -1244,7 +1245,7 @@ static lmd_status launch_persistent(K kernel, KParams &p, const lmd_store *s, ui
 		// opt in to the full 227 KB once: the same kernel is launched with different list / filter sizes
 		LMD_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
 		for (int w = 4; w >= 1; w >>= 1) {
-			const int forced = spread ? 1 : s->tune.warps_per_cta;
+			const int forced = spread ? 1 : (s->tune.warps_per_cta ? s->tune.warps_per_cta : (int)p.cta_warps);
 			if ((forced == 1 || forced == 2 || forced == 4) && w != forced) {
 				continue;
 			}

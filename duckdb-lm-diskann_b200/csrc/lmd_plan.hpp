@@ -145,24 +145,35 @@ inline int plan_filter_mode(int tune_mode, bool reads_sidecar, bool filtered) {
 	return reads_sidecar && !filtered ? 2 : 1;
 }
 
-// The pre-filtered exact kernel (72 registers: 7 CTAs of 4 warps by the register file) held 6 CTAs per SM because the
-// 8 KB power-of-two filter is what shared memory cut off; the modulo-mapped filter takes exactly what 28 warps leave
-// (3 504 entries = 7 008 bytes at L = 56, D = 128). One batch at a time it changes nothing (0.99 ms); with two batches in
-// flight - the way bench.py and the adapter's combining run it - 0.895 -> 0.82 ms per 10 k queries (profiles/r2_31_*).
-// Returns entries = 0 when the rule does not apply (long lists: fewer than 2 048 entries left; stores beyond the exact
-// range of the 16-bit tag) and the caller keeps plan_filter().
-inline FilterPlan plan_filter_modulo(uint64_t nodes, size_t fixed_bytes, uint32_t warps) {
+// The 128-d exact kernels (72 registers: 7 CTAs of 4 warps by the register file) held 6 CTAs per SM because the 8 KB
+// power-of-two filter is what shared memory cut off; the modulo-mapped filter takes what `warps` resident warps leave
+// of `smem_kb`, and no more than 3 072 entries (6 KB). smem_kb = 227 is all an SM can give. The plain kernels pass 196:
+// the shared-memory carve-out comes in steps (... 164, 196, 228 KB), whatever it leaves of the SM's 256 KB is L1, and
+// they measurably want the 60 KB a 196 KB carve-out leaves rather than 28 (3 000 entries beat 3 072 and 3 568 at every
+// list size). 1 M x 128, 10 k queries, ms per batch alone / with two batches in flight
+// (profiles/r2_31_32_modulo_filter.json, r2_34_35_modulo_plain.json):
+//   pre-filtered exact L = 56   0.99 / 0.893 -> 1.00 / 0.818      96-d L = 64   1.05 / 0.965 -> 1.04 / 0.851
+//   plain exact  L = 32  0.786 / 0.626 -> 0.746 / 0.588    L = 56  1.235 / 1.143 -> 1.185 / 1.074
+//                L = 64  1.343 / 1.275 -> 1.300 / 1.158    L = 100 (128-entry list) no gain: not applied
+// `max_load` > 0 (plain kernels: a forgotten node costs a 512-byte row) keeps the rule to searches whose expected
+// discoveries (0.8 R * 1.05 L) stay below that fraction of the table. Returns entries = 0 when the rule does not apply
+// (long lists; stores beyond the exact range of the 16-bit tag) and the caller keeps plan_filter().
+inline FilterPlan plan_filter_modulo(uint64_t nodes, size_t fixed_bytes, uint32_t warps, uint32_t smem_kb = 227,
+                                     uint32_t r = 0, uint32_t L = 0, double max_load = 0.0) {
 	FilterPlan f;
 	f.mode = 0;
 	f.lg = 0;
 	f.bytes = 0;
-	const size_t budget = ((size_t)227 * 1024 - (size_t)warps / 4 * 1024) / warps / 16 * 16;
+	const size_t budget = ((size_t)smem_kb * 1024 - (size_t)warps / 4 * 1024) / warps / 16 * 16;
 	if (budget <= fixed_bytes + 4096) {
 		return f;
 	}
 	uint32_t e = (uint32_t)((budget - fixed_bytes) / 2 / 8 * 8);
-	e = e > 8192 ? 8192 : e;
+	e = e > 3072 ? 3072 : e;
 	if (!modulo_filter_fits(nodes, e)) {
+		return f;
+	}
+	if (max_load > 0.0 && 0.8 * (double)r * 1.05 * (double)L > max_load * (double)e) {
 		return f;
 	}
 	f.mode = 3;

@@ -288,11 +288,20 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	FilterPlan fp = plan_filter(s->n, s->cfg.r, s->words, a.L, fixed, s->tune.plane_filter_cap != 0 && !exact, min_warps,
 	                            plan_filter_mode(s->tune.filter_mode, kroute != LMD_ROUTE_EXACT, a.d_allowed != nullptr),
 	                            (int)s->tune.filter_log2, s->tune.filter_entries);
-	if (kroute == LMD_KROUTE_EXACT_PF && specialised && s->tune.filter_mode < 0 && s->tune.filter_log2 == 0) {
-		// a 7th CTA per SM for the pre-filtered kernel: the filter takes exactly what 28 warps leave (lmd_plan.hpp)
-		const FilterPlan fm = plan_filter_modulo(s->n, fixed, 28);
+	if (specialised && !a.d_allowed && p.latency == 0 && s->tune.filter_mode < 0 && s->tune.filter_log2 == 0) {
+		// a 7th CTA per SM for the 72-register exact kernels: the filter takes what 28 warps leave (lmd_plan.hpp)
+		FilterPlan fm;
+		fm.entries = 0;
+		if (kroute == LMD_KROUTE_EXACT_PF) {
+			fm = plan_filter_modulo(s->n, fixed, 28);
+		} else if (kroute == LMD_ROUTE_EXACT && p.row_floats == 128 && lpl <= 2) {
+			fm = plan_filter_modulo(s->n, fixed, 28, 196, s->cfg.r, a.L, 0.6);
+		}
 		if (fm.entries && fm.bytes < fp.bytes) {
 			fp = fm;
+			// two batches in flight: CTAs of one warp hand their SM share to the next kernel as soon as that warp runs out
+			// of queries (pre-filtered L = 56: 0.814 -> 0.794 ms; the plain kernels: no difference; profiles/r2_35_cta_*)
+			p.cta_warps = kroute == LMD_KROUTE_EXACT_PF ? 1u : 0u;
 		}
 	}
 	if (kroute == LMD_ROUTE_EXACT && !p.strict && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {

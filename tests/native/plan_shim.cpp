@@ -35,8 +35,9 @@ void plan_filter(uint64_t nodes, uint32_t r, uint32_t words, uint32_t L, uint64_
 	out[2] = f.bytes;
 }
 // out[0..2] = mode, entries, bytes of the modulo-mapped filter (entries 0 = the rule does not apply)
-void plan_filter_modulo(uint64_t nodes, uint64_t fixed_bytes, uint32_t warps, uint32_t *out) {
-	const lmd::FilterPlan f = lmd::plan_filter_modulo(nodes, (size_t)fixed_bytes, warps);
+void plan_filter_modulo(uint64_t nodes, uint64_t fixed_bytes, uint32_t warps, uint32_t smem_kb, uint32_t r, uint32_t L,
+                        double max_load, uint32_t *out) {
+	const lmd::FilterPlan f = lmd::plan_filter_modulo(nodes, (size_t)fixed_bytes, warps, smem_kb, r, L, max_load);
 	out[0] = f.mode;
 	out[1] = f.entries;
 	out[2] = f.bytes;

@@ -130,20 +130,28 @@ def test_direct_mapped_filter_for_the_sidecar_routes(plan):
 
 
 def test_modulo_filter_takes_what_28_warps_leave(plan):
-    """The pre-filtered exact kernel: 7 CTAs of 4 warps per SM, the filter sized to the byte."""
-    plan.plan_filter_modulo.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint32)]
+    """The 72-register exact kernels: 7 CTAs of 4 warps per SM, the filter sized for it, 6 KB at most."""
+    plan.plan_filter_modulo.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32,
+                                        ctypes.c_uint32, ctypes.c_double, ctypes.POINTER(ctypes.c_uint32)]
     plan.plan_filter_modulo.restype = None
     plan.modulo_filter_fits.argtypes = [ctypes.c_uint64, ctypes.c_uint32]
     out = (ctypes.c_uint32 * 3)()
     fixed = 64 * 8 + 384 + 128  # list of 64 keys, the warp's fixed block, the int8 query of a 128-d row
-    plan.plan_filter_modulo(1_000_000, fixed, 28, out)
-    assert list(out) == [3, 3504, 7008]
-    assert 7 * (4 * (fixed + out[2]) + 1024) <= 227 * 1024 < 7 * (4 * (fixed + out[2] + 16) + 1024)
-    plan.plan_filter_modulo(1_000_000, 128 * 8 + 384 + 128, 28, out)   # a 128-entry list leaves 3 248 entries
-    assert list(out) == [3, 3248, 6496]
-    plan.plan_filter_modulo(1_000_000, 512 * 8 + 384 + 128, 28, out)   # long lists: the rule steps aside
+    plan.plan_filter_modulo(1_000_000, fixed, 28, 227, 0, 0, 0.0, out)
+    assert list(out) == [3, 3072, 6144]
+    assert 7 * (4 * (fixed + out[2]) + 1024) <= 227 * 1024
+    plan.plan_filter_modulo(1_000_000, 7 * 1024 - 5000, 28, 227, 0, 0, 0.0, out)   # less room: exactly what 28 warps leave
+    assert list(out) == [3, 2928, 5856] and 7 * (4 * (7 * 1024 - 5000 + 5856) + 1024) <= 227 * 1024
+    assert 7 * (4 * (7 * 1024 - 5000 + 5856 + 32) + 1024) > 227 * 1024
+    plan.plan_filter_modulo(1_000_000, 512 * 8 + 384 + 128, 28, 227, 0, 0, 0.0, out)   # long lists: the rule steps aside
     assert out[1] == 0
-    plan.plan_filter_modulo(400_000_000, fixed, 28, out)               # beyond the exact range of (slot, 16-bit tag)
+    plan.plan_filter_modulo(400_000_000, fixed, 28, 227, 0, 0, 0.0, out)               # beyond the exact range of (slot, 16-bit tag)
+    assert out[1] == 0
+    # plain kernels: only while the expected discoveries stay under 0.6 of the table
+    # ... and inside the 196 KB shared-memory carve-out, which leaves 60 KB of the SM to L1
+    plan.plan_filter_modulo(1_000_000, 64 * 8 + 384, 28, 196, 32, 64, 0.6, out)
+    assert list(out) == [3, 3008, 6016] and 7 * (4 * (64 * 8 + 384 + 6016) + 1024) <= 196 * 1024
+    plan.plan_filter_modulo(1_000_000, 64 * 8 + 384, 28, 196, 64, 64, 0.6, out)
     assert out[1] == 0
     assert plan.modulo_filter_fits(229_000_000, 3504) and not plan.modulo_filter_fits(230_000_000, 3504)
     assert not plan.modulo_filter_fits(1000, 64) and not plan.modulo_filter_fits(1000, 1001)
