@@ -351,7 +351,7 @@ def extra_codec(J, store, batch_local, truth_local, k, L):
     return out
 
 
-def extra_built(J, tag, n, dims, metric, kind, nq_total, split, k, runs, r=32, l_insert=64, release=False):
+def extra_built(J, tag, n, dims, metric, kind, nq_total, split, k, runs, r=32, l_insert=64, release=False, codec=False):
     """A GPU-generated, GPU-built index replicated on every rank. split=True: ONE batch of nq_total queries split over the
     ranks (strong); False: nq_total / N queries per rank, every rank its own. runs = [(label, route, L, flags)]."""
     torch, lmd, wl = J.torch, J.lmd, J.wl
@@ -376,6 +376,9 @@ def extra_built(J, tag, n, dims, metric, kind, nq_total, split, k, runs, r=32, l
             full_gb = store.device_bytes / 1e9
             store.finalize()
             store.release_blocks()
+        released_gb = store.device_bytes / 1e9
+        if codec:  # int8 code sidecar: exact routing runs behind the lower-bound pre-filter (same results, fewer rows)
+            store.enable_codec()
     except Exception as e:  # noqa: BLE001
         err = repr(e)
     torch.cuda.empty_cache()
@@ -392,7 +395,10 @@ def extra_built(J, tag, n, dims, metric, kind, nq_total, split, k, runs, r=32, l
            "mode": ("one %d-query batch split %d ways (strong)" if split else "%d queries per step over %d GPUs, replicated") % (
                nq_total, J.world)}
     if release:
-        rec["store_GB_per_gpu_blocks_released"] = round(store.device_bytes / 1e9, 2)
+        rec["store_GB_per_gpu_blocks_released"] = round(released_gb, 2)
+    if codec:
+        rec["store_GB_per_gpu_with_codes"] = round(store.device_bytes / 1e9, 2)
+        rec["int8_code_sidecar"] = "on (runs without LMD_SEARCH_NO_PREFILTER use the pre-filtered exact kernel)"
     for label, route, L, flags in runs:
         # recall on the sample: time the whole slice, count hits on its first ns rows
         row = J.query_sharded(store, q, None, k, L, route, nq_total if split else (nq_total // J.world) * J.world, flags)
@@ -408,7 +414,7 @@ def extra_built(J, tag, n, dims, metric, kind, nq_total, split, k, runs, r=32, l
     return rec
 
 
-def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64):
+def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64, codec=False):
     """configs[4]: dataset-sharded - rank s holds rows [lo_s, hi_s) with a shard-local graph; every rank searches the FULL
     batch, ONE NCCL all-gather of the [Q][k] (distance, row id) lists, k-way merge kernel."""
     torch, lmd, wl, sh = J.torch, J.lmd, J.wl, J.sh
@@ -428,6 +434,8 @@ def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64):
         full_gb = store.device_bytes / 1e9
         store.finalize()
         store.release_blocks()
+        if codec:
+            store.enable_codec()
     except Exception as e:  # noqa: BLE001
         err = repr(e)
     try:
@@ -448,7 +456,8 @@ def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64):
                        "l_insert=%d), global row ids" % (n, dims, J.world, hi - lo, l_insert),
            "gen_build_s": round(t_build, 2), "store_GB_per_gpu": round(full_gb, 2),
            "store_GB_per_gpu_blocks_released": round(store.device_bytes / 1e9, 2),
-           "nccl_ranks": J.dist.get_world_size(), "allgather_bytes_per_rank": nq * k * 12, "runs": []}
+           "nccl_ranks": J.dist.get_world_size(), "allgather_bytes_per_rank": nq * k * 12,
+           "int8_code_sidecar": "on (pre-filtered exact kernel)" if codec else "off", "runs": []}
     store.set_stream(J.stream.cuda_stream)
     searcher = sh.DatasetShardedSearcher(store, device=torch.device(J.dev))
     ids = torch.empty((nq, k), dtype=torch.int64, device=J.dev)
@@ -793,10 +802,12 @@ def main():
         other["c2_iid"] = guarded(J, "c2_iid", extra_built, "iid", 1_000_000, 128, "L2", "iid", 10_000 * world, False, a.k,
                                   [("exact_L64", lmd.ROUTE_EXACT, 64, 0), ("exact_L256", lmd.ROUTE_EXACT, 256, 0)])
         other["c4"] = guarded(J, "c4", extra_built, "c4", 10_000_000, 96, "L2", "clustered", 100_000, False, a.k,
-                              [("exact_L96", lmd.ROUTE_EXACT, 96, 0)], release=True)
+                              [("exact_L96", lmd.ROUTE_EXACT, 96, 0),
+                               ("exact_L96_no_prefilter", lmd.ROUTE_EXACT, 96, lmd.SEARCH_NO_PREFILTER)], release=True,
+                              codec=use_codec)
         if dist_on:
             # 12.5 M rows per GPU: the 100 M x 96 configuration at N = 8, the same shard size below that
-            other["c5"] = guarded(J, "c5", extra_c5, 12_500_000, 96, a.k, [48, 64])
+            other["c5"] = guarded(J, "c5", extra_c5, 12_500_000, 96, a.k, [48, 64], codec=use_codec)
         else:
             other["c5"] = {"skipped": "dataset sharding needs N >= 2 (its all-gather is the point)"}
     if rank != 0:
