@@ -434,6 +434,7 @@ def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64, codec=False):
         full_gb = store.device_bytes / 1e9
         store.finalize()
         store.release_blocks()
+        released_gb = store.device_bytes / 1e9
         if codec:
             store.enable_codec()
     except Exception as e:  # noqa: BLE001
@@ -455,7 +456,8 @@ def extra_c5(J, rows_per_gpu, dims, k, Ls, r=32, l_insert=64, codec=False):
     rec = {"workload": "synthetic %dx%d float32 L2 (clustered), %d shards of %d rows, shard-local graphs (lmd_build_graph, "
                        "l_insert=%d), global row ids" % (n, dims, J.world, hi - lo, l_insert),
            "gen_build_s": round(t_build, 2), "store_GB_per_gpu": round(full_gb, 2),
-           "store_GB_per_gpu_blocks_released": round(store.device_bytes / 1e9, 2),
+           "store_GB_per_gpu_blocks_released": round(released_gb, 2),
+           "store_GB_per_gpu_searched": round(store.device_bytes / 1e9, 2),
            "nccl_ranks": J.dist.get_world_size(), "allgather_bytes_per_rank": nq * k * 12,
            "int8_code_sidecar": "on (pre-filtered exact kernel)" if codec else "off", "runs": []}
     store.set_stream(J.stream.cuda_stream)
