@@ -297,11 +297,16 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 		} else if (kroute == LMD_ROUTE_EXACT && p.row_floats == 128 && lpl <= 2) {
 			fm = plan_filter_modulo(s->n, fixed, 28, 196, s->cfg.r, a.L, 0.6);
 		}
-		if (fm.entries && fm.bytes < fp.bytes) {
+		// (pre-filtered kernel: also where the power-of-two rule had shrunk to 4 KB for a 128-entry list - 7 CTAs hold the
+		// 6 KB table too, and it forgets less: 1 M x 128 L = 100 / 128 in flight 1.537 -> 1.471 / 1.894 -> 1.814 ms;
+		// 10 M x 96 L = 96, 100 k queries: kernel 12.5 -> 12.3 ms; profiles/r2_41_pf_long_lists.json)
+		if (fm.entries && (fm.bytes < fp.bytes || kroute == LMD_KROUTE_EXACT_PF)) {
 			fp = fm;
 			// two batches in flight: CTAs of one warp hand their SM share to the next kernel as soon as that warp runs out
 			// of queries (pre-filtered L = 56: 0.814 -> 0.794 ms; the plain kernels: no difference; profiles/r2_35_cta_*)
-			p.cta_warps = kroute == LMD_KROUTE_EXACT_PF ? 1u : 0u;
+			// ... which only matters while a batch is a few rounds of the resident warps: larger batches keep the CTAs of 4
+			// (100 k queries over 10 M x 96 rows: 13.2 ms either way, profiles/r2_42_bench_n1.json, r2_43_bench_n1.json)
+			p.cta_warps = kroute == LMD_KROUTE_EXACT_PF && a.nq <= 8u * 28u * (uint32_t)s->sm_count ? 1u : 0u;
 		}
 	}
 	if (kroute == LMD_ROUTE_EXACT && !p.strict && plan_96d_prefers_g4(p.row_floats, exact, a.d_allowed != nullptr, (int)p.latency, lat, lpl, fp.bytes)) {
