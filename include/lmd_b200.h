@@ -328,7 +328,8 @@ lmd_status lmd_search_batch_static(lmd_store *s, const float *queries, uint64_t 
 /* --- misc --- */
 const char *lmd_last_error(void);   /* thread-local message of the last non-OK status */
 uint32_t lmd_abi_version(void);
-/* Tuning knobs for experiments (not needed for correct use): "filter_log2", "filter_mode", "warps_per_cta",
+/* Tuning knobs for experiments (not needed for correct use): "filter_log2", "filter_mode" (0 u32 open addressing, 1 two-
+ * choice 16-bit buckets, 2 direct-mapped 16-bit, 3 direct-mapped by slot modulo "filter_entries"), "warps_per_cta",
  * "ctas_per_sm", "tie_slots", "merge_min", "prefetch_planes", "latency_mode" (-1 auto by batch size / 0 the throughput
  * kernels / 1 the small-batch kernels that gather all neighbours of an expansion in one pass / 2 the mid-size-batch
  * kernels with 4 rows in flight per team; 128-d and 96-d rows, exact routing). */
