@@ -800,7 +800,9 @@ def main():
     torch.cuda.empty_cache()
     if a.extras != "none":
         other["c3_strong"] = guarded(J, "c3_strong", extra_built, "c3", 1_000_000, 768, "COSINE", "clustered", 10_000, True,
-                                     a.k, [("exact_L32", lmd.ROUTE_EXACT, 32, 0), ("ternary_L80", lmd.ROUTE_TERNARY, 80, 0)])
+                                     a.k, [("exact_L32", lmd.ROUTE_EXACT, 32, 0),
+                                           ("exact_L32_no_prefilter", lmd.ROUTE_EXACT, 32, lmd.SEARCH_NO_PREFILTER),
+                                           ("ternary_L80", lmd.ROUTE_TERNARY, 80, 0)], codec=use_codec)
         other["c2_iid"] = guarded(J, "c2_iid", extra_built, "iid", 1_000_000, 128, "L2", "iid", 10_000 * world, False, a.k,
                                   [("exact_L64", lmd.ROUTE_EXACT, 64, 0), ("exact_L256", lmd.ROUTE_EXACT, 256, 0)])
         other["c4"] = guarded(J, "c4", extra_built, "c4", 10_000_000, 96, "L2", "clustered", 100_000, False, a.k,

@@ -751,8 +751,10 @@ __device__ __forceinline__ float ternary_distance(const KParams &p, const uint8_
 // x ~ off[d] + scale * c[d]. The query is brought onto the same grid once per query: qi[d] = clamp(rint((q[d] - off[d]) /
 // scale)), kept as int8 in shared memory; a_sq = sum qi^2 (exact integer); e_q = || (q - off) - scale * qi || (fp32).
 // Then for a neighbour with codes c:  || q^ - x^ ||^2 = scale^2 * (a_sq - 2 * dot(qi, c) + csq)  - all integer, dp4a.
+// `qmul`: COSINE stores keep UNIT rows on the grid, and the query goes there as q / || q || (qmul = 1 / || q ||; 0 for a
+// zero query, whose e_q becomes +inf so that no bound ever excludes a row).
 __device__ __forceinline__ void encode_query_int8(const KParams &p, uint32_t qi, int lane, int8_t *s_qi8, int &a_sq,
-                                                  float &e_q) {
+                                                  float &e_q, float qmul = 1.0f) {
 	const float *src = p.queries + (uint64_t)qi * p.q_stride;
 	const float inv = 1.0f / p.code_scale;
 	int a = 0;
@@ -760,7 +762,7 @@ __device__ __forceinline__ void encode_query_int8(const KParams &p, uint32_t qi,
 	for (uint32_t f = lane; f < p.row_floats; f += 32) { // row_floats is a multiple of 32 >= dims: the tail encodes 0
 		int c = 0;
 		if (f < p.dims) {
-			const float v = __ldg(src + f) - __ldg(p.code_off + f);
+			const float v = __ldg(src + f) * qmul - __ldg(p.code_off + f);
 			c = __float2int_rn(v * inv);
 			c = c < -127 ? -127 : (c > 127 ? 127 : c);
 			const float r = v - p.code_scale * (float)c;
@@ -775,7 +777,7 @@ __device__ __forceinline__ void encode_query_int8(const KParams &p, uint32_t qi,
 		e += __shfl_xor_sync(FULL, e, o);
 	}
 	a_sq = a;
-	e_q = sqrtf(e) * 1.0001f;
+	e_q = qmul > 0.0f ? sqrtf(e) * 1.0001f : __int_as_float(0x7f800000);
 	__syncwarp();
 }
 
@@ -870,7 +872,12 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 			encode_query_planes(p, qi, lane, s_qp, s_qn);
 		}
 		if (CODES) {
-			encode_query_int8(p, qi, lane, s_qi8, q_asq, q_err);
+			float qmul = 1.0f;
+			if (METRIC == LMD_METRIC_COSINE) {
+				qmul = Q.na > 0.0f ? 1.0f / sqrtf(Q.na) : 0.0f;
+				qmul = isfinite(qmul) ? qmul : 0.0f;
+			}
+			encode_query_int8(p, qi, lane, s_qi8, q_asq, q_err, qmul);
 		}
 		__syncwarp();
 
@@ -966,7 +973,25 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 				bool have = isnew;
 				uint32_t gmask = mask; // neighbours whose exact row is gathered
 				int gm = m;
-				if (CODES) {
+				if (CODES && ROUTE == LMD_KROUTE_EXACT_PF && METRIC == LMD_METRIC_COSINE) {
+					// COSINE stores: the zero-offset grid holds the UNIT rows (x^ = scale * c ~ x / || x ||) and the unit query.
+					// With u = q / || q ||, w = x / || x ||:  u.w = u^.w^ + (u - u^).w^ + u.(w - w^)
+					//   <= scale^2 qi.c + || u - u^ || (1 + || w - w^ ||) + || w - w^ ||,
+					// so 1 - that is a lower bound of the distance of core/distance.hpp:85-98 (whose clamp to [-1, 1] can only
+					// raise the distance above the bound). fp32 rounding of either side stays below 5e-5 in these units
+					// (D * 2^-24); the margin is 2e-4. Zero rows / a zero query carry err = +inf: the bound is -inf, they are
+					// fetched and get the reference's 1.0.
+					const float ub = p.code_scale * p.code_scale * (float)c_dot + q_err * (1.0f + c_err) + c_err;
+					const float lb = 1.0f - ub;
+					const float worst0 = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
+					const bool skip = n >= L && lb > worst0 + 2e-4f;
+					gmask = __ballot_sync(FULL, isnew && !skip);
+					gm = __popc(gmask);
+					if (gm == 0) {
+						continue;
+					}
+					isnew = isnew && !skip;
+				} else if (CODES) {
 					// || q^ - x^ || on the code grid: integers all the way to the square root
 					const int i2 = q_asq - 2 * c_dot + (int)c_sq;
 					d = p.code_scale * sqrtf((float)(i2 > 0 ? i2 : 0)) + 0.0f;

@@ -73,17 +73,54 @@ __global__ void code_stats_kernel(const float *__restrict__ vecs, uint32_t row_f
 	}
 }
 
+// COSINE stores put the UNIT rows x / || x || on the grid (the metric does not see the length): per-dimension sum of
+// squares of the unit rows. One warp per row, per-block partial sums in shared memory.
+__global__ void code_stats_unit_kernel(const float *__restrict__ vecs, uint32_t row_floats, uint32_t dims, uint64_t n,
+                                       uint64_t rows_per_block, double *__restrict__ sumsq) {
+	extern __shared__ float s_acc[];
+	for (uint32_t d = threadIdx.x; d < row_floats; d += blockDim.x) {
+		s_acc[d] = 0.0f;
+	}
+	__syncthreads();
+	const uint64_t r0 = blockIdx.x * rows_per_block;
+	const uint64_t r1 = r0 + rows_per_block < n ? r0 + rows_per_block : n;
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+	for (uint64_t row = r0 + warp; row < r1; row += warps) {
+		const float *v = vecs + row * row_floats;
+		float xx = 0.0f;
+		for (uint32_t d = lane; d < dims; d += 32) {
+			xx = fmaf(v[d], v[d], xx);
+		}
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) {
+			xx += __shfl_xor_sync(0xFFFFFFFFu, xx, o);
+		}
+		if (xx > 0.0f) {
+			const float inv = 1.0f / xx;
+			for (uint32_t d = lane; d < dims; d += 32) {
+				atomicAdd(&s_acc[d], v[d] * v[d] * inv);
+			}
+		}
+	}
+	__syncthreads();
+	for (uint32_t d = threadIdx.x; d < dims; d += blockDim.x) {
+		atomicAdd(&sumsq[d], (double)s_acc[d]);
+	}
+}
+
 // off[d] = mean of dimension d; off[row_floats] = scale = sigmas * max_d sigma_d / 127 (one grid for all dimensions, so
 // that distances on the grid are plain integer arithmetic). Values beyond +-127 steps are clamped; every neighbour's
 // own reconstruction error is stored next to its codes, so clamping costs bound tightness, never correctness.
+// `centred` = 0 (COSINE stores): the grid has no offsets - x ~ scale * c - because a dot product, unlike a difference,
+// does not cancel them; sigma_d is then the root of the second moment about zero.
 __global__ void code_params_kernel(const double *__restrict__ sum, const double *__restrict__ sumsq, uint64_t n,
-                                   uint32_t dims, uint32_t row_floats, float sigmas, float *__restrict__ off) {
+                                   uint32_t dims, uint32_t row_floats, float sigmas, int centred, float *__restrict__ off) {
 	__shared__ float s_max[256];
 	float mx = 0.0f;
 	for (uint32_t d = threadIdx.x; d < row_floats; d += blockDim.x) {
 		float o = 0.0f;
 		if (d < dims) {
-			const double m = sum[d] / (double)n;
+			const double m = centred ? sum[d] / (double)n : 0.0;
 			double var = sumsq[d] / (double)n - m * m;
 			var = var > 0.0 ? var : 0.0;
 			o = (float)m;
@@ -107,9 +144,11 @@ __global__ void code_params_kernel(const double *__restrict__ sum, const double 
 
 // One warp per node: for each neighbour j its vector is brought onto the grid, c = clamp(rint((x - off) / scale)),
 // csq = sum c^2 (integer), err = || (x - off) - scale * c || (fp32, inflated by 1e-4 so that it is an upper bound).
+// `unit` = 1 (COSINE stores): the UNIT row x / || x || goes onto the (zero-offset) grid, err = || x / || x || - scale * c ||;
+// a zero row gets codes 0 and err = +inf, so that no bound ever excludes it (the reference gives it distance 1.0).
 __global__ void build_code_side_kernel(const float *__restrict__ vecs, uint32_t row_floats, uint32_t dims, uint32_t r,
                                        uint64_t n, const uint32_t *__restrict__ nbrs, const float *__restrict__ off,
-                                       uint8_t *__restrict__ side, uint32_t side_bytes, uint32_t data_off) {
+                                       uint8_t *__restrict__ side, uint32_t side_bytes, uint32_t data_off, int unit) {
 	const uint64_t node = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
 	const uint32_t lane = threadIdx.x & 31;
 	if (node >= n) {
@@ -121,7 +160,25 @@ __global__ void build_code_side_kernel(const float *__restrict__ vecs, uint32_t 
 	for (uint32_t j = 0; j < r; j++) {
 		const uint32_t slot = nbrs[node * r + j];
 		int csq = 0;
-		float e = 0.0f;
+		float e = 0.0f, xmul = 1.0f;
+		if (unit) {
+			float xx = 0.0f;
+			if (slot != LMD_INVALID_SLOT) {
+				for (uint32_t f = lane; f < dims; f += 32) {
+					const float v = vecs[(uint64_t)slot * row_floats + f];
+					xx = fmaf(v, v, xx);
+				}
+			}
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) {
+				xx += __shfl_xor_sync(0xFFFFFFFFu, xx, o);
+			}
+			xmul = xx > 0.0f ? 1.0f / sqrtf(xx) : 0.0f;
+			if (!(xx > 0.0f) || !isfinite(xmul)) {
+				xmul = 0.0f;
+				e = __int_as_float(0x7f800000); // + inf: never excluded
+			}
+		}
 		for (uint32_t f = lane * 4; f < row_floats; f += 128) { // row_floats is a multiple of 32 floats
 			int c[4] = {0, 0, 0, 0};
 			if (slot != LMD_INVALID_SLOT) {
@@ -130,7 +187,7 @@ __global__ void build_code_side_kernel(const float *__restrict__ vecs, uint32_t 
 #pragma unroll
 				for (int t = 0; t < 4; t++) {
 					if (f + t < dims) {
-						const float v = xv[t] - off[f + t];
+						const float v = xv[t] * xmul - off[f + t];
 						int q = __float2int_rn(v * inv);
 						q = q < -127 ? -127 : (q > 127 ? 127 : q);
 						const float rr = v - scale * (float)q;
@@ -209,11 +266,19 @@ lmd_status build_code_side(lmd_store *s) {
 	cudaMemsetAsync(d_stats, 0, 2 * (size_t)rf * sizeof(double), s->stream);
 	const uint64_t rows_per_block = std::max<uint64_t>(64, (s->n + 8 * 148 - 1) / (8 * 148));
 	const unsigned nb = (unsigned)((s->n + rows_per_block - 1) / rows_per_block);
-	code_stats_kernel<<<nb, 256, 0, s->stream>>>(s->d_vecs, rf, s->cfg.dims, s->n, rows_per_block, d_stats, d_stats + rf);
+	if (s->cfg.metric == LMD_METRIC_COSINE) {
+		code_stats_unit_kernel<<<nb, 256, rf * sizeof(float), s->stream>>>(s->d_vecs, rf, s->cfg.dims, s->n, rows_per_block,
+		                                                                   d_stats + rf);
+	} else {
+		code_stats_kernel<<<nb, 256, 0, s->stream>>>(s->d_vecs, rf, s->cfg.dims, s->n, rows_per_block, d_stats, d_stats + rf);
+	}
 	const float sigmas = s->tune.code_sigmas > 0 ? (float)s->tune.code_sigmas * 0.1f : 4.0f;
-	code_params_kernel<<<1, 256, 0, s->stream>>>(d_stats, d_stats + rf, s->n, s->cfg.dims, rf, sigmas, s->d_code_off);
+	const int cosine = s->cfg.metric == LMD_METRIC_COSINE ? 1 : 0;
+	code_params_kernel<<<1, 256, 0, s->stream>>>(d_stats, d_stats + rf, s->n, s->cfg.dims, rf, sigmas, cosine ? 0 : 1,
+	                                             s->d_code_off);
 	build_code_side_kernel<<<(unsigned)((s->n * 32 + 255) / 256), 256, 0, s->stream>>>(
-	    s->d_vecs, rf, s->cfg.dims, r, s->n, s->d_nbrs, s->d_code_off, s->d_codes, s->code_block_bytes, s->code_data_off);
+	    s->d_vecs, rf, s->cfg.dims, r, s->n, s->d_nbrs, s->d_code_off, s->d_codes, s->code_block_bytes, s->code_data_off,
+	    cosine);
 	cudaError_t e = cudaGetLastError();
 	if (e == cudaSuccess) {
 		e = cudaMemcpyAsync(&s->code_scale, s->d_code_off + rf, sizeof(float), cudaMemcpyDeviceToHost, s->stream);
@@ -287,9 +352,10 @@ lmd_status lmd_store_enable_codec(lmd_store *s, uint32_t codec) {
 		set_error("lmd_store_enable_codec: unknown codec %u", codec);
 		return LMD_ERR_INVALID_ARG;
 	}
-	if (codec == LMD_CODEC_INT8 && s->cfg.metric != LMD_METRIC_L2) {
-		// the grid distance || q^ - x^ || bounds / approximates an L2 distance; COSINE and IP have the ternary codec
-		set_error("the int8 edge codec is defined for the L2 metric only");
+	if (codec == LMD_CODEC_INT8 && s->cfg.metric == LMD_METRIC_IP) {
+		// L2: the grid distance || q^ - x^ || bounds and approximates the distance (pre-filter and LMD_ROUTE_INT8);
+		// COSINE: the grid dot product bounds it (pre-filter of the exact route only); IP has the ternary codec
+		set_error("the int8 edge codec is defined for the L2 and COSINE metrics only");
 		return LMD_ERR_UNSUPPORTED;
 	}
 	{
