@@ -150,6 +150,10 @@ void DeviceNodeStore::SetEntryPoint(common::row_t row_id) {
 	Check(lmd_store_set_entry(store_, row_id), "DeviceNodeStore::SetEntryPoint");
 }
 
+void DeviceNodeStore::SetEdgeCodec(bool on) {
+	Check(lmd_store_enable_codec(store_, on ? LMD_CODEC_INT8 : LMD_CODEC_NONE), "DeviceNodeStore::SetEdgeCodec");
+}
+
 void DeviceNodeStore::UploadVectors(const common::row_t *row_ids, const float *vectors, common::idx_t n) {
 	Check(lmd_store_upload_vectors(store_, row_ids, vectors, n), "DeviceNodeStore::UploadVectors");
 }

@@ -605,6 +605,15 @@ int lmdhost_concurrent_searches(void *p, const float *queries, uint64_t nq, uint
 	});
 }
 
+// 0 = ok, 1 = threw (message through lmdhost_last_error)
+int lmdhost_set_edge_codec(void *p, int on) {
+	return Guard([&]() {
+		if (auto *g = dynamic_cast<b200::GpuSearcher *>(static_cast<Host *>(p)->searcher.get())) {
+			g->Store().SetEdgeCodec(on != 0);
+		}
+	});
+}
+
 void lmdhost_set_combining(void *p, int on) {
 	if (auto *g = dynamic_cast<b200::GpuSearcher *>(static_cast<Host *>(p)->searcher.get())) {
 		g->SetCombining(on != 0);

@@ -45,6 +45,7 @@ def _lib():
     l.lmdhost_concurrent_searches.argtypes = [P, P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32,
                                               C.c_uint64, P, P, P]
     l.lmdhost_set_combining.argtypes = [P, C.c_int]
+    l.lmdhost_set_edge_codec.argtypes = [P, C.c_int]
     l.lmdhost_combining_stats.argtypes = [P, P, P]
     l.lmdgroup_create.restype = P
     l.lmdgroup_create.argtypes = [P, P, C.c_uint64, P, P, C.c_uint32, P, C.c_int, C.c_int, C.c_int, C.c_uint64,
@@ -248,6 +249,32 @@ def test_multi_scan_equals_single_scans(oracle, make_index):
         for qi in (0, 17, 95):
             err, one, _, _ = h.scan_all(ix["queries"][qi], k)
             assert np.array_equal(one, ids[qi, :len(one)])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric", ["L2", "COSINE", "IP"])
+def test_edge_codec_through_the_adapter(make_index, metric):
+    """DeviceNodeStore::SetEdgeCodec: the scans of an L2 / COSINE index return the same rows with the int8 code sidecar on
+    (the pre-filter only skips rows the list would turn away); an IP index refuses it."""
+    dims, r, k = 128, 32, 10
+    ix = make_index(3000, dims, r, metric=metric, kind="clustered", nq=96)
+    lib = _lib()
+    with Host(lib, ix["blocks_np"], ix["block_bytes"], dims, r, metric={"L2": 1, "COSINE": 2, "IP": 3}[metric],
+              l_search=100) as h:
+        err, ids0, cnt0, _ = h.multi_scan(ix["queries"], k)
+        assert err is None
+        rc = lib.lmdhost_set_edge_codec(h.h, 1)
+        if metric == "IP":
+            assert rc != 0 and b"L2 and COSINE" in lib.lmdhost_last_error()
+            return
+        assert rc == 0, lib.lmdhost_last_error()
+        err, ids1, cnt1, _ = h.multi_scan(ix["queries"], k)
+        assert err is None and np.array_equal(ids0, ids1) and np.array_equal(cnt0, cnt1)
+        err, one, _, _ = h.scan_all(ix["queries"][5], k)
+        assert np.array_equal(one, ids0[5, :len(one)])
+        assert lib.lmdhost_set_edge_codec(h.h, 0) == 0
+        err, ids2, _, _ = h.multi_scan(ix["queries"], k)
+        assert np.array_equal(ids0, ids2)
 
 
 @pytest.mark.gpu
