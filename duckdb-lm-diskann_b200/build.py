@@ -15,7 +15,7 @@ OUT = os.path.join(HERE, "liblmd_b200.so")
 SOURCES = ["lmd_store.cu", "lmd_sidecar.cu", "lmd_search_kernels.cu", "lmd_api.cu", "lmd_group.cu", "lmd_rerank_tc.cu", "lmd_build.cu", "lmd_static.cu"]
 # lmd_kernel_inst.cu is compiled once per kernel family: (object suffix, extra defines)
 INSTANCES = [("trav_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=0", "-DLMD_INST_METRIC=%d" % m, "-DLMD_INST_ROUTE=%d" % r])
-             for m, r in ((1, 0), (2, 0), (3, 0), (2, 1), (3, 1), (1, 2), (1, 3), (2, 3))] + \
+             for m, r in ((1, 0), (2, 0), (3, 0), (2, 1), (3, 1), (1, 2), (1, 3), (2, 3), (3, 3))] + \
             [("travf_m%d_r%d" % (m, r), ["-DLMD_INST_KIND=3", "-DLMD_INST_METRIC=%d" % m, "-DLMD_INST_ROUTE=%d" % r])
              for m, r in ((1, 0), (2, 0), (3, 0), (2, 1), (3, 1))] + \
             [("travl_m%d" % m, ["-DLMD_INST_KIND=4", "-DLMD_INST_METRIC=%d" % m]) for m in (1, 2, 3)] + \

@@ -172,6 +172,7 @@ struct lmd_store {
 	uint8_t *d_codes = nullptr;
 	float *d_code_off = nullptr;         // [row_floats + 1]: per-dimension offsets, then the scale
 	float code_scale = 1.0f;
+	float code_rho = 0.0f; // RMS row length (IP stores: the query is scaled to it before it goes onto the grid)
 	uint32_t code_block_bytes = 0, code_data_off = 0;
 	uint64_t codes_gen = 0;
 	bool blocks_released = false;        // lmd_store_release_blocks: d_blocks is gone (search-only store)

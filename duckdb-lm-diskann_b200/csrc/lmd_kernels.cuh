@@ -70,6 +70,7 @@ struct KParams {
 	// int8 edge codec: x ~ code_off[d] + code_scale * c[d], c in [-127, 127]
 	const float *__restrict__ code_off; // [row_floats]
 	float code_scale;
+	float code_rho; // IP pre-filter: RMS row length
 	uint32_t prefilter;     // exact routing: 1 = the int8 lower bound decides which neighbours' rows are fetched at all
 	uint32_t pf_g;          // host side only: rows in flight per team of the pre-filtered kernels (1 or 2)
 	uint32_t row_prefetch;  // 2 = auto (see the gather), 1 = always prefetch the rows of a gather into L2, 0 = never
@@ -876,6 +877,9 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 			if (METRIC == LMD_METRIC_COSINE) {
 				qmul = Q.na > 0.0f ? 1.0f / sqrtf(Q.na) : 0.0f;
 				qmul = isfinite(qmul) ? qmul : 0.0f;
+			} else if (METRIC == LMD_METRIC_IP) { // the query at the rows' RMS length, so that it lands inside the grid
+				qmul = Q.na > 0.0f ? p.code_rho / sqrtf(Q.na) : 0.0f;
+				qmul = isfinite(qmul) ? qmul : 0.0f;
 			}
 			encode_query_int8(p, qi, lane, s_qi8, q_asq, q_err, qmul);
 		}
@@ -985,6 +989,23 @@ __global__ void __launch_bounds__(128, (ROUTE == LMD_KROUTE_EXACT_PF && G == 1) 
 					const float lb = 1.0f - ub;
 					const float worst0 = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
 					const bool skip = n >= L && lb > worst0 + 2e-4f;
+					gmask = __ballot_sync(FULL, isnew && !skip);
+					gm = __popc(gmask);
+					if (gm == 0) {
+						continue;
+					}
+					isnew = isnew && !skip;
+				} else if (CODES && ROUTE == LMD_KROUTE_EXACT_PF && METRIC == LMD_METRIC_IP) {
+					// IP stores: raw rows on a zero-offset grid, the query scaled to the rows' RMS length rho (u = q rho / || q ||):
+					// q.x = (|| q || / rho) u.x,  u.x <= scale^2 qi.c + || u - u^ || || x^ || + rho || x - x^ ||,  || x^ || = scale sqrt(csq);
+					// the distance of core/distance.hpp:74 is -q.x. Margin: 1e-4 || q || (|| x^ || + || x - x^ ||) >= 1e-4 || q || || x ||,
+					// against D * 2^-24 relative rounding of the exact dot product. A zero query (or an all-zero store) has
+					// err = +inf: 0 * inf is a NaN, which never compares greater - nothing is skipped.
+					const float qn = sqrtf(Q.na);
+					const float xh = p.code_scale * sqrtf((float)c_sq);
+					const float ub = (qn / p.code_rho) * (p.code_scale * p.code_scale * (float)c_dot + q_err * xh + p.code_rho * c_err);
+					const float worst0 = n >= L ? key_dist(s_list[L - 1]) : 0.0f;
+					const bool skip = n >= L && -ub > worst0 + 1e-4f * qn * (xh + c_err);
 					gmask = __ballot_sync(FULL, isnew && !skip);
 					gm = __popc(gmask);
 					if (gm == 0) {

@@ -62,7 +62,8 @@ LMD_DECL_TRAVERSE(2, 1)
 LMD_DECL_TRAVERSE(3, 1)
 LMD_DECL_TRAVERSE(1, 2) // int8 routing (L2)
 LMD_DECL_TRAVERSE(1, 3) // exact routing with the int8 pre-filter (L2)
-LMD_DECL_TRAVERSE(2, 3) // ... and COSINE (lower bound from the grid dot product)
+LMD_DECL_TRAVERSE(2, 3) // ... and COSINE / IP (lower bound from the grid dot product)
+LMD_DECL_TRAVERSE(3, 3)
 #define LMD_DECL_TRAVERSE_FILT(M, R)                                                                                   \
 	lmd_status dispatch_traverse_filt_m##M##_r##R(KParams &p, const lmd_store *s, uint32_t nq, int lpl, cudaStream_t st);
 LMD_DECL_TRAVERSE_FILT(1, 0)
@@ -137,8 +138,14 @@ static lmd_status dispatch_traverse(KParams &p, const lmd_store *s, uint32_t nq,
 		return dispatch_traverse_m1_r2(p, s, nq, lpl, st);
 	}
 	if (route == LMD_KROUTE_EXACT_PF) {
-		return p.metric == LMD_METRIC_COSINE ? dispatch_traverse_m2_r3(p, s, nq, lpl, st)
-		                                     : dispatch_traverse_m1_r3(p, s, nq, lpl, st);
+		switch (p.metric) {
+		case LMD_METRIC_COSINE:
+			return dispatch_traverse_m2_r3(p, s, nq, lpl, st);
+		case LMD_METRIC_IP:
+			return dispatch_traverse_m3_r3(p, s, nq, lpl, st);
+		default:
+			return dispatch_traverse_m1_r3(p, s, nq, lpl, st);
+		}
 	}
 	if (route == LMD_ROUTE_EXACT && p.latency == 2) {
 		switch (p.metric) {
@@ -224,7 +231,6 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 	const bool small_batch = specialised_shape && plan_family(a.nq, (uint32_t)s->sm_count, s->tune.latency_mode) != 0;
 	if (a.route == LMD_ROUTE_EXACT && s->codec == LMD_CODEC_INT8 && s->codes_gen == s->views_gen && !a.no_prefilter &&
 	    !a.d_allowed && !p.strict && s->tune.prefilter &&
-	    (s->cfg.metric == LMD_METRIC_L2 || s->cfg.metric == LMD_METRIC_COSINE) &&
 	    (!small_batch || s->tune.prefilter == 2)) {
 		kroute = LMD_KROUTE_EXACT_PF;
 	}
@@ -241,6 +247,7 @@ lmd_status launch_traverse(const TraverseArgs &a, cudaStream_t st) {
 		p.side_data_off = s->code_data_off;
 		p.code_off = s->d_code_off;
 		p.code_scale = s->code_scale;
+		p.code_rho = s->code_rho;
 	}
 	int lpl = lpl_for(a.L + tie_slots);
 	if (!lpl) {

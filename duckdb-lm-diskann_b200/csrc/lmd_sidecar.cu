@@ -116,10 +116,13 @@ __global__ void code_stats_unit_kernel(const float *__restrict__ vecs, uint32_t 
 __global__ void code_params_kernel(const double *__restrict__ sum, const double *__restrict__ sumsq, uint64_t n,
                                    uint32_t dims, uint32_t row_floats, float sigmas, int centred, float *__restrict__ off) {
 	__shared__ float s_max[256];
+	__shared__ double s_tot[256];
 	float mx = 0.0f;
+	double tot = 0.0; // sum over d of E[x_d^2] = mean squared row length
 	for (uint32_t d = threadIdx.x; d < row_floats; d += blockDim.x) {
 		float o = 0.0f;
 		if (d < dims) {
+			tot += sumsq[d] / (double)n;
 			const double m = centred ? sum[d] / (double)n : 0.0;
 			double var = sumsq[d] / (double)n - m * m;
 			var = var > 0.0 ? var : 0.0;
@@ -129,16 +132,19 @@ __global__ void code_params_kernel(const double *__restrict__ sum, const double 
 		off[d] = o;
 	}
 	s_max[threadIdx.x] = mx;
+	s_tot[threadIdx.x] = tot;
 	__syncthreads();
 	for (uint32_t st = blockDim.x / 2; st > 0; st >>= 1) {
 		if (threadIdx.x < st) {
 			s_max[threadIdx.x] = fmaxf(s_max[threadIdx.x], s_max[threadIdx.x + st]);
+			s_tot[threadIdx.x] += s_tot[threadIdx.x + st];
 		}
 		__syncthreads();
 	}
 	if (threadIdx.x == 0) {
 		const float sc = sigmas * s_max[0] / 127.0f;
 		off[row_floats] = sc > 0.0f ? sc : 1.0f;
+		off[row_floats + 1] = (float)sqrt(s_tot[0]); // rho: the RMS row length (IP stores scale the query to it)
 	}
 }
 
@@ -259,7 +265,7 @@ lmd_status build_code_side(lmd_store *s) {
 		return rc;
 	}
 	if (!s->d_code_off) {
-		LMD_CUDA_OK(cudaMalloc((void **)&s->d_code_off, (rf + 1) * sizeof(float)));
+		LMD_CUDA_OK(cudaMalloc((void **)&s->d_code_off, (rf + 2) * sizeof(float)));
 	}
 	double *d_stats = nullptr;
 	LMD_CUDA_OK(cudaMalloc((void **)&d_stats, 2 * (size_t)rf * sizeof(double)));
@@ -274,17 +280,23 @@ lmd_status build_code_side(lmd_store *s) {
 	}
 	const float sigmas = s->tune.code_sigmas > 0 ? (float)s->tune.code_sigmas * 0.1f : 4.0f;
 	const int cosine = s->cfg.metric == LMD_METRIC_COSINE ? 1 : 0;
-	code_params_kernel<<<1, 256, 0, s->stream>>>(d_stats, d_stats + rf, s->n, s->cfg.dims, rf, sigmas, cosine ? 0 : 1,
-	                                             s->d_code_off);
+	// L2: per-dimension means as offsets (a difference cancels them); COSINE / IP: a dot product does not, zero offsets
+	code_params_kernel<<<1, 256, 0, s->stream>>>(d_stats, d_stats + rf, s->n, s->cfg.dims, rf, sigmas,
+	                                             s->cfg.metric == LMD_METRIC_L2 ? 1 : 0, s->d_code_off);
 	build_code_side_kernel<<<(unsigned)((s->n * 32 + 255) / 256), 256, 0, s->stream>>>(
 	    s->d_vecs, rf, s->cfg.dims, r, s->n, s->d_nbrs, s->d_code_off, s->d_codes, s->code_block_bytes, s->code_data_off,
 	    cosine);
+	float h_par[2] = {1.0f, 0.0f}; // scale, rho
 	cudaError_t e = cudaGetLastError();
 	if (e == cudaSuccess) {
-		e = cudaMemcpyAsync(&s->code_scale, s->d_code_off + rf, sizeof(float), cudaMemcpyDeviceToHost, s->stream);
+		e = cudaMemcpyAsync(h_par, s->d_code_off + rf, 2 * sizeof(float), cudaMemcpyDeviceToHost, s->stream);
 	}
 	if (e == cudaSuccess) {
 		e = cudaStreamSynchronize(s->stream);
+	}
+	if (e == cudaSuccess) {
+		s->code_scale = h_par[0];
+		s->code_rho = h_par[1];
 	}
 	cudaFree(d_stats);
 	if (e != cudaSuccess) {
@@ -352,12 +364,8 @@ lmd_status lmd_store_enable_codec(lmd_store *s, uint32_t codec) {
 		set_error("lmd_store_enable_codec: unknown codec %u", codec);
 		return LMD_ERR_INVALID_ARG;
 	}
-	if (codec == LMD_CODEC_INT8 && s->cfg.metric == LMD_METRIC_IP) {
-		// L2: the grid distance || q^ - x^ || bounds and approximates the distance (pre-filter and LMD_ROUTE_INT8);
-		// COSINE: the grid dot product bounds it (pre-filter of the exact route only); IP has the ternary codec
-		set_error("the int8 edge codec is defined for the L2 and COSINE metrics only");
-		return LMD_ERR_UNSUPPORTED;
-	}
+	// L2: the grid distance || q^ - x^ || bounds and approximates the distance (pre-filter and LMD_ROUTE_INT8);
+	// COSINE / IP: the grid dot product bounds it (pre-filter of the exact route only)
 	{
 		std::unique_lock<std::shared_mutex> g(s->mu);
 		s->codec = codec;

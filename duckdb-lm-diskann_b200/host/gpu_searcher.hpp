@@ -89,9 +89,9 @@ public:
 	common::idx_t BlockBytes() const {
 		return block_bytes_;
 	}
-	// int8 code sidecar (lmd_store_enable_codec): exact searches of an L2 / COSINE index then fetch only the rows an int8
-	// lower bound cannot exclude - same ids and distances, about a quarter of the vector bytes. Costs R * dims bytes per
-	// node of device memory; throws for IP (the codes bound a distance or a cosine, not a bare dot product).
+	// int8 code sidecar (lmd_store_enable_codec): exact searches then fetch only the rows an int8 lower bound cannot
+	// exclude - same ids and distances, a quarter to a third of the vector bytes. Costs R * dims bytes per node of device
+	// memory.
 	void SetEdgeCodec(bool on);
 	lmd_store *Handle() const {
 		return store_;

@@ -152,10 +152,11 @@ lmd_status lmd_store_download_block(lmd_store *s, int64_t row_id, void *out_bloc
 lmd_status lmd_store_set_stream(lmd_store *s, void *cuda_stream);
 /* int8 edge codec (row f4). Builds (and from then on keeps up to date, lazily, before the next search that needs it)
  * the code sidecar: 12 R + R * dims bytes per node. With it, LMD_ROUTE_INT8 searches work (L2 stores), and
- * LMD_ROUTE_EXACT searches of an L2 or COSINE store use the codes as a LOWER BOUND that decides which neighbours' vectors
+ * LMD_ROUTE_EXACT searches (any metric) use the codes as a LOWER BOUND that decides which neighbours' vectors
  * are fetched at all - results, distances and expansion counts stay bit-identical to the plain traversal (see
  * LMD_SEARCH_NO_PREFILTER). L2: codes of x on a per-dimension-centred grid, bound from the grid distance; COSINE: codes
- * of x / || x || on a zero-offset grid, bound from the grid dot product. IP stores: LMD_ERR_UNSUPPORTED. */
+ * of x / || x || on a zero-offset grid, IP: codes of x on a zero-offset grid with the query scaled to the rows' RMS
+ * length - bound from the grid dot product. */
 lmd_status lmd_store_enable_codec(lmd_store *s, uint32_t codec);
 /* The codec's grid: offsets [dims] (host buffer) and the scale; x ~ offsets[d] + scale * code[d]. LMD_ERR_STATE while no
  * codec is built. */

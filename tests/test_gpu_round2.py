@@ -198,7 +198,7 @@ def test_int8_route_parity(lmd, oracle, make_index, fixtures_mod, n, dims, r, ki
 
 
 def test_int8_codec_metrics(lmd, make_index):
-    """int8 ROUTING is L2-only; the code sidecar (pre-filter of the exact route) exists for L2 and COSINE, not for IP."""
+    """int8 ROUTING is L2-only; the code sidecar (pre-filter of the exact route) exists for all three metrics."""
     for metric in ("COSINE", "IP"):
         ix = make_index(1200, 33, 16, metric=metric, kind="clustered", nq=8)
         with _store(lmd, ix, 33, 16, metric) as s:
@@ -207,25 +207,22 @@ def test_int8_codec_metrics(lmd, make_index):
             with pytest.raises(lmd.LmdError) as e:
                 s.search(ix["queries"], 5, 32, route=lmd.ROUTE_INT8)
             assert e.value.status == lmd.ERR_UNSUPPORTED
-            if metric == "IP":
-                with pytest.raises(lmd.LmdError):
-                    s.enable_codec()
-            else:
-                s.enable_codec()
-                with pytest.raises(lmd.LmdError) as e:
-                    s.search(ix["queries"], 5, 32, route=lmd.ROUTE_INT8)
-                assert e.value.status == lmd.ERR_UNSUPPORTED
+            s.enable_codec()
+            with pytest.raises(lmd.LmdError) as e:
+                s.search(ix["queries"], 5, 32, route=lmd.ROUTE_INT8)
+            assert e.value.status == lmd.ERR_UNSUPPORTED
 
 
 @pytest.mark.parametrize("n,dims,r,kind,L,metric", [
     (6000, 128, 32, "clustered", 64, "L2"), (4000, 96, 32, "clustered", 128, "L2"), (3000, 128, 64, "iid", 32, "L2"),
     (3000, 100, 24, "clustered", 256, "L2"), (2000, 768, 32, "clustered", 64, "L2"),
     (5000, 128, 32, "clustered", 64, "COSINE"), (2000, 768, 32, "clustered", 80, "COSINE"),
-    (3000, 100, 24, "iid", 48, "COSINE"), (3000, 96, 32, "clustered", 128, "COSINE")])
+    (3000, 100, 24, "iid", 48, "COSINE"), (3000, 96, 32, "clustered", 128, "COSINE"),
+    (5000, 128, 32, "clustered", 64, "IP"), (2000, 768, 32, "clustered", 48, "IP"), (3000, 100, 24, "iid", 64, "IP")])
 def test_prefilter_changes_nothing_but_the_bytes(lmd, oracle, make_index, n, dims, r, kind, L, metric):
     """Exact routing on a codec store: the int8 lower bound only skips rows that the list would have turned away, so ids,
     distance BITS and per-query expansion / evaluation counts equal the plain traversal's - with fewer rows fetched.
-    L2: bound from the grid distance; COSINE: from the grid dot product (zero-offset grid, || x || in the sidecar)."""
+    L2: bound from the grid distance; COSINE / IP: from the grid dot product (zero-offset grid; unit rows for COSINE)."""
     ix = make_index(n, dims, r, metric=metric, kind=kind, nq=128)
     k = 10
     with _store(lmd, ix, dims, r, metric) as s:
@@ -266,11 +263,12 @@ def test_prefilter_changes_nothing_but_the_bytes(lmd, oracle, make_index, n, dim
     assert pf[3].algorithmic_bytes != plain[3].algorithmic_bytes
 
 
-def test_cosine_prefilter_with_unnormalised_rows(lmd, fixtures_mod):
+@pytest.mark.parametrize("metric", ["COSINE", "IP"])
+def test_cosine_prefilter_with_unnormalised_rows(lmd, fixtures_mod, metric):
     """The cosine lower bound divides by || q || || x ||: rows and queries of any length, a zero row and a zero query must
     come out exactly as without the pre-filter (core/distance.hpp:85-98: zero norm -> distance 1.0)."""
     n, dims, r, k, L = 4000, 128, 32, 10, 64
-    ix = fixtures_mod.build_index(n, dims, r, metric="COSINE", kind="clustered", device="cpu")
+    ix = fixtures_mod.build_index(n, dims, r, metric=metric, kind="clustered", device="cpu")
     rng = np.random.default_rng(11)
     x = np.asarray(ix["x"], dtype=np.float32) * rng.uniform(0.05, 20.0, size=(n, 1)).astype(np.float32)
     x[17] = 0.0
@@ -279,7 +277,7 @@ def test_cosine_prefilter_with_unnormalised_rows(lmd, fixtures_mod):
     q = np.ascontiguousarray(np.asarray(fixtures_mod.make_dataset(128, dims, kind="clustered", seed=5, normalize=True),
                                         dtype=np.float32) * rng.uniform(0.01, 100.0, size=(128, 1)).astype(np.float32))
     q[3] = 0.0
-    with lmd.Store(dims, r, metric=lmd.METRIC_COSINE, capacity=n) as s:
+    with lmd.Store(dims, r, metric=METRIC[metric], capacity=n) as s:
         s.upload(blocks)
         s.set_entry(0)
         plain = s.search(q, k, L, qstats=True)
