@@ -17,6 +17,8 @@ ap.add_argument("--dims", type=int, default=128)
 ap.add_argument("--nq", type=int, default=10_000)
 ap.add_argument("--filter-log2", type=int, nargs="*", default=[0], help="visited-filter sizes to compare (0 = the library's choice)")
 ap.add_argument("--fracs", type=float, nargs="*", default=[1.0, 0.5, 0.1, 0.01])
+ap.add_argument("--Ls", type=int, nargs="*", default=[64, 128, 256])
+ap.add_argument("--tune", nargs="*", default=[], help="lmd_set_tuning pairs, e.g. filter_mode=3 filter_entries=3072")
 a = ap.parse_args()
 lmd = importlib.import_module("duckdb-lm-diskann_b200")
 dev = torch.device("cuda", 0)
@@ -24,6 +26,8 @@ x = gen(a.n, a.dims, 42, dev, False)
 q = gen(a.nq, a.dims, 43, dev, False)
 store = lmd.Store(a.dims, 32, capacity=a.n)
 store.upload_vectors(x); store.build_graph(l_insert=64)
+for kv in a.tune:
+    store.set_tuning(kv.split("=")[0], int(kv.split("=")[1]))
 ids = torch.empty((a.nq, 10), dtype=torch.int64, device=dev)
 cnt = torch.empty((a.nq,), dtype=torch.int32, device=dev)
 rows = []
@@ -36,7 +40,7 @@ for frac in a.fracs:
     truth = allowed[ti]
     del xs
     with store.make_filter(allowed) as f:
-        for L, flg in [(L, v) for L in (64, 128, 256) for v in a.filter_log2]:
+        for L, flg in [(L, v) for L in a.Ls for v in a.filter_log2]:
             store.set_tuning("filter_log2", flg)
             best = None
             for i in range(5):
