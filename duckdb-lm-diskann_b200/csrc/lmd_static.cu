@@ -5,7 +5,9 @@
 // rerank kernel reads - placed in a file-scope __device__ array of LMD_STATIC_SCRATCH_BYTES instead of cudaMalloc'ed
 // memory. Every device that loads the library holds that array until the process exits.
 //
-// This file calls no cudaMalloc / cudaFree / cudaHostAlloc and no allocating library routine. The store's own device
+// This file calls no cudaMalloc / cudaFree / cudaHostAlloc and no allocating library routine (what the launch path may
+// still do on the HOST: one entry in the store's launch cache, a std::unordered_map, the first time a kernel / shared-memory
+// size pair is launched, after its occupancy query). The store's own device
 // memory was allocated earlier, by lmd_store_create / upload / a first regular search; a route whose sidecar is not built yet is
 // refused here (building one allocates), not prepared.
 //
