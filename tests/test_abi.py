@@ -87,3 +87,15 @@ def test_product_does_not_touch_oracle():
                 txt = open(os.path.join(dp, f)).read()
                 assert "pyoracle" not in txt and "lmd_oracle" not in txt and "lmdo_" not in txt and \
                     "lmdref_" not in txt, os.path.join(dp, f)
+
+
+def test_static_scratch_entry_point_host_side(lmd):
+    """lmd_search_batch_static (no counterpart in the reference): its stated limit and the argument checks that come
+    before any CUDA call - no compute without a GPU."""
+    import ctypes as C
+    lib = lmd.lib()
+    assert lib.lmd_static_scratch_bytes() == 8 << 20
+    q = (C.c_float * 4)()
+    out = (C.c_int64 * 4)()
+    rc = lib.lmd_search_batch_static(None, q, 1, 1, 0, lmd.ROUTE_EXACT, 0, out, q, out, None)
+    assert rc == lmd.ERR_INVALID_ARG and b"null store" in lib.lmd_last_error()
