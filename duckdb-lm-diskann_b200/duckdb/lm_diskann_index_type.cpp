@@ -29,6 +29,14 @@ idx_t LmDiskannSettings::ListSize(ClientContext &context, const ::diskann::core:
 	return config.l_search;
 }
 
+bool LmDiskannSettings::EdgeCodec(ClientContext &context) {
+	Value opt;
+	if (context.TryGetCurrentSetting(EDGE_CODEC, opt) && !opt.IsNull() && opt.type() == LogicalType::BOOLEAN) {
+		return opt.GetValue<bool>();
+	}
+	return true;
+}
+
 ::diskann::b200::GpuSearcher *LmDiskannGpuSearcherOf(LmDiskannIndex &index) {
 	auto *coordinator = index.GetCoordinator();
 	if (!coordinator) {
@@ -163,6 +171,10 @@ void LmDiskannModule::RegisterIndexType(DatabaseInstance &db) {
 	db.config.AddExtensionOption(LmDiskannSettings::GPU_DEVICES,
 	                             "LM_DISKANN: number of GPUs a newly opened index is mirrored to (query-sharded replicas)",
 	                             LogicalType::BIGINT, Value::BIGINT(1));
+	db.config.AddExtensionOption(LmDiskannSettings::EDGE_CODEC,
+	                             "LM_DISKANN: keep the int8 code sidecar on the device mirror (exact searches fetch only the "
+	                             "rows its lower bound cannot exclude; same results; R * dims bytes per node)",
+	                             LogicalType::BOOLEAN, Value::BOOLEAN(true));
 	db.config.GetIndexTypes().RegisterIndexType(type);
 }
 

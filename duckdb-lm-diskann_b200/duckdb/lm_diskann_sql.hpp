@@ -38,6 +38,9 @@ using LmDiskannIndex = ::diskann::db::LmDiskannIndex;
 struct LmDiskannSettings {
 	static constexpr const char *L_SEARCH = "lm_diskann_l_search";   // search list size override, 0 / unset = index default
 	static constexpr const char *GPU_DEVICES = "lm_diskann_gpu_devices"; // how many devices a new index mirrors itself to
+	// int8 code sidecar on the device mirror (DeviceNodeStore::SetEdgeCodec): same results, fewer vector bytes per search
+	static constexpr const char *EDGE_CODEC = "lm_diskann_edge_codec";
+	static bool EdgeCodec(ClientContext &context); // the setting; true when unset
 	// L for a scan of `index` in `context`: the setting when it is a positive BIGINT, else config.l_search
 	// (core/Searcher.cpp:261-265 resolves 0 further)
 	static idx_t ListSize(ClientContext &context, const ::diskann::core::LmDiskannConfig &config);
